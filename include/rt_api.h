@@ -1,0 +1,241 @@
+/* rt_api.h — C ABI of librt.so, the B200-native path-tracing core.
+ *
+ * The boundary is cut along the three calls the reference's renderer makes on its GPU scene
+ * (reference paths are relative to ARTurleite6/RayTracer):
+ *   build   gpu_scene_init / gpu_scene_bake            src/raytracer/gpu_scene.odin:45-118
+ *   trace   raytracing_renderer_render_scene           src/raytracer/raytracing_renderer.odin:194-270
+ *           -> command_buffer_trace_rays               src/raytracer/command_buffer.odin:261-274
+ *   consume the RGBA32F output image (blit source)     src/raytracer/raytracing_renderer.odin:271-339
+ * plus resize (:108-126), destroy (gpu_scene.odin:49-75) and the incremental update set
+ * (gpu_scene.odin:430-601).  All record layouts are the reference's own, so an Odin host can
+ * hand over raw_data(slice) pointers (INTEGRATION.md shows the `foreign import` block).
+ *
+ * Conventions: every entry point returns RT_OK (0) or a negative rt_status; the message of the
+ * last failure is kept per context (rt_last_error).  Nothing aborts the host (the reference's
+ * vk_check calls os.exit(1): src/raytracer/vulkan_context.odin:385-394).  The caller owns every
+ * input array; the library copies during the call and keeps no host pointer.  One rt_ctx is
+ * used from one host thread at a time; calls are ordered on the context's CUDA stream.
+ * There is no CPU fallback: rt_create fails with RT_ERR_NO_DEVICE when no sm_100 GPU is usable.
+ */
+#ifndef RT_API_H
+#define RT_API_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define RT_API __attribute__((visibility("default")))
+#else
+#define RT_API
+#endif
+
+typedef struct rt_ctx rt_ctx;
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID_ARGUMENT = -1,
+    RT_ERR_NO_DEVICE = -2,
+    RT_ERR_CUDA = -3,
+    RT_ERR_OUT_OF_MEMORY = -4,
+    RT_ERR_NO_SCENE = -5,
+    RT_ERR_NO_TARGET = -6,
+    RT_ERR_BVH_TOO_DEEP = -7,
+    RT_ERR_INDEX_RANGE = -8
+} rt_status;
+
+/* flags mirror the compile-time switches of shaders/simple.rchit:9-11 */
+enum {
+    RT_FLAG_DIRECT_LIGHTING = 1u << 0, /* USE_DIRECT_LIGHTING 1 */
+    RT_FLAG_MIS = 1u << 1,             /* USE_MIS 1 */
+    RT_FLAG_COUNTERS = 1u << 2,        /* maintain device ray/node/triangle counters */
+    RT_FLAG_DEFAULT = (1u << 0) | (1u << 1) | (1u << 2)
+};
+
+/* frame pipelines */
+enum {
+    RT_PIPELINE_WAVEFRONT = 0, /* raygen -> extend -> shade -> shadow queues (default) */
+    RT_PIPELINE_MEGAKERNEL = 1 /* one persistent kernel, one path per thread */
+};
+
+typedef struct rt_config {
+    int32_t device;          /* CUDA ordinal; -1 = current device */
+    int32_t max_depth;       /* shaders/simple.rgen:23  MAX_DEPTH = 3 */
+    int32_t rr_start_depth;  /* shaders/simple.rgen:56  roulette is a no-op below depth 3 */
+    float radiance_clamp;    /* shaders/simple.rgen:121 min(color, 5.0) */
+    uint32_t flags;          /* RT_FLAG_* */
+    uint32_t pipeline;       /* RT_PIPELINE_* */
+    /* screen-tile sharding: this context renders the image rows y with
+     * (y / strip_rows) % strip_count == strip_index; seeds and camera rays always use the full
+     * launch size, so the union over ranks is bit-identical to strip_count == 1. */
+    uint32_t strip_rows;   /* 0 -> 8 */
+    uint32_t strip_index;  /* rank */
+    uint32_t strip_count;  /* world size; 0 -> 1 */
+    uint32_t reserved[7];
+} rt_config;
+
+/* scene.odin:10-13 / ray_common.glsl:48-51 — 24 B */
+typedef struct rt_vertex {
+    float pos[3];
+    float normal[3];
+} rt_vertex;
+
+/* scene.odin:56-60 */
+typedef struct rt_mesh {
+    const rt_vertex* vertices;
+    uint32_t n_vertices;
+    const uint32_t* indices; /* triangle list, 3 per triangle (acceleration_structure.odin:32-63) */
+    uint32_t n_indices;
+} rt_mesh;
+
+/* scene.odin:41-54 — the object's model matrix is column-major (m[c*4+r]) */
+typedef struct rt_object {
+    uint32_t mesh_index;
+    uint32_t material_index;
+    float model[16];
+} rt_object;
+
+/* gpu_scene.odin:17-21 / ray_common.glsl:3-11 — 44 B scalar layout */
+typedef struct rt_material {
+    float albedo[3];
+    float emission_color[3];
+    float emission_power;
+    float roughness;
+    float metallic;
+    float transmission;
+    float ior;
+} rt_material;
+
+/* push constant of the trace (raytracing_renderer.odin:33-36 / simple.rgen:18-21) is passed as
+ * (clear_color, frame_number); Camera_UBO (camera.odin:15-20) as 64 floats:
+ * proj, view, inverse_view, inverse_proj, each column-major. */
+
+typedef struct rt_counters {
+    uint64_t extend_rays;   /* closest-hit rays issued (traceRayEXT, simple.rgen:92-104) */
+    uint64_t shadow_rays;   /* visibility rays issued (isVisibleRQ, simple.rchit:350-385) */
+    uint64_t nodes;         /* BVH8 nodes fetched (80 B each) */
+    uint64_t tris;          /* triangles fetched (48 B each) */
+    uint64_t hits;          /* closest-hit shader invocations */
+    uint64_t nee;           /* light samples taken */
+    uint64_t frames;        /* rt_trace_frame calls since the last reset */
+    uint64_t reserved;
+} rt_counters;
+
+typedef struct rt_scene_info {
+    uint32_t n_triangles;   /* instanced, world-space */
+    uint32_t n_nodes;       /* BVH8 nodes */
+    uint32_t bvh_depth;
+    uint32_t n_lights;
+    uint32_t n_objects;
+    uint32_t n_materials;
+    float build_ms;         /* device time of the last BVH build */
+    uint32_t reserved;
+} rt_scene_info;
+
+/* 32-byte reservoir, shaders/restir/restir_structs.glsl:1-12 */
+typedef struct rt_reservoir {
+    float weight_sum;
+    float target_pdf;
+    uint32_t M;
+    uint32_t light_index;   /* 0xFFFFFFFF = empty (RTXDI_EmptyDIReservoir, :14-23) */
+    float uv[2];
+    float distance;         /* carries the sampled light triangle index (as bits) in this build */
+    float W;
+} rt_reservoir;
+
+enum {
+    RT_RESTIR_TEMPORAL = 1u << 0,
+    RT_RESTIR_SPATIAL = 1u << 1
+};
+
+typedef struct rt_restir_params {
+    uint32_t flags;              /* RT_RESTIR_* */
+    uint32_t initial_candidates; /* light candidates per pixel (default 8) */
+    uint32_t spatial_samples;    /* neighbours per pixel (default 4) */
+    float spatial_radius;        /* pixels (default 16) */
+    uint32_t history_cap;        /* M clamp multiple for temporal reuse (default 20) */
+    uint32_t reserved[3];
+} rt_restir_params;
+
+/* ---- lifetime ------------------------------------------------------------------------- */
+RT_API int rt_create(const rt_config* cfg, rt_ctx** out);
+RT_API void rt_destroy(rt_ctx* ctx);
+RT_API void rt_default_config(rt_config* cfg);
+RT_API const char* rt_last_error(const rt_ctx* ctx); /* ctx may be NULL: error of the last rt_create */
+RT_API const char* rt_version(void);
+
+/* ---- build: replaces gpu_scene_init (gpu_scene.odin:45-118) -------------------------------
+ * Derives lights (objects whose material has emission_power > 0, :366-379), instance masks and
+ * light_index exactly as the reference does, flattens instances to world space and builds the
+ * BVH8 on the GPU. */
+RT_API int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const rt_object* objects,
+                   uint32_t n_objects, const rt_material* materials, uint32_t n_materials);
+RT_API int rt_scene_info_get(rt_ctx* ctx, rt_scene_info* out);
+
+/* ---- incremental updates: gpu_scene.odin:430-601 (applied before the next trace) ----------- */
+RT_API int rt_update_material(rt_ctx* ctx, uint32_t material_index, const rt_material* m);      /* :430-455 */
+RT_API int rt_update_object_transform(rt_ctx* ctx, uint32_t object_index, const float model[16]); /* :457-515 */
+RT_API int rt_update_object_material(rt_ctx* ctx, uint32_t object_index, uint32_t material_index); /* :517-560 */
+RT_API int rt_update_object_mesh(rt_ctx* ctx, uint32_t object_index, uint32_t mesh_index);       /* :562-601 */
+
+/* ---- target: raytracing_renderer_on_resize (raytracing_renderer.odin:108-126) -------------- */
+RT_API int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height);
+
+/* ---- trace: one sample per pixel, stream-ordered (like a recorded command buffer) ---------
+ * frame_number == 0 overwrites the image, otherwise running mean (simple.rgen:127-136). */
+RT_API int rt_trace_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t frame_number);
+/* n consecutive frames with an unchanged camera == n calls of rt_trace_frame
+ * (application loop, application.odin:109-115); lets terminated paths regenerate across frames. */
+RT_API int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
+                    uint32_t n_frames);
+RT_API int rt_synchronize(rt_ctx* ctx);
+
+/* ---- consume ----------------------------------------------------------------------------
+ * rt_readback: synchronises and copies this context's rows into a full-size W*H RGBA32F host
+ * image (rows owned by other strips are left untouched). */
+RT_API int rt_readback(rt_ctx* ctx, float* dst_rgba32f, size_t bytes);
+/* what the blit to B8G8R8A8_SRGB shows (raytracing_renderer.odin:299-316): clamp01 + sRGB OETF */
+RT_API int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst_rgba8, size_t bytes);
+/* device-resident compact strip buffer (local_rows * W * 4 floats) for NCCL gathers by the host */
+RT_API int rt_device_image(rt_ctx* ctx, void** device_ptr, uint32_t* local_rows);
+/* checkpoint/resume of a long accumulation: upload a full-size image as the running mean */
+RT_API int rt_upload_accum(rt_ctx* ctx, const float* src_rgba32f, size_t bytes);
+
+/* ---- G-buffer pass: shaders/restir.rgen:43-92, restir.rchit:36-59, restir.rmiss:18-20 ------ */
+RT_API int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]);
+/* any pointer may be NULL.  albedo/output rgba8 (4 B), normal_rough/emission rgba16f (8 B),
+ * position_metal rgba32f (16 B) per pixel, full-size W*H images. */
+RT_API int rt_readback_gbuffer(rt_ctx* ctx, uint8_t* albedo, uint16_t* normal_rough, float* position_metal,
+                        uint16_t* emission, uint8_t* output);
+
+/* ---- ReSTIR DI on the G-buffer (layout: shaders/restir/restir_structs.glsl; algorithm: the
+ * reference has none — shaders/restir/restir_di.rgen:17-22 is a stub; parity unpinned) -------- */
+RT_API void rt_default_restir_params(rt_restir_params* p);
+RT_API int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t frame_number,
+                    const rt_restir_params* params);
+RT_API int rt_readback_reservoirs(rt_ctx* ctx, rt_reservoir* dst, size_t bytes);
+
+/* ---- instrumentation -------------------------------------------------------------------- */
+RT_API int rt_get_counters(rt_ctx* ctx, rt_counters* out);
+RT_API int rt_reset_counters(rt_ctx* ctx);
+/* device time (ms) of the last rt_trace_frame(s)/rt_restir_frame/rt_trace_gbuffer call */
+RT_API int rt_last_trace_ms(rt_ctx* ctx, float* ms);
+
+/* ---- verification hooks (used by tests; same kernels as the frame path) --------------------
+ * rays: n x 8 floats (ox,oy,oz,tmin, dx,dy,dz,tmax), host memory.
+ * closest: out_tuv n x 3 floats, out_id n x u32 flat triangle id (0xFFFFFFFF = miss).
+ * any: out_occluded n x u32 (1 = a triangle of an instance != ignore_inst[i] lies in range). */
+RT_API int rt_trace_rays_closest(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id);
+RT_API int rt_trace_rays_any(rt_ctx* ctx, const float* rays, uint32_t n, const uint32_t* ignore_inst, uint32_t* out_occluded);
+/* BVH download for the bit-exact comparison with the deterministic CPU twin.
+ * nodes: n_nodes x 80 B, tris: n_triangles x 48 B, morton/sorted ids: n_triangles each; NULL skips. */
+RT_API int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t tris_bytes, uint64_t* morton,
+               uint32_t* sorted_ids);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_API_H */

@@ -1,0 +1,641 @@
+// rt_api.cu — the C ABI of librt.so (include/rt_api.h): context, scene tables, frame loop plumbing.
+// Host-side data preparation mirrors src/raytracer/gpu_scene.odin (:120-150 instances, :317-397
+// objects and lights, :399-428 materials, :430-601 incremental updates).  All arithmetic that shapes
+// pixels runs in the CUDA kernels; there is no CPU rendering path in this library.
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "rt_internal.h"
+
+using namespace rt;
+
+static thread_local std::string g_create_error;
+
+#define CTX_CHECK(ctx)                          \
+    if (!(ctx)) return RT_ERR_INVALID_ARGUMENT; \
+    cudaSetDevice((ctx)->device);
+#define set_error ctx->set_error
+
+extern "C" {
+
+const char* rt_version(void) { return "raytracer_b200 librt 0.1 (sm_100a)"; }
+
+void rt_default_config(rt_config* cfg) {
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->device = -1;
+    cfg->max_depth = 3;        // shaders/simple.rgen:23
+    cfg->rr_start_depth = 3;   // shaders/simple.rgen:56
+    cfg->radiance_clamp = 5.0f;  // shaders/simple.rgen:121
+    cfg->flags = RT_FLAG_DEFAULT;
+    cfg->pipeline = RT_PIPELINE_WAVEFRONT;
+    cfg->strip_rows = 8;
+    cfg->strip_index = 0;
+    cfg->strip_count = 1;
+}
+
+const char* rt_last_error(const rt_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int rt_create(const rt_config* cfg_in, rt_ctx** out) {
+    if (!out) return RT_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    rt_config cfg;
+    if (cfg_in) cfg = *cfg_in; else rt_default_config(&cfg);
+    if (cfg.strip_rows == 0) cfg.strip_rows = 8;
+    if (cfg.strip_count == 0) cfg.strip_count = 1;
+    if (cfg.max_depth < 1 || cfg.rr_start_depth < 1 || cfg.strip_index >= cfg.strip_count ||
+        cfg.pipeline > RT_PIPELINE_MEGAKERNEL || !(cfg.radiance_clamp == cfg.radiance_clamp)) {
+        g_create_error = "rt_create: invalid configuration";
+        return RT_ERR_INVALID_ARGUMENT;
+    }
+    if ((cfg.flags & (RT_FLAG_DIRECT_LIGHTING | RT_FLAG_MIS)) != (RT_FLAG_DIRECT_LIGHTING | RT_FLAG_MIS)) {
+        g_create_error = "rt_create: only USE_DIRECT_LIGHTING=1, USE_MIS=1 (the shipped shader) is built";
+        return RT_ERR_INVALID_ARGUMENT;
+    }
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
+        cudaGetLastError();
+        g_create_error = "rt_create: no CUDA device (this library has no CPU fallback)";
+        return RT_ERR_NO_DEVICE;
+    }
+    int dev = cfg.device;
+    if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) dev = 0; }
+    if (dev >= n_dev) { g_create_error = "rt_create: device ordinal out of range"; return RT_ERR_NO_DEVICE; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major != 10) {
+        g_create_error = "rt_create: device is not sm_100 (kernels are built for sm_100a only)";
+        return RT_ERR_NO_DEVICE;
+    }
+    if (cudaSetDevice(dev) != cudaSuccess) { g_create_error = "rt_create: cudaSetDevice failed"; return RT_ERR_CUDA; }
+    rt_ctx* ctx = new rt_ctx();
+    ctx->cfg = cfg;
+    ctx->device = dev;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+        ctx->counters.alloc(1) != cudaSuccess) {
+        g_create_error = std::string("rt_create: ") + cudaGetErrorString(cudaGetLastError());
+        delete ctx;
+        return RT_ERR_CUDA;
+    }
+    cudaMemsetAsync(ctx->counters.p, 0, sizeof(DevCounters), ctx->stream);
+    *out = ctx;
+    return RT_OK;
+}
+
+void rt_destroy(rt_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->wf) wavefront_free(ctx->wf);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+}  // extern "C"
+
+// ---- scene tables ------------------------------------------------------------------------------
+static void make_dev_object(const rt_ctx* ctx, uint32_t i, uint32_t tri_offset, DevObject* o) {
+    const rt_object& src = ctx->objects[i];
+    const HostMesh& m = ctx->meshes[src.mesh_index];
+    memset(o, 0, sizeof(*o));
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 3; r++) o->model[c * 3 + r] = src.model[c * 4 + r];
+    o->material_index = src.material_index;
+    o->light_index = ctx->light_index[i];
+    o->vertex_base = m.vertex_base;
+    o->index_base = m.index_base;
+    o->tri_offset = tri_offset;
+    o->n_tris = (uint32_t)(m.idx.size() / 3);
+    o->mesh_index = src.mesh_index;
+}
+
+__global__ void normal_matrix_kernel(DevObject* objects, uint32_t n) {
+    // transpose(inverse(mat3(ObjectToWorld))) for simple.rchit:607, evaluated once per object with the
+    // contract's arithmetic (cofactors / determinant)
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    DevObject* o = objects + i;
+    float m16[16];
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 3; r++) m16[c * 4 + r] = o->model[c * 3 + r];
+    cofactor_normal_matrix(m16, o->nrm);
+}
+
+static int upload_tables(rt_ctx* ctx) {
+    const uint32_t no = (uint32_t)ctx->objects.size();
+    std::vector<DevObject> dobj(no);
+    std::vector<uint32_t> offs(no + 1);
+    std::vector<DevLight> lights;
+    uint32_t off = 0;
+    for (uint32_t i = 0; i < no; i++) {
+        offs[i] = off;
+        make_dev_object(ctx, i, off, &dobj[i]);
+        off += dobj[i].n_tris;
+        // a light is any object whose material has emission_power > 0 (gpu_scene.odin:366-379)
+        const rt_material& mat = ctx->materials[ctx->objects[i].material_index];
+        if (mat.emission_power > 0.0f) {
+            DevLight l;
+            memcpy(l.transform, dobj[i].model, sizeof(l.transform));
+            l.object_index = i;
+            l.num_triangles = dobj[i].n_tris;
+            l.instance_mask = 1u << (i & 7u);
+            l.emission_power = mat.emission_power;
+            lights.push_back(l);
+        }
+    }
+    offs[no] = off;
+    ctx->n_tris = off;
+    ctx->n_lights = (uint32_t)lights.size();
+    RT_CUDA_TRY(ctx->d_objects.ensure(no));
+    RT_CUDA_TRY(ctx->d_tri_offsets.ensure(no + 1));
+    RT_CUDA_TRY(ctx->d_lights.ensure(lights.size()));
+    RT_CUDA_TRY(ctx->d_materials.ensure(ctx->materials.size()));
+    // the copies below read pageable host vectors: synchronise before they go out of scope
+    if (no) RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_objects.p, dobj.data(), no * sizeof(DevObject), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_tri_offsets.p, offs.data(), (no + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (!lights.empty())
+        RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_lights.p, lights.data(), lights.size() * sizeof(DevLight), cudaMemcpyHostToDevice, ctx->stream));
+    if (!ctx->materials.empty())
+        RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_materials.p, ctx->materials.data(), ctx->materials.size() * sizeof(rt_material),
+                                    cudaMemcpyHostToDevice, ctx->stream));
+    if (no) normal_matrix_kernel<<<(no + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_objects.p, no);
+    RT_CUDA_TRY(cudaGetLastError());
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->tables_dirty = false;
+    return RT_OK;
+}
+
+static int rebuild_bvh(rt_ctx* ctx) {
+    BuildInput in;
+    in.d_objects = ctx->d_objects.p;
+    in.d_tri_offsets = ctx->d_tri_offsets.p;
+    in.d_vertices = ctx->d_vertices.p;
+    in.d_indices = ctx->d_indices.p;
+    in.n_objects = (uint32_t)ctx->objects.size();
+    in.n_tris = ctx->n_tris;
+    std::string err;
+    const int rc = build_bvh8(in, ctx->bvh, ctx->stream, err);
+    if (rc != RT_OK) { set_error("rt_build_scene: " + err); return rc; }
+    if (ctx->bvh.depth > RT_MAX_BVH_DEPTH) {
+        set_error("rt_build_scene: BVH8 deeper than the traversal stack");
+        return RT_ERR_BVH_TOO_DEEP;
+    }
+    ctx->geometry_dirty = false;
+    return RT_OK;
+}
+
+static int flush_scene(rt_ctx* ctx) {
+    if (!ctx->has_scene) { set_error("no scene: call rt_build_scene first"); return RT_ERR_NO_SCENE; }
+    if (ctx->tables_dirty || ctx->geometry_dirty) {
+        const bool geo = ctx->geometry_dirty;
+        int rc = upload_tables(ctx);
+        if (rc != RT_OK) return rc;
+        if (geo) { rc = rebuild_bvh(ctx); if (rc != RT_OK) return rc; }
+    }
+    return RT_OK;
+}
+
+static SceneView scene_view(const rt_ctx* ctx) {
+    SceneView sc;
+    sc.nodes = ctx->bvh.nodes.p;
+    sc.tris = ctx->bvh.tris.p;
+    sc.objects = ctx->d_objects.p;
+    sc.lights = ctx->d_lights.p;
+    sc.materials = ctx->d_materials.p;
+    sc.vertices = ctx->d_vertices.p;
+    sc.indices = ctx->d_indices.p;
+    sc.n_lights = ctx->n_lights;
+    sc.n_objects = (uint32_t)ctx->objects.size();
+    sc.n_tris = ctx->n_tris;
+    sc.n_nodes = ctx->bvh.n_nodes;
+    return sc;
+}
+
+extern "C" {
+
+int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const rt_object* objects, uint32_t n_objects,
+                   const rt_material* materials, uint32_t n_materials) {
+    CTX_CHECK(ctx);
+    if ((n_meshes && !meshes) || (n_objects && !objects) || (n_materials && !materials)) {
+        set_error("rt_build_scene: null array");
+        return RT_ERR_INVALID_ARGUMENT;
+    }
+    std::vector<HostMesh> hm(n_meshes);
+    size_t nv = 0, ni = 0;
+    for (uint32_t i = 0; i < n_meshes; i++) {
+        const rt_mesh& m = meshes[i];
+        if ((m.n_vertices && !m.vertices) || (m.n_indices && !m.indices) || (m.n_indices % 3u) != 0u) {
+            set_error("rt_build_scene: malformed mesh");
+            return RT_ERR_INVALID_ARGUMENT;
+        }
+        for (uint32_t k = 0; k < m.n_indices; k++)
+            if (m.indices[k] >= m.n_vertices) { set_error("rt_build_scene: vertex index out of range"); return RT_ERR_INDEX_RANGE; }
+        hm[i].v.assign(m.vertices, m.vertices + m.n_vertices);
+        hm[i].idx.assign(m.indices, m.indices + m.n_indices);
+        hm[i].vertex_base = (uint32_t)nv;
+        hm[i].index_base = (uint32_t)ni;
+        nv += m.n_vertices;
+        ni += m.n_indices;
+    }
+    uint64_t total_tris = 0;
+    for (uint32_t i = 0; i < n_objects; i++) {
+        if (objects[i].mesh_index >= n_meshes) { set_error("rt_build_scene: Invalid mesh index"); return RT_ERR_INDEX_RANGE; }
+        if (objects[i].material_index >= n_materials) { set_error("rt_build_scene: Invalid material index"); return RT_ERR_INDEX_RANGE; }
+        total_tris += hm[objects[i].mesh_index].idx.size() / 3;
+    }
+    if (total_tris >= 0x7FFFFFFFull || nv >= 0xFFFFFFFFull || ni >= 0xFFFFFFFFull) {
+        set_error("rt_build_scene: scene too large for 32-bit triangle ids");
+        return RT_ERR_INVALID_ARGUMENT;
+    }
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->meshes.swap(hm);
+    ctx->objects.assign(objects, objects + n_objects);
+    ctx->materials.assign(materials, materials + n_materials);
+    ctx->light_index.assign(n_objects, 0u);
+    RT_CUDA_TRY(ctx->d_vertices.ensure(nv));
+    RT_CUDA_TRY(ctx->d_indices.ensure(ni));
+    for (const HostMesh& m : ctx->meshes) {  // staging copies, like buffer_init_with_staging_buffer (gpu_scene.odin:80-112)
+        if (!m.v.empty())
+            RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_vertices.p + m.vertex_base, m.v.data(), m.v.size() * sizeof(rt_vertex),
+                                        cudaMemcpyHostToDevice, ctx->stream));
+        if (!m.idx.empty())
+            RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_indices.p + m.index_base, m.idx.data(), m.idx.size() * 4, cudaMemcpyHostToDevice,
+                                        ctx->stream));
+    }
+    ctx->has_scene = true;
+    ctx->tables_dirty = true;
+    ctx->geometry_dirty = true;
+    return flush_scene(ctx);
+}
+
+int rt_scene_info_get(rt_ctx* ctx, rt_scene_info* out) {
+    CTX_CHECK(ctx);
+    if (!out) return RT_ERR_INVALID_ARGUMENT;
+    const int rc = flush_scene(ctx);
+    if (rc != RT_OK) return rc;
+    memset(out, 0, sizeof(*out));
+    out->n_triangles = ctx->n_tris;
+    out->n_nodes = ctx->bvh.n_nodes;
+    out->bvh_depth = ctx->bvh.depth;
+    out->n_lights = ctx->n_lights;
+    out->n_objects = (uint32_t)ctx->objects.size();
+    out->n_materials = (uint32_t)ctx->materials.size();
+    out->build_ms = ctx->bvh.build_ms;
+    return RT_OK;
+}
+
+// gpu_scene_update_material (gpu_scene.odin:562-601): overwrite the record, recompile the lights
+int rt_update_material(rt_ctx* ctx, uint32_t material_index, const rt_material* m) {
+    CTX_CHECK(ctx);
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    if (!m || material_index >= ctx->materials.size()) { set_error("rt_update_material: bad index"); return RT_ERR_INDEX_RANGE; }
+    ctx->materials[material_index] = *m;
+    ctx->tables_dirty = true;
+    return RT_OK;
+}
+
+// gpu_scene_update_object_transform (gpu_scene.odin:457-483): instance transform + TLAS update
+int rt_update_object_transform(rt_ctx* ctx, uint32_t object_index, const float model[16]) {
+    CTX_CHECK(ctx);
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    if (!model || object_index >= ctx->objects.size()) { set_error("rt_update_object_transform: bad index"); return RT_ERR_INDEX_RANGE; }
+    memcpy(ctx->objects[object_index].model, model, 64);
+    ctx->tables_dirty = true;
+    ctx->geometry_dirty = true;
+    return RT_OK;
+}
+
+// gpu_scene_update_object with changed_material (gpu_scene.odin:517-560): the one place light_index is set
+int rt_update_object_material(rt_ctx* ctx, uint32_t object_index, uint32_t material_index) {
+    CTX_CHECK(ctx);
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    if (object_index >= ctx->objects.size() || material_index >= ctx->materials.size()) {
+        set_error("rt_update_object_material: bad index");
+        return RT_ERR_INDEX_RANGE;
+    }
+    ctx->objects[object_index].material_index = material_index;
+    uint32_t li = 0, k = 0;
+    for (uint32_t i = 0; i < ctx->objects.size(); i++) {
+        if (ctx->materials[ctx->objects[i].material_index].emission_power > 0.0f) {
+            if (i == object_index) li = k;
+            k++;
+        }
+    }
+    ctx->light_index[object_index] = li;
+    ctx->tables_dirty = true;
+    return RT_OK;
+}
+
+// gpu_scene_update_object_mesh (gpu_scene.odin:485-515)
+int rt_update_object_mesh(rt_ctx* ctx, uint32_t object_index, uint32_t mesh_index) {
+    CTX_CHECK(ctx);
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    if (object_index >= ctx->objects.size() || mesh_index >= ctx->meshes.size()) {
+        set_error("rt_update_object_mesh: bad index");
+        return RT_ERR_INDEX_RANGE;
+    }
+    ctx->objects[object_index].mesh_index = mesh_index;
+    ctx->tables_dirty = true;
+    ctx->geometry_dirty = true;
+    return RT_OK;
+}
+
+}  // extern "C"
+
+// ---- target / frame loop -------------------------------------------------------------------------
+static uint32_t count_local_rows(const rt_config& c, uint32_t height) {
+    uint32_t n = 0;
+    for (uint32_t y = 0; y < height; y++)
+        if ((y / c.strip_rows) % c.strip_count == c.strip_index) n++;
+    return n;
+}
+
+static void fill_frame_params(const rt_ctx* ctx, const float* cam, const float* clear, uint32_t frame, FrameParams* fp) {
+    memcpy(fp->inv_view, cam + 32, 64);  // Camera_UBO: proj, view, inverse_view, inverse_proj (camera.odin:15-20)
+    memcpy(fp->inv_proj, cam + 48, 64);
+    if (clear) memcpy(fp->clear, clear, 12); else fp->clear[0] = fp->clear[1] = fp->clear[2] = 0.0f;
+    fp->frame = frame;
+    fp->width = ctx->width;
+    fp->height = ctx->height;
+    fp->strip_rows = ctx->cfg.strip_rows;
+    fp->strip_index = ctx->cfg.strip_index;
+    fp->strip_count = ctx->cfg.strip_count;
+    fp->local_rows = ctx->local_rows;
+    fp->max_depth = ctx->cfg.max_depth;
+    fp->rr_start = ctx->cfg.rr_start_depth;
+    fp->clamp = ctx->cfg.radiance_clamp;
+    fp->flags = ctx->cfg.flags;
+}
+
+static int require_target(rt_ctx* ctx) {
+    if (ctx->width == 0 || ctx->height == 0) { set_error("no target: call rt_resize first"); return RT_ERR_NO_TARGET; }
+    return RT_OK;
+}
+
+static void begin_timing(rt_ctx* ctx) { cudaEventRecord(ctx->ev0, ctx->stream); }
+static void end_timing(rt_ctx* ctx) {
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    ctx->timing_pending = true;
+}
+
+extern "C" {
+
+// raytracing_renderer_on_resize (raytracing_renderer.odin:108-126): new output image, accumulation restarts
+int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
+    CTX_CHECK(ctx);
+    if (width == 0 || height == 0 || (uint64_t)width * height > 0x7FFFFFFFull) {
+        set_error("rt_resize: bad extent");
+        return RT_ERR_INVALID_ARGUMENT;
+    }
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->width = width;
+    ctx->height = height;
+    ctx->local_rows = count_local_rows(ctx->cfg, height);
+    const size_t n = (size_t)ctx->local_rows * width;
+    RT_CUDA_TRY(ctx->image.alloc(n));
+    RT_CUDA_TRY(cudaMemsetAsync(ctx->image.p, 0, std::max<size_t>(n, 1) * sizeof(float4), ctx->stream));
+    ctx->srgb.release();
+    ctx->has_gbuffer = false;
+    if (ctx->wf) { wavefront_free(ctx->wf); ctx->wf = nullptr; }
+    if (ctx->cfg.pipeline == RT_PIPELINE_WAVEFRONT) {
+        std::string err;
+        const int rc = wavefront_alloc(&ctx->wf, (uint32_t)n, err);
+        if (rc != RT_OK) { set_error(err); return rc; }
+    }
+    return RT_OK;
+}
+
+int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
+                    uint32_t n_frames) {
+    CTX_CHECK(ctx);
+    if (!camera_ubo || !clear_color) { set_error("rt_trace_frame: null argument"); return RT_ERR_INVALID_ARGUMENT; }
+    int rc = flush_scene(ctx);
+    if (rc != RT_OK) return rc;
+    rc = require_target(ctx);
+    if (rc != RT_OK) return rc;
+    const SceneView sc = scene_view(ctx);
+    FrameResources res;
+    res.image = ctx->image.p;
+    res.counters = ctx->counters.p;
+    res.wf = ctx->wf;
+    std::string err;
+    begin_timing(ctx);
+    for (uint32_t f = 0; f < n_frames; f++) {
+        FrameParams fp;
+        fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f, &fp);
+        rc = (ctx->cfg.pipeline == RT_PIPELINE_MEGAKERNEL) ? launch_frame_megakernel(sc, fp, res, ctx->stream, err)
+                                                           : launch_frame_wavefront(sc, fp, res, ctx->stream, err);
+        if (rc != RT_OK) { set_error(err); return rc; }
+    }
+    ctx->frames_traced += n_frames;
+    end_timing(ctx);
+    return RT_OK;
+}
+
+int rt_trace_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t frame_number) {
+    return rt_trace_frames(ctx, camera_ubo, clear_color, frame_number, 1);
+}
+
+int rt_synchronize(rt_ctx* ctx) {
+    CTX_CHECK(ctx);
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+int rt_last_trace_ms(rt_ctx* ctx, float* ms) {
+    CTX_CHECK(ctx);
+    if (!ms) return RT_ERR_INVALID_ARGUMENT;
+    if (ctx->timing_pending) {
+        RT_CUDA_TRY(cudaEventSynchronize(ctx->ev1));
+        RT_CUDA_TRY(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
+        ctx->timing_pending = false;
+    }
+    *ms = ctx->last_ms;
+    return RT_OK;
+}
+
+// copy the compact strip image into the rows this context owns of a full-size host image
+static int scatter_rows_to_host(rt_ctx* ctx, const void* d_src, void* dst, size_t bytes, size_t px_bytes) {
+    const size_t need = (size_t)ctx->width * ctx->height * px_bytes;
+    if (!dst || bytes < need) { set_error("readback: destination too small"); return RT_ERR_INVALID_ARGUMENT; }
+    const size_t row = (size_t)ctx->width * px_bytes;
+    if (ctx->cfg.strip_count == 1) {
+        RT_CUDA_TRY(cudaMemcpyAsync(dst, d_src, need, cudaMemcpyDeviceToHost, ctx->stream));
+    } else {
+        const uint32_t sr = ctx->cfg.strip_rows;
+        for (uint32_t lrow = 0; lrow < ctx->local_rows; lrow += sr) {  // one copy per band
+            const uint32_t rows = std::min(sr, ctx->local_rows - lrow);
+            const uint32_t y = strip_global_row(lrow, sr, ctx->cfg.strip_index, ctx->cfg.strip_count);
+            RT_CUDA_TRY(cudaMemcpyAsync((char*)dst + (size_t)y * row, (const char*)d_src + (size_t)lrow * row, rows * row,
+                                        cudaMemcpyDeviceToHost, ctx->stream));
+        }
+    }
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+int rt_readback(rt_ctx* ctx, float* dst, size_t bytes) {
+    CTX_CHECK(ctx);
+    const int rc = require_target(ctx);
+    if (rc != RT_OK) return rc;
+    return scatter_rows_to_host(ctx, ctx->image.p, dst, bytes, sizeof(float4));
+}
+
+int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst, size_t bytes) {
+    CTX_CHECK(ctx);
+    int rc = require_target(ctx);
+    if (rc != RT_OK) return rc;
+    const size_t n = (size_t)ctx->local_rows * ctx->width;
+    RT_CUDA_TRY(ctx->srgb.ensure(n));
+    std::string err;
+    rc = launch_srgb8(ctx->image.p, ctx->srgb.p, (uint32_t)n, ctx->stream, err);
+    if (rc != RT_OK) { set_error(err); return rc; }
+    return scatter_rows_to_host(ctx, ctx->srgb.p, dst, bytes, sizeof(uchar4));
+}
+
+int rt_device_image(rt_ctx* ctx, void** device_ptr, uint32_t* local_rows) {
+    CTX_CHECK(ctx);
+    const int rc = require_target(ctx);
+    if (rc != RT_OK) return rc;
+    if (device_ptr) *device_ptr = ctx->image.p;
+    if (local_rows) *local_rows = ctx->local_rows;
+    return RT_OK;
+}
+
+int rt_upload_accum(rt_ctx* ctx, const float* src, size_t bytes) {
+    CTX_CHECK(ctx);
+    const int rc = require_target(ctx);
+    if (rc != RT_OK) return rc;
+    const size_t row = (size_t)ctx->width * sizeof(float4);
+    if (!src || bytes < row * ctx->height) { set_error("rt_upload_accum: source too small"); return RT_ERR_INVALID_ARGUMENT; }
+    const uint32_t sr = ctx->cfg.strip_rows;
+    for (uint32_t lrow = 0; lrow < ctx->local_rows; lrow += sr) {
+        const uint32_t rows = std::min(sr, ctx->local_rows - lrow);
+        const uint32_t y = strip_global_row(lrow, sr, ctx->cfg.strip_index, ctx->cfg.strip_count);
+        RT_CUDA_TRY(cudaMemcpyAsync((char*)ctx->image.p + (size_t)lrow * row, (const char*)src + (size_t)y * row, rows * row,
+                                    cudaMemcpyHostToDevice, ctx->stream));
+    }
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+// ---- G-buffer --------------------------------------------------------------------------------------
+int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]) {
+    CTX_CHECK(ctx);
+    if (!camera_ubo) return RT_ERR_INVALID_ARGUMENT;
+    int rc = flush_scene(ctx);
+    if (rc != RT_OK) return rc;
+    rc = require_target(ctx);
+    if (rc != RT_OK) return rc;
+    const size_t n = (size_t)ctx->local_rows * ctx->width;
+    RT_CUDA_TRY(ctx->g_albedo.ensure(n));
+    RT_CUDA_TRY(ctx->g_output.ensure(n));
+    RT_CUDA_TRY(ctx->g_normal.ensure(n));
+    RT_CUDA_TRY(ctx->g_emission.ensure(n));
+    RT_CUDA_TRY(ctx->g_position.ensure(n));
+    FrameParams fp;
+    fill_frame_params(ctx, camera_ubo, nullptr, 0, &fp);
+    GBufferImages g;
+    g.albedo = ctx->g_albedo.p; g.output = ctx->g_output.p; g.normal_rough = ctx->g_normal.p;
+    g.emission = ctx->g_emission.p; g.position_metal = ctx->g_position.p;
+    std::string err;
+    begin_timing(ctx);
+    rc = launch_gbuffer(scene_view(ctx), fp, g, (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->stream, err);
+    end_timing(ctx);
+    if (rc != RT_OK) { set_error(err); return rc; }
+    ctx->has_gbuffer = true;
+    return RT_OK;
+}
+
+int rt_readback_gbuffer(rt_ctx* ctx, uint8_t* albedo, uint16_t* normal_rough, float* position_metal, uint16_t* emission,
+                        uint8_t* output) {
+    CTX_CHECK(ctx);
+    if (!ctx->has_gbuffer) { set_error("rt_readback_gbuffer: no G-buffer traced"); return RT_ERR_NO_TARGET; }
+    const size_t px = (size_t)ctx->width * ctx->height;
+    int rc = RT_OK;
+    if (albedo && rc == RT_OK) rc = scatter_rows_to_host(ctx, ctx->g_albedo.p, albedo, px * 4, 4);
+    if (normal_rough && rc == RT_OK) rc = scatter_rows_to_host(ctx, ctx->g_normal.p, normal_rough, px * 8, 8);
+    if (position_metal && rc == RT_OK) rc = scatter_rows_to_host(ctx, ctx->g_position.p, position_metal, px * 16, 16);
+    if (emission && rc == RT_OK) rc = scatter_rows_to_host(ctx, ctx->g_emission.p, emission, px * 8, 8);
+    if (output && rc == RT_OK) rc = scatter_rows_to_host(ctx, ctx->g_output.p, output, px * 4, 4);
+    return rc;
+}
+
+// ---- instrumentation -------------------------------------------------------------------------------
+int rt_get_counters(rt_ctx* ctx, rt_counters* out) {
+    CTX_CHECK(ctx);
+    if (!out) return RT_ERR_INVALID_ARGUMENT;
+    DevCounters c;
+    RT_CUDA_TRY(cudaMemcpyAsync(&c, ctx->counters.p, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    out->extend_rays = c.extend_rays; out->shadow_rays = c.shadow_rays; out->nodes = c.nodes; out->tris = c.tris;
+    out->hits = c.hits; out->nee = c.nee; out->frames = ctx->frames_traced; out->reserved = 0;
+    return RT_OK;
+}
+
+int rt_reset_counters(rt_ctx* ctx) {
+    CTX_CHECK(ctx);
+    RT_CUDA_TRY(cudaMemsetAsync(ctx->counters.p, 0, sizeof(DevCounters), ctx->stream));
+    ctx->frames_traced = 0;
+    return RT_OK;
+}
+
+// ---- verification hooks ----------------------------------------------------------------------------
+static int trace_rays_common(rt_ctx* ctx, const float* rays, uint32_t n, bool any, const uint32_t* ignore, float* out_tuv,
+                             uint32_t* out_id) {
+    int rc = flush_scene(ctx);
+    if (rc != RT_OK) return rc;
+    if (n == 0) return RT_OK;
+    if (!rays || !out_id || (!any && !out_tuv)) { set_error("rt_trace_rays: null argument"); return RT_ERR_INVALID_ARGUMENT; }
+    DevBuf<float> d_rays, d_tuv;
+    DevBuf<uint32_t> d_id, d_ig;
+    RT_CUDA_TRY(d_rays.alloc((size_t)n * 8));
+    RT_CUDA_TRY(d_id.alloc(n));
+    RT_CUDA_TRY(d_tuv.alloc((size_t)n * 3));
+    RT_CUDA_TRY(cudaMemcpyAsync(d_rays.p, rays, (size_t)n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    if (any && ignore) {
+        RT_CUDA_TRY(d_ig.alloc(n));
+        RT_CUDA_TRY(cudaMemcpyAsync(d_ig.p, ignore, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    std::string err;
+    rc = launch_trace_rays(scene_view(ctx), d_rays.p, n, any, (any && ignore) ? d_ig.p : nullptr, d_tuv.p, d_id.p,
+                           (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->stream, err);
+    if (rc != RT_OK) { set_error(err); return rc; }
+    RT_CUDA_TRY(cudaMemcpyAsync(out_id, d_id.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (!any) RT_CUDA_TRY(cudaMemcpyAsync(out_tuv, d_tuv.p, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+int rt_trace_rays_closest(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id) {
+    CTX_CHECK(ctx);
+    return trace_rays_common(ctx, rays, n, false, nullptr, out_tuv, out_id);
+}
+
+int rt_trace_rays_any(rt_ctx* ctx, const float* rays, uint32_t n, const uint32_t* ignore_inst, uint32_t* out_occluded) {
+    CTX_CHECK(ctx);
+    return trace_rays_common(ctx, rays, n, true, ignore_inst, nullptr, out_occluded);
+}
+
+int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t tris_bytes, uint64_t* morton,
+               uint32_t* sorted_ids) {
+    CTX_CHECK(ctx);
+    const int rc = flush_scene(ctx);
+    if (rc != RT_OK) return rc;
+    const size_t nb = (size_t)ctx->bvh.n_nodes * 80, tb = (size_t)ctx->n_tris * 48;
+    if ((nodes && nodes_bytes < nb) || (tris && tris_bytes < tb)) { set_error("rt_get_bvh: buffer too small"); return RT_ERR_INVALID_ARGUMENT; }
+    if (nodes) RT_CUDA_TRY(cudaMemcpyAsync(nodes, ctx->bvh.nodes.p, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (tris && tb) RT_CUDA_TRY(cudaMemcpyAsync(tris, ctx->bvh.tris.p, tb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (morton && ctx->n_tris) RT_CUDA_TRY(cudaMemcpyAsync(morton, ctx->bvh.morton.p, (size_t)ctx->n_tris * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (sorted_ids && ctx->n_tris) RT_CUDA_TRY(cudaMemcpyAsync(sorted_ids, ctx->bvh.sorted_ids.p, (size_t)ctx->n_tris * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+}  // extern "C"

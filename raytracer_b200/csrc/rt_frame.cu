@@ -1,0 +1,561 @@
+// rt_frame.cu — the frame: CUDA replacement of vkCmdTraceRaysKHR(W, H, 1) as recorded by
+// raytracing_renderer_render_scene (src/raytracer/raytracing_renderer.odin:204-270) and of the
+// shaders it drives (shaders/simple.rgen / simple.rchit / simple.rmiss, inline isVisibleRQ).
+//
+// Two pipelines produce bit-identical images:
+//   wavefront  raygen -> [extend -> shade -> shadow] x max_depth -> accumulate.  Path state lives in
+//              SoA arrays indexed by pixel slot; queues hold slots, filled with warp-aggregated
+//              atomics (ballot compaction); traversal kernels are persistent and fetch work per warp.
+//   megakernel one path per thread, shadow rays inline (kept as the cross-check and for tiny frames).
+#include "rt_internal.h"
+#include "rt_shade.cuh"
+#include "rt_trav.cuh"
+
+namespace rt {
+
+#define FRAME_TRY(expr)                                                              \
+    do {                                                                             \
+        cudaError_t _e = (expr);                                                     \
+        if (_e != cudaSuccess) {                                                     \
+            err = std::string(#expr) + ": " + cudaGetErrorString(_e);                \
+            return (_e == cudaErrorMemoryAllocation) ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA; \
+        }                                                                            \
+    } while (0)
+
+static int g_num_sms = 0;
+static int num_sms() {
+    if (g_num_sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        if (g_num_sms <= 0) g_num_sms = 148;
+    }
+    return g_num_sms;
+}
+
+// ---- counters: one atomic per warp -------------------------------------------------------------
+__device__ __forceinline__ void warp_add(unsigned long long* dst, uint32_t v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    if ((threadIdx.x & 31u) == 0u && v) atomicAdd(dst, (unsigned long long)v);
+}
+
+// warp-aggregated queue append: one atomicAdd per warp, slots keep lane order
+__device__ __forceinline__ uint32_t queue_push(uint32_t* counter, bool pred) {
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, pred);
+    if (ballot == 0u) return 0u;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t leader = __ffs(ballot) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(ballot));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    return base + __popc(ballot & ((1u << lane) - 1u));
+}
+
+// ================================================================================================
+// verification hook: arbitrary rays through the same traversal code (rt_trace_rays_closest / _any)
+// ================================================================================================
+template <bool ANY>
+__global__ void __launch_bounds__(128) trace_rays_kernel(SceneView sc, const float4* rays, uint32_t n,
+                                                         const uint32_t* ignore, float* tuv, uint32_t* ids,
+                                                         DevCounters* counters) {
+    uint32_t nn = 0, nt = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = rays[2 * (size_t)i], b = rays[2 * (size_t)i + 1];
+        const Hit h = traverse<ANY, true>(sc, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), a.w, b.w,
+                                          ANY ? (ignore ? ignore[i] : 0xFFFFFFFFu) : 0xFFFFFFFFu, nn, nt);
+        if (ANY) {
+            ids[i] = (h.id != 0xFFFFFFFFu) ? 1u : 0u;
+        } else {
+            ids[i] = h.id;
+            const bool ok = h.id != 0xFFFFFFFFu;
+            tuv[3 * (size_t)i + 0] = ok ? h.t : 0.0f;
+            tuv[3 * (size_t)i + 1] = ok ? h.u : 0.0f;
+            tuv[3 * (size_t)i + 2] = ok ? h.v : 0.0f;
+        }
+    }
+    if (counters) {
+        atomicAdd(&counters->nodes, (unsigned long long)nn);
+        atomicAdd(&counters->tris, (unsigned long long)nt);
+    }
+}
+
+int launch_trace_rays(const SceneView& sc, const float* d_rays, uint32_t n, bool any, const uint32_t* d_ignore,
+                      float* d_tuv, uint32_t* d_id, DevCounters* counters, cudaStream_t stream, std::string& err) {
+    if (n == 0) return RT_OK;
+    const uint32_t grid = std::min<uint32_t>((n + 127) / 128, (uint32_t)num_sms() * 16);
+    if (any)
+        trace_rays_kernel<true><<<grid, 128, 0, stream>>>(sc, reinterpret_cast<const float4*>(d_rays), n, d_ignore, d_tuv,
+                                                          d_id, counters);
+    else
+        trace_rays_kernel<false><<<grid, 128, 0, stream>>>(sc, reinterpret_cast<const float4*>(d_rays), n, d_ignore, d_tuv,
+                                                           d_id, counters);
+    FRAME_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+// ================================================================================================
+// megakernel: simple.rgen:70-137 as one thread per pixel
+// ================================================================================================
+template <bool COUNT>
+__global__ void __launch_bounds__(128) megakernel_frame(SceneView sc, FrameParams fp, float4* image, DevCounters* counters) {
+    const uint32_t n_slots = fp.local_rows * fp.width;
+    uint32_t c_ext = 0, c_sh = 0, c_nodes = 0, c_tris = 0, c_hits = 0, c_nee = 0;
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
+        const uint32_t lrow = slot / fp.width, x = slot - lrow * fp.width;
+        const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+        PathState ps;
+        vec3 o, d;
+        raygen_init(fp, x, y, ps, &o, &d);
+        const vec3 clearc = mk3(fp.clear[0], fp.clear[1], fp.clear[2]);
+        for (int depth = 0; depth < fp.max_depth; depth++) {
+            if (!russian_roulette(ps, depth, fp.rr_start)) break;
+            c_ext++;
+            const Hit h = traverse<false, COUNT>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, c_nodes, c_tris);
+            bool alive = false;
+            if (h.id != 0xFFFFFFFFu) {
+                c_hits++;
+                ShadowRequest sr;
+                const ShadeResult res = shade_hit(sc, ps, h, d, sr, c_nee);
+                if (sr.pending) {
+                    c_sh++;
+                    const Hit sh = traverse<true, COUNT>(sc, sr.origin, sr.dir, 0.001f, sr.tmax, sr.light_object, c_nodes, c_tris);
+                    if (sh.id == 0xFFFFFFFFu) ps.color = add3(ps.color, sr.contrib);
+                }
+                if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
+                alive = res.alive;
+                o = res.next_origin;
+                d = res.next_dir;
+            }
+            if (!alive) {
+                ps.color = add3(ps.color, mul3(ps.throughput, clearc));
+                break;
+            }
+            if (throughput_dead(ps.throughput)) break;
+        }
+        image[slot] = accumulate_pixel(fp.frame ? image[slot] : make_float4(0.f, 0.f, 0.f, 0.f), ps.color, fp.clamp, fp.frame);
+    }
+    if (COUNT) {
+        warp_add(&counters->extend_rays, c_ext); warp_add(&counters->shadow_rays, c_sh);
+        warp_add(&counters->nodes, c_nodes); warp_add(&counters->tris, c_tris);
+        warp_add(&counters->hits, c_hits); warp_add(&counters->nee, c_nee);
+    }
+}
+
+int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
+                            std::string& err) {
+    const uint32_t n_slots = fp.local_rows * fp.width;
+    if (n_slots == 0) return RT_OK;
+    const uint32_t grid = std::min<uint32_t>((n_slots + 127) / 128, (uint32_t)num_sms() * 64);
+    if (fp.flags & RT_FLAG_COUNTERS)
+        megakernel_frame<true><<<grid, 128, 0, stream>>>(sc, fp, res.image, res.counters);
+    else
+        megakernel_frame<false><<<grid, 128, 0, stream>>>(sc, fp, res.image, res.counters);
+    FRAME_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+// ================================================================================================
+// wavefront pipeline
+// ================================================================================================
+// Path state, SoA over pixel slots.  flag bits in prev.w:
+enum { PF_FIRST = 1u, PF_SPECULAR = 2u, PF_DID_DIRECT = 4u };
+
+struct WavefrontBuffers {
+    uint32_t n_slots = 0;
+    DevBuf<float4> ray_o;   // origin.xyz, -
+    DevBuf<float4> ray_d;   // direction.xyz, -
+    DevBuf<float4> thr;     // throughput.xyz, previousBrdfPdf
+    DevBuf<float4> col;     // color.xyz, p_sample_light
+    DevBuf<float4> prev;    // previousHitPos.xyz, flags
+    DevBuf<uint2> seeds;    // payload.seed, ray-gen seed
+    DevBuf<uint4> hit;      // u bits, v bits, inst (0xFFFFFFFF = miss), prim
+    DevBuf<uint32_t> queue[2];
+    DevBuf<float4> sh_o;    // shadow origin.xyz, tmax
+    DevBuf<float4> sh_d;    // shadow dir.xyz, light object bits
+    DevBuf<float4> sh_c;    // contribution.xyz, slot bits
+    DevBuf<float4> sh_e;    // emissive term.xyz, flags (1 = emissive add, 2 = sky add)
+    DevBuf<uint32_t> ctrl;  // [0..1] queue counts, [2] shadow count, [3..5] work cursors (extend, shade, shadow)
+};
+
+int wavefront_alloc(WavefrontBuffers** out, uint32_t n_slots, std::string& err) {
+    WavefrontBuffers* w = new WavefrontBuffers();
+    w->n_slots = n_slots;
+    cudaError_t e = cudaSuccess;
+    auto A = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    A(w->ray_o.alloc(n_slots)); A(w->ray_d.alloc(n_slots)); A(w->thr.alloc(n_slots)); A(w->col.alloc(n_slots));
+    A(w->prev.alloc(n_slots)); A(w->seeds.alloc(n_slots)); A(w->hit.alloc(n_slots));
+    A(w->queue[0].alloc(n_slots)); A(w->queue[1].alloc(n_slots));
+    A(w->sh_o.alloc(n_slots)); A(w->sh_d.alloc(n_slots)); A(w->sh_c.alloc(n_slots)); A(w->sh_e.alloc(n_slots));
+    A(w->ctrl.alloc(8));
+    if (e != cudaSuccess) {
+        err = std::string("wavefront_alloc: ") + cudaGetErrorString(e);
+        delete w;
+        return e == cudaErrorMemoryAllocation ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA;
+    }
+    *out = w;
+    return RT_OK;
+}
+void wavefront_free(WavefrontBuffers* w) { delete w; }
+
+struct WfView {
+    float4 *ray_o, *ray_d, *thr, *col, *prev;
+    uint2* seeds;
+    uint4* hit;
+    float4 *sh_o, *sh_d, *sh_c, *sh_e;
+    uint32_t* ctrl;
+};
+
+// ctrl layout
+#define CT_Q0 0
+#define CT_Q1 1
+#define CT_SH 2
+#define CT_CUR_EXT 3
+#define CT_CUR_SHD 4
+#define CT_CUR_SHW 5
+
+__global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_count) {
+    // before a bounce: the out queue, the shadow queue and the cursors are empty
+    const uint32_t t = threadIdx.x;
+    if (t == 0) {
+        ctrl[q_in ^ 1u] = 0; ctrl[CT_SH] = 0; ctrl[CT_CUR_EXT] = 0; ctrl[CT_CUR_SHD] = 0; ctrl[CT_CUR_SHW] = 0;
+        if (q_in_count != 0xFFFFFFFFu) ctrl[q_in] = q_in_count;
+    }
+}
+
+// raygen: simple.rgen:70-85.  All slots enter bounce 0 (unless roulette is enabled from depth 0).
+__global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView wf) {
+    const uint32_t n_slots = fp.local_rows * fp.width;
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_slots) return;
+    const uint32_t lrow = slot / fp.width, x = slot - lrow * fp.width;
+    const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+    PathState ps;
+    vec3 o, d;
+    raygen_init(fp, x, y, ps, &o, &d);
+    wf.ray_o[slot] = make_float4(o.x, o.y, o.z, 0.0f);
+    wf.ray_d[slot] = make_float4(d.x, d.y, d.z, 0.0f);
+    wf.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    wf.col[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    wf.prev[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(PF_FIRST));
+    wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
+}
+
+// extend: closest hit for every queued path.  Persistent: each warp claims 32 queue entries at a time.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_extend_kernel(SceneView sc, WfView wf, const uint32_t* queue, uint32_t q_idx,
+                                                        DevCounters* counters) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = wf.ctrl[q_idx];
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&wf.ctrl[CT_CUR_EXT], 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const uint32_t i = base + lane;
+        if (i < n) {
+            const uint32_t slot = queue ? queue[i] : i;
+            const float4 o = wf.ray_o[slot], d = wf.ray_d[slot];
+            const Hit h = traverse<false, COUNT>(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, 10000.0f, 0xFFFFFFFFu,
+                                                 c_nodes, c_tris);
+            wf.hit[slot] = make_uint4(__float_as_uint(h.u), __float_as_uint(h.v), h.id == 0xFFFFFFFFu ? 0xFFFFFFFFu : h.inst,
+                                      h.prim);
+            c_rays++;
+        }
+    }
+    if (COUNT) {
+        warp_add(&counters->extend_rays, c_rays);
+        warp_add(&counters->nodes, c_nodes);
+        warp_add(&counters->tris, c_tris);
+    }
+}
+
+// shade: simple.rmiss / simple.rchit for every queued path + the ray-gen loop tail (simple.rgen:106-118).
+// Colour terms are added in the reference's order: NEE, emissive, sky.  When the NEE term waits for
+// its visibility ray, the later terms travel with the shadow-queue entry and wf_shadow_kernel adds them.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
+                                                       uint32_t q_idx, uint32_t* q_out, int depth, DevCounters* counters) {
+    const uint32_t n = wf.ctrl[q_idx];
+    uint32_t c_hits = 0, c_nee = 0;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n_round = (n + 31u) & ~31u;  // whole warps iterate together (ballots below)
+    const vec3 clearc = mk3(fp.clear[0], fp.clear[1], fp.clear[2]);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        bool push_next = false, push_shadow = false, sky = false;
+        uint32_t slot = 0;
+        ShadowRequest sr;
+        sr.pending = false;
+        ShadeResult res;
+        res.emissive_add = false;
+        res.alive = false;
+        PathState ps;
+        if (i < n) {
+            slot = q_in ? q_in[i] : i;
+            const uint4 hrec = wf.hit[slot];
+            const float4 tv = wf.thr[slot], cv = wf.col[slot];
+            ps.throughput = mk3(tv.x, tv.y, tv.z);
+            ps.prev_brdf_pdf = tv.w;
+            ps.color = mk3(cv.x, cv.y, cv.z);
+            ps.p_sample_light = cv.w;
+            if (hrec.z == 0xFFFFFFFFu) {  // simple.rmiss:26-29 -> simple.rgen:106-109
+                sky = true;
+            } else {
+                const float4 pv = wf.prev[slot], dv = wf.ray_d[slot];
+                const uint2 sd = wf.seeds[slot];
+                const uint32_t fl = __float_as_uint(pv.w);
+                ps.prev_hit_pos = mk3(pv.x, pv.y, pv.z);
+                ps.first_bounce = (fl & PF_FIRST) != 0u;
+                ps.is_specular = (fl & PF_SPECULAR) != 0u;
+                ps.did_direct = (fl & PF_DID_DIRECT) != 0u;
+                ps.seed = sd.x;
+                ps.rr_seed = sd.y;
+                Hit h;
+                h.t = 0.0f; h.u = __uint_as_float(hrec.x); h.v = __uint_as_float(hrec.y); h.id = 0u; h.inst = hrec.z; h.prim = hrec.w;
+                c_hits++;
+                res = shade_hit(sc, ps, h, mk3(dv.x, dv.y, dv.z), sr, c_nee);
+                if (!res.alive) {
+                    sky = true;  // payload.hit = false -> the ray-gen shader adds the sky term
+                } else {
+                    // simple.rgen:111-118, then the head of the next iteration (:87, :55-68)
+                    bool go = !throughput_dead(ps.throughput) && (depth + 1 < fp.max_depth);
+                    if (go) go = russian_roulette(ps, depth + 1, fp.rr_start);
+                    push_next = go;
+                }
+            }
+            push_shadow = sr.pending;
+            if (!push_shadow) {
+                if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
+                if (sky) ps.color = add3(ps.color, mul3(ps.throughput, clearc));
+            }
+            wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, ps.p_sample_light);
+            if (push_next) {
+                wf.ray_o[slot] = make_float4(res.next_origin.x, res.next_origin.y, res.next_origin.z, 0.0f);
+                wf.ray_d[slot] = make_float4(res.next_dir.x, res.next_dir.y, res.next_dir.z, 0.0f);
+                wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_brdf_pdf);
+                const uint32_t fl = (ps.is_specular ? PF_SPECULAR : 0u) | (ps.did_direct ? PF_DID_DIRECT : 0u);
+                wf.prev[slot] = make_float4(ps.prev_hit_pos.x, ps.prev_hit_pos.y, ps.prev_hit_pos.z, __uint_as_float(fl));
+                wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
+            }
+        }
+        const uint32_t qi = queue_push(&wf.ctrl[q_idx ^ 1u], push_next);
+        if (push_next) q_out[qi] = slot;
+        const uint32_t si = queue_push(&wf.ctrl[CT_SH], push_shadow);
+        if (push_shadow) {
+            // a sky term is only pending when the hit shader ended the path, in which case the throughput
+            // in the state array is still the one the term needs
+            wf.sh_o[si] = make_float4(sr.origin.x, sr.origin.y, sr.origin.z, sr.tmax);
+            wf.sh_d[si] = make_float4(sr.dir.x, sr.dir.y, sr.dir.z, __uint_as_float(sr.light_object));
+            wf.sh_c[si] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, __uint_as_float(slot));
+            const uint32_t fl = (res.emissive_add ? 1u : 0u) | (sky ? 2u : 0u);
+            wf.sh_e[si] = make_float4(res.emissive_add ? res.emissive.x : 0.0f, res.emissive_add ? res.emissive.y : 0.0f,
+                                      res.emissive_add ? res.emissive.z : 0.0f, __uint_as_float(fl));
+        }
+    }
+    if (COUNT) {
+        warp_add(&counters->hits, c_hits);
+        warp_add(&counters->nee, c_nee);
+    }
+}
+
+// shadow: isVisibleRQ (simple.rchit:350-385) for every queued NEE sample, then the ordered colour adds
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_shadow_kernel(SceneView sc, FrameParams fp, WfView wf, DevCounters* counters) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = wf.ctrl[CT_SH];
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&wf.ctrl[CT_CUR_SHW], 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const uint32_t i = base + lane;
+        if (i < n) {
+            const float4 o = wf.sh_o[i], d = wf.sh_d[i];
+            const Hit h = traverse<true, COUNT>(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, o.w, __float_as_uint(d.w),
+                                                c_nodes, c_tris);
+            c_rays++;
+            const float4 c = wf.sh_c[i], e = wf.sh_e[i];
+            const uint32_t slot = __float_as_uint(c.w), fl = __float_as_uint(e.w);
+            float4 cv = wf.col[slot];
+            vec3 col = mk3(cv.x, cv.y, cv.z);
+            if (h.id == 0xFFFFFFFFu) col = add3(col, mk3(c.x, c.y, c.z));
+            if (fl & 1u) col = add3(col, mk3(e.x, e.y, e.z));
+            if (fl & 2u) {
+                const float4 tv = wf.thr[slot];
+                col = add3(col, mul3(mk3(tv.x, tv.y, tv.z), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
+            }
+            wf.col[slot] = make_float4(col.x, col.y, col.z, cv.w);
+        }
+    }
+    if (COUNT) {
+        warp_add(&counters->shadow_rays, c_rays);
+        warp_add(&counters->nodes, c_nodes);
+        warp_add(&counters->tris, c_tris);
+    }
+}
+
+// accumulate: simple.rgen:121-136
+__global__ void __launch_bounds__(256) wf_accumulate_kernel(FrameParams fp, WfView wf, float4* image) {
+    const uint32_t n_slots = fp.local_rows * fp.width;
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_slots) return;
+    const float4 c = wf.col[slot];
+    image[slot] = accumulate_pixel(fp.frame ? image[slot] : make_float4(0.f, 0.f, 0.f, 0.f), mk3(c.x, c.y, c.z), fp.clamp, fp.frame);
+}
+
+template <typename K>
+static int persistent_grid(K kernel, int threads) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm <= 0) per_sm = 4;
+    return per_sm * num_sms();
+}
+
+template <bool COUNT>
+static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
+                             std::string& err) {
+    WavefrontBuffers* w = res.wf;
+    const uint32_t n_slots = fp.local_rows * fp.width;
+    if (n_slots == 0) return RT_OK;
+    if (!w || w->n_slots < n_slots) { err = "wavefront buffers not allocated"; return RT_ERR_NO_TARGET; }
+    WfView v;
+    v.ray_o = w->ray_o.p; v.ray_d = w->ray_d.p; v.thr = w->thr.p; v.col = w->col.p; v.prev = w->prev.p;
+    v.seeds = w->seeds.p; v.hit = w->hit.p; v.sh_o = w->sh_o.p; v.sh_d = w->sh_d.p; v.sh_c = w->sh_c.p; v.sh_e = w->sh_e.p;
+    v.ctrl = w->ctrl.p;
+    static int g_ext = 0, g_shw = 0, g_shd = 0;
+    if (!g_ext) {
+        g_ext = persistent_grid(wf_extend_kernel<COUNT>, 128);
+        g_shw = persistent_grid(wf_shadow_kernel<COUNT>, 128);
+        g_shd = persistent_grid(wf_shade_kernel<COUNT>, 128);
+    }
+    const uint32_t gb = (n_slots + 255) / 256;
+    wf_raygen_kernel<<<gb, 256, 0, stream>>>(fp, v);
+    uint32_t q_in = 0;
+    for (int depth = 0; depth < fp.max_depth; depth++) {
+        wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, q_in, depth == 0 ? n_slots : 0xFFFFFFFFu);
+        const uint32_t* qi = depth == 0 ? nullptr : w->queue[q_in].p;
+        // no more blocks than the widest possible queue needs
+        const int need = (int)((n_slots + 127) / 128);
+        wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, res.counters);
+        wf_shade_kernel<COUNT><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
+                                                                          res.counters);
+        wf_shadow_kernel<COUNT><<<std::min(g_shw, need), 128, 0, stream>>>(sc, fp, v, res.counters);
+        q_in ^= 1u;
+    }
+    wf_accumulate_kernel<<<gb, 256, 0, stream>>>(fp, v, res.image);
+    FRAME_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+int launch_frame_wavefront(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
+                           std::string& err) {
+    return (fp.flags & RT_FLAG_COUNTERS) ? frame_wavefront_t<true>(sc, fp, res, stream, err)
+                                         : frame_wavefront_t<false>(sc, fp, res, stream, err);
+}
+
+// ================================================================================================
+// G-buffer pass: shaders/restir.rgen:43-92 + restir.rchit:36-59 + restir.rmiss:18-20
+// ================================================================================================
+__global__ void __launch_bounds__(128) gbuffer_kernel(SceneView sc, FrameParams fp, GBufferImages g, DevCounters* counters) {
+    const uint32_t n_slots = fp.local_rows * fp.width;
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
+        const uint32_t lrow = slot / fp.width, x = slot - lrow * fp.width;
+        const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+        vec3 o, d;
+        camera_ray(fp, (float)x, (float)y, false, &o, &d);  // pixel corner, direction not re-normalised
+        c_rays++;
+        const Hit h = traverse<false, true>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, c_nodes, c_tris);
+        if (h.id != 0xFFFFFFFFu) {
+            const DevObject* obj = sc.objects + h.inst;
+            const Mat mat = load_material(sc.materials + __ldg(&obj->material_index));
+            const uint32_t* ip = sc.indices + __ldg(&obj->index_base) + 3u * h.prim;
+            const rt_vertex* vb = sc.vertices + __ldg(&obj->vertex_base);
+            const rt_vertex *v0 = vb + __ldg(ip), *v1 = vb + __ldg(ip + 1), *v2 = vb + __ldg(ip + 2);
+            const float bx = (1.0f - h.u) - h.v, by = h.u, bz = h.v;
+            float model[12], n9[9];
+#pragma unroll
+            for (int k = 0; k < 12; k++) model[k] = __ldg(&obj->model[k]);
+#pragma unroll
+            for (int k = 0; k < 9; k++) n9[k] = __ldg(&obj->nrm[k]);
+            const vec3 pos = add3(add3(scale3(vertex_pos(v0), bx), scale3(vertex_pos(v1), by)), scale3(vertex_pos(v2), bz));
+            const vec3 wp = xf_point(model, pos);
+            const vec3 nrm = normalize3(add3(add3(scale3(vertex_nrm(v0), bx), scale3(vertex_nrm(v1), by)), scale3(vertex_nrm(v2), bz)));
+            const vec3 N = normalize3(mat3_mul(n9, nrm));
+            const uchar4 alb = make_uchar4(unorm8_rne(mat.albedo.x), unorm8_rne(mat.albedo.y), unorm8_rne(mat.albedo.z), 255);
+            g.albedo[slot] = alb;
+            g.output[slot] = alb;
+            g.normal_rough[slot] = make_ushort4(half_bits_rne(N.x), half_bits_rne(N.y), half_bits_rne(N.z), half_bits_rne(mat.roughness));
+            g.position_metal[slot] = make_float4(wp.x, wp.y, wp.z, mat.metallic);
+            g.emission[slot] = make_ushort4(half_bits_rne(mat.emission_color.x), half_bits_rne(mat.emission_color.y),
+                                            half_bits_rne(mat.emission_color.z), half_bits_rne(mat.emission_power));
+        } else {
+            g.albedo[slot] = make_uchar4(0, 0, 0, 255);
+            g.output[slot] = make_uchar4(0, 0, 0, 255);
+            g.normal_rough[slot] = make_ushort4(0, 0, 0, 0x3C00);
+            g.position_metal[slot] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+            g.emission[slot] = make_ushort4(0, 0, 0, 0x3C00);
+        }
+    }
+    if (counters) {
+        warp_add(&counters->extend_rays, c_rays);
+        warp_add(&counters->nodes, c_nodes);
+        warp_add(&counters->tris, c_tris);
+    }
+}
+
+int launch_gbuffer(const SceneView& sc, const FrameParams& fp, const GBufferImages& g, DevCounters* counters,
+                   cudaStream_t stream, std::string& err) {
+    const uint32_t n_slots = fp.local_rows * fp.width;
+    if (n_slots == 0) return RT_OK;
+    const uint32_t grid = std::min<uint32_t>((n_slots + 127) / 128, (uint32_t)num_sms() * 32);
+    gbuffer_kernel<<<grid, 128, 0, stream>>>(sc, fp, g, counters);
+    FRAME_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+// ================================================================================================
+// what the blit to B8G8R8A8_SRGB shows (raytracing_renderer.odin:299-316): clamp to [0,1], sRGB OETF,
+// 8-bit.  The OETF is evaluated as a count of thresholds (the linear values at which the 8-bit code
+// steps), so the result does not depend on a device powf.
+// ================================================================================================
+__constant__ float c_srgb_thresholds[256];  // [k] = smallest linear value that encodes to >= k (k >= 1)
+
+__device__ __forceinline__ uint8_t srgb8(float v) {
+    if (!(v > 0.0f)) return 0;
+    int lo = 0, hi = 255;  // largest k with thresholds[k] <= v
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (c_srgb_thresholds[mid] <= v) lo = mid; else hi = mid - 1;
+    }
+    return (uint8_t)lo;
+}
+
+__global__ void srgb8_kernel(const float4* image, uchar4* out, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 c = image[i];
+    out[i] = make_uchar4(srgb8(c.x), srgb8(c.y), srgb8(c.z), 255);
+}
+
+int launch_srgb8(const float4* image, uchar4* out, uint32_t n, cudaStream_t stream, std::string& err) {
+    static bool table_ready = false;
+    if (!table_ready) {
+        float t[256];
+        t[0] = 0.0f;
+        for (int k = 1; k < 256; k++) {
+            const double s = ((double)k - 0.5) / 255.0;  // encoded value at the rounding boundary
+            const double lin = (s <= 0.04045) ? s / 12.92 : pow((s + 0.055) / 1.055, 2.4);
+            t[k] = (float)lin;
+        }
+        FRAME_TRY(cudaMemcpyToSymbol(c_srgb_thresholds, t, sizeof(t)));
+        table_ready = true;
+    }
+    if (n == 0) return RT_OK;
+    srgb8_kernel<<<(n + 255) / 256, 256, 0, stream>>>(image, out, n);
+    FRAME_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+}  // namespace rt

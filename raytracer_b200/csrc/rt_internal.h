@@ -1,0 +1,140 @@
+// rt_internal.h — host-side declarations shared by the translation units of librt.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "rt_types.cuh"
+
+namespace rt {
+
+#define RT_CUDA_TRY(expr)                                                                    \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                   \
+            return (_e == cudaErrorMemoryAllocation) ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA;   \
+        }                                                                                    \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        release();
+        if (count == 0) count = 1;
+        cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        if (e == cudaSuccess) n = count; else p = nullptr;
+        return e;
+    }
+    cudaError_t ensure(size_t count) { return (count <= n && p) ? cudaSuccess : alloc(count); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr; n = 0;
+    }
+    ~DevBuf() { release(); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+// ---- BVH build (rt_build.cu) --------------------------------------------------------------
+struct BuildInput {
+    const DevObject* d_objects;  // device
+    const uint32_t* d_tri_offsets;  // device, n_objects + 1 entries (prefix sums of triangle counts)
+    const rt_vertex* d_vertices;
+    const uint32_t* d_indices;
+    uint32_t n_objects;
+    uint32_t n_tris;  // instanced (flat) triangle count
+};
+struct BuildOutput {
+    DevBuf<uint4> nodes;        // Node8 x n_nodes
+    DevBuf<float4> tris;        // BvhTri x n_tris, in leaf order
+    DevBuf<unsigned long long> morton;  // sorted keys
+    DevBuf<uint32_t> sorted_ids;        // flat ids in key order
+    uint32_t n_nodes = 0;
+    uint32_t depth = 0;
+    float build_ms = 0.0f;
+};
+// returns rt_status; err receives a message on failure
+int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std::string& err);
+
+// ---- frame kernels (rt_frame.cu) -----------------------------------------------------------
+struct WavefrontBuffers;  // opaque to the API layer
+struct FrameResources {
+    float4* image = nullptr;      // local_rows x width RGBA32F running mean
+    DevCounters* counters = nullptr;
+    WavefrontBuffers* wf = nullptr;
+};
+int wavefront_alloc(WavefrontBuffers** wf, uint32_t n_pixels, std::string& err);
+void wavefront_free(WavefrontBuffers* wf);
+int launch_frame_wavefront(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
+                           std::string& err);
+int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
+                            std::string& err);
+int launch_trace_rays(const SceneView& sc, const float* d_rays, uint32_t n, bool any, const uint32_t* d_ignore,
+                      float* d_tuv, uint32_t* d_id, DevCounters* counters, cudaStream_t stream, std::string& err);
+struct GBufferImages {
+    uchar4* albedo; ushort4* normal_rough; float4* position_metal; ushort4* emission; uchar4* output;
+};
+int launch_gbuffer(const SceneView& sc, const FrameParams& fp, const GBufferImages& g, DevCounters* counters,
+                   cudaStream_t stream, std::string& err);
+int launch_srgb8(const float4* image, uchar4* out, uint32_t n, cudaStream_t stream, std::string& err);
+
+}  // namespace rt
+
+// ---- the context behind the C ABI (rt_api.cu, rt_restir.cu) --------------------------------------
+struct HostMesh {
+    std::vector<rt_vertex> v;
+    std::vector<uint32_t> idx;
+    uint32_t vertex_base = 0, index_base = 0;
+};
+
+struct rt_ctx {
+    rt_config cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string error;
+
+    // host copies (the reference keeps the Scene on the host too and re-derives tables on edits)
+    std::vector<HostMesh> meshes;
+    std::vector<rt_object> objects;
+    std::vector<rt_material> materials;
+    std::vector<uint32_t> light_index;  // per object, 0 after a bake (gpu_scene.odin:333-336)
+    bool has_scene = false;
+    bool geometry_dirty = false;  // BVH must be rebuilt before the next trace
+    bool tables_dirty = false;    // objects / lights / materials must be re-uploaded
+
+    // device scene
+    rt::DevBuf<rt_vertex> d_vertices;
+    rt::DevBuf<uint32_t> d_indices;
+    rt::DevBuf<rt::DevObject> d_objects;
+    rt::DevBuf<uint32_t> d_tri_offsets;
+    rt::DevBuf<rt::DevLight> d_lights;
+    rt::DevBuf<rt_material> d_materials;
+    rt::BuildOutput bvh;
+    uint32_t n_tris = 0, n_lights = 0;
+
+    // target
+    uint32_t width = 0, height = 0, local_rows = 0;
+    rt::DevBuf<float4> image;
+    rt::DevBuf<uchar4> srgb;
+    rt::DevBuf<rt::DevCounters> counters;
+    rt::WavefrontBuffers* wf = nullptr;
+    // g-buffer images (allocated on first use)
+    rt::DevBuf<uchar4> g_albedo, g_output;
+    rt::DevBuf<ushort4> g_normal, g_emission;
+    rt::DevBuf<float4> g_position;
+    bool has_gbuffer = false;
+
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.0f;
+    uint64_t frames_traced = 0;
+    bool timing_pending = false;
+
+    void set_error(const std::string& s) { error = s; }
+};
+

@@ -1,0 +1,114 @@
+// rt_types.cuh — device-side record layouts of librt.so.
+//
+// Input layouts are the reference's (include/rt_api.h); the derived tables below are what the
+// shading kernels read instead of the Vulkan descriptors of the reference:
+//   ObjectData  (shaders/ray_common.glsl:34-40, gpu_scene.odin:23-29)  -> DevObject
+//   LightData   (shaders/ray_common.glsl:42-46, gpu_scene.odin:31-36)  -> DevLight
+//   TLAS/BLAS   (acceleration_structure.odin:65-199, driver-opaque)    -> Node8 + BvhTri
+#pragma once
+#include <stdint.h>
+
+#include "../../include/rt_api.h"
+#include "rt_math.cuh"
+
+// traversal stack entries per ray; a BVH8 deeper than this is rejected at build time
+#define RT_STACK_SIZE 32
+#define RT_MAX_BVH_DEPTH RT_STACK_SIZE
+
+namespace rt {
+
+// 80-byte compressed 8-wide node: five 16-byte words, fetched with five LDG.128.
+//   word 0: p.x p.y p.z | e.x e.y e.z imask
+//   word 1: child_base tri_base meta[0..3] meta[4..7]
+//   word 2: qlo.x[8] qlo.y[8]      word 3: qlo.z[8] qhi.x[8]      word 4: qhi.y[8] qhi.z[8]
+// Child box on axis a = p[a] + 2^(e[a]-127) * [qlo, qhi].  meta: 0 = empty slot; internal child =
+// 0x20 | (24 + slot) (one bit, position = slot); leaf = unary triangle count << 5 | offset from tri_base.
+struct __align__(16) Node8 {
+    float p[3];
+    uint8_t e[3];
+    uint8_t imask;
+    uint32_t child_base;
+    uint32_t tri_base;
+    uint8_t meta[8];
+    uint8_t qlo[3][8];
+    uint8_t qhi[3][8];
+};
+static_assert(sizeof(Node8) == 80, "Node8 is 80 bytes");
+
+// 48-byte triangle: three float4 (world-space vertices + ids), fetched with three LDG.128.
+struct __align__(16) BvhTri {
+    float p0[3]; uint32_t id;    // flat triangle id = object.tri_offset + primitive
+    float p1[3]; uint32_t inst;  // object index (instanceCustomIndex, gpu_scene.odin:135)
+    float p2[3]; uint32_t prim;  // gl_PrimitiveID
+};
+static_assert(sizeof(BvhTri) == 48, "BvhTri is 48 bytes");
+
+struct __align__(16) DevObject {  // 128 B
+    float model[12];      // columns 0..3 of ObjectToWorld, 3 rows each (model[c*3+r])
+    float nrm[9];         // transpose(inverse(mat3(model))) columns
+    uint32_t material_index;
+    uint32_t light_index; // 0 after a bake (gpu_scene.odin:333-336 writes it into a copy)
+    uint32_t vertex_base; // into the concatenated vertex array
+    uint32_t index_base;  // into the concatenated index array
+    uint32_t tri_offset;  // first flat triangle id
+    uint32_t n_tris;
+    uint32_t mesh_index;
+    uint32_t pad[4];
+};
+static_assert(sizeof(DevObject) == 128, "DevObject is 128 bytes");
+
+struct __align__(16) DevLight {  // 64 B
+    float transform[12];  // as DevObject.model
+    uint32_t object_index;
+    uint32_t num_triangles;
+    uint32_t instance_mask;  // 1 << (object & 7), gpu_scene.odin:129-132 (no ray uses it)
+    float emission_power;    // materials[objects[object_index].material].emission_power
+};
+static_assert(sizeof(DevLight) == 64, "DevLight is 64 bytes");
+
+struct Hit {
+    float t, u, v;
+    uint32_t id;    // flat triangle id, 0xFFFFFFFF = miss
+    uint32_t inst, prim;
+};
+
+struct DevCounters {  // mirrors rt_counters
+    unsigned long long extend_rays, shadow_rays, nodes, tris, hits, nee, frames, reserved;
+};
+
+// Everything a traversal / shading kernel needs, passed by value.
+struct SceneView {
+    const uint4* nodes;        // Node8 as 5 x uint4
+    const float4* tris;        // BvhTri as 3 x float4
+    const DevObject* objects;
+    const DevLight* lights;
+    const rt_material* materials;
+    const rt_vertex* vertices;
+    const uint32_t* indices;
+    uint32_t n_lights;
+    uint32_t n_objects;
+    uint32_t n_tris;
+    uint32_t n_nodes;
+};
+
+struct FrameParams {
+    float inv_view[16];
+    float inv_proj[16];
+    float clear[3];
+    uint32_t frame;
+    uint32_t width, height;
+    uint32_t strip_rows, strip_index, strip_count;  // rows owned: (y / strip_rows) % strip_count == strip_index
+    uint32_t local_rows;                            // rows in this context's compact image
+    int32_t max_depth;
+    int32_t rr_start;
+    float clamp;
+    uint32_t flags;
+};
+
+// local row <-> global row of the strip partition
+RT_HD uint32_t strip_global_row(uint32_t local_row, uint32_t strip_rows, uint32_t strip_index, uint32_t strip_count) {
+    uint32_t band = local_row / strip_rows, r = local_row % strip_rows;
+    return (band * strip_count + strip_index) * strip_rows + r;
+}
+
+}  // namespace rt

@@ -1,0 +1,323 @@
+"""GPU parity tests (-m gpu): every call goes through the C ABI of librt.so and is compared with the
+CPU oracle on the same inputs.  Bar: bit-exact for BVH arrays, hit ids and — because the device code and
+the oracle share one arithmetic contract — also for t/u/v and for whole RGBA32F frames.
+"""
+import numpy as np
+import pytest
+
+import raytracer_b200 as rb
+from conftest import CLEAR, fixture_scene, random_rays, soup_scene
+from oracle.binding import OracleScene
+from raytracer_b200 import librt
+
+pytestmark = pytest.mark.gpu
+
+SCENES = ["cornell_box", "cornell_pbr", "conference", "conference_mirror_chairs", "multi_dispersion",
+          "conference_room_large_pbr", "cornell_box_gltf"]
+
+
+def _camera_for(name, aspect):
+    if name == "cornell_pbr":
+        return rb.Camera(position=(0.0, 1.0, 4.5), aspect=aspect, target=(0.0, 1.0, 0.0))
+    if name.startswith("conference"):
+        return rb.Camera(position=(-3.5, -2.0, 1.6), aspect=aspect, target=(1.0, 0.5, 1.0), up=(0.0, 0.0, 1.0))
+    if name == "multi_dispersion":
+        return rb.Camera(position=(0.0, 2.0, 8.0), aspect=aspect, target=(0.0, 0.5, 0.0))
+    return rb.Camera(aspect=aspect)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = librt.Context(device=0)
+    yield c
+    c.close()
+
+
+def _assert_bvh_equal(ctx, scene):
+    info = ctx.build_scene(scene)
+    orc = OracleScene(scene).build_bvh()
+    nodes, tris, keys, ids = ctx.get_bvh()
+    o_nodes, o_tris, o_keys, o_ids = orc.bvh_arrays()
+    assert info.n_triangles == orc.num_tris
+    assert info.n_lights == orc.num_lights
+    assert np.array_equal(keys, o_keys), "sorted Morton keys differ"
+    assert np.array_equal(ids, o_ids), "sorted triangle ids differ"
+    assert info.n_nodes == len(o_nodes)
+    assert info.bvh_depth == orc.bvh_depth
+    assert np.array_equal(nodes, o_nodes), f"{int((nodes != o_nodes).any(axis=1).sum())} BVH8 nodes differ"
+    assert np.array_equal(tris, o_tris), "BVH triangle order/content differs"
+    return orc, info
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_bvh_bit_exact_fixture(ctx, name):
+    _assert_bvh_equal(ctx, fixture_scene(name))
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 9, 33, 1000, 60000])
+def test_bvh_bit_exact_soup(ctx, n):
+    _assert_bvh_equal(ctx, soup_scene(n, seed=n, n_objects=1 if n < 9 else 3))
+
+
+def test_bvh_duplicate_triangles(ctx):
+    """Identical Morton keys: the radix tree falls back to index splits (Karras, tie-break by index)."""
+    s = rb.Scene()
+    s.add_material(rb.Material("m", albedo=(0.5, 0.5, 0.5), roughness=1.0))
+    one = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    v = np.tile(one, (300, 1))
+    v[300:600] += np.float32(1e-9)
+    mi = s.add_mesh(rb.make_mesh("dup", v, np.tile([[0, 0, 1]], (900, 1)), np.arange(900, dtype=np.uint32)))
+    s.add_object("o", mi, 0)
+    _assert_bvh_equal(ctx, s)
+
+
+def test_empty_scene(ctx):
+    s = rb.Scene()
+    s.add_material(rb.Material("m"))
+    info = ctx.build_scene(s)
+    assert info.n_triangles == 0 and info.n_nodes == 1
+    ctx.resize(16, 8)
+    cam = rb.Camera(aspect=2.0)
+    ctx.trace_frame(cam.ubo(), CLEAR, 0)
+    img = ctx.readback()
+    assert np.array_equal(img[..., :3], np.broadcast_to(np.asarray(CLEAR, np.float32), (8, 16, 3)))
+    assert np.all(img[..., 3] == 1.0)
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "cornell_pbr", "conference_mirror_chairs"])
+def test_closest_and_any_hit_vs_brute_force(ctx, name):
+    scene = fixture_scene(name)
+    orc, _ = _assert_bvh_equal(ctx, scene)
+    rays = random_rays(20000, 7, lo=(-4, -4, -4), hi=(4, 4, 4), target_lo=(-2, -2, -2), target_hi=(2, 2, 2))
+    tuv, ids = ctx.trace_rays_closest(rays)
+    o_tuv, o_ids = orc.trace_rays(rays, mode="brute")
+    assert (ids != 0xFFFFFFFF).sum() > 1000
+    assert np.array_equal(ids, o_ids)
+    assert np.array_equal(tuv.view(np.uint32), o_tuv.view(np.uint32)), "t/u/v not bit-identical"
+    ignore = (np.arange(len(rays)) % max(len(scene.objects), 1)).astype(np.uint32)
+    rays[:, 7] = 3.0
+    occ = ctx.trace_rays_any(rays, ignore)
+    _, o_occ = orc.trace_rays(rays, mode="brute", any_hit=True, ignore_inst=ignore)
+    assert np.array_equal(occ, o_occ)
+    assert 0 < occ.sum() < len(occ)
+
+
+def test_closest_hit_ties_shared_edges(ctx):
+    """Rays through shared edges/vertices of a grid of coplanar triangles: lowest flat id wins."""
+    s = rb.Scene()
+    s.add_material(rb.Material("m", albedo=(0.5, 0.5, 0.5), roughness=1.0))
+    g = 9
+    xs, ys = np.meshgrid(np.arange(g, dtype=np.float32), np.arange(g, dtype=np.float32))
+    pos = np.stack([xs.ravel(), ys.ravel(), np.zeros(g * g, np.float32)], 1)
+    idx = []
+    for j in range(g - 1):
+        for i in range(g - 1):
+            a = j * g + i
+            idx += [a, a + 1, a + g + 1, a, a + g + 1, a + g]
+    mi = s.add_mesh(rb.make_mesh("grid", pos, np.tile([[0, 0, 1]], (g * g, 1)), np.asarray(idx, np.uint32)))
+    s.add_object("a", mi, 0)
+    s.add_object("b", mi, 0)  # an exact duplicate instance: every hit is a tie between two ids
+    orc, _ = _assert_bvh_equal(ctx, s)
+    pts = np.stack(np.meshgrid(np.arange(0, g - 1 + 0.5, 0.5, dtype=np.float32),
+                               np.arange(0, g - 1 + 0.5, 0.5, dtype=np.float32)), -1).reshape(-1, 2)
+    rays = np.zeros((len(pts), 8), np.float32)
+    rays[:, 0:2], rays[:, 2], rays[:, 3] = pts, 5.0, 1e-3
+    rays[:, 6], rays[:, 7] = -1.0, 1e4
+    tuv, ids = ctx.trace_rays_closest(rays)
+    o_tuv, o_ids = orc.trace_rays(rays, mode="brute")
+    assert np.array_equal(ids, o_ids)
+    assert np.array_equal(tuv.view(np.uint32), o_tuv.view(np.uint32))
+    assert (ids != 0xFFFFFFFF).mean() > 0.9 and ids[ids != 0xFFFFFFFF].max() < 2 * (g - 1) ** 2
+
+
+@pytest.mark.parametrize("pipeline", [librt.RT_PIPELINE_WAVEFRONT, librt.RT_PIPELINE_MEGAKERNEL])
+@pytest.mark.parametrize("name", ["cornell_box", "cornell_pbr", "conference", "conference_mirror_chairs",
+                                  "multi_dispersion", "cornell_box_gltf"])
+def test_frames_bit_exact(name, pipeline):
+    """Fixed-seed low-spp frames: RGBA32F output identical to the oracle, counters identical too."""
+    scene = fixture_scene(name)
+    W, H = 160, 96
+    cam = _camera_for(name, W / H)
+    c = librt.Context(device=0, pipeline=pipeline)
+    try:
+        c.build_scene(scene)
+        c.resize(W, H)
+        orc = OracleScene(scene).build_bvh()
+        ref = None
+        cnt = np.zeros(6, np.uint64)
+        for f in range(3):
+            c.trace_frame(cam.ubo(), CLEAR, f)
+            ref = orc.render(cam.ubo(), CLEAR, f, W, H, image=ref, counters=cnt)
+            got = c.readback()
+            bad = (got.view(np.uint32) != ref.view(np.uint32)).any(axis=2)
+            assert not bad.any(), f"frame {f}: {int(bad.sum())} pixels differ, max abs {np.abs(got - ref).max()}"
+        dev = c.counters()
+        assert [dev[k] for k in ("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee")] == [int(x) for x in cnt]
+        assert ref[..., :3].max() > 0.05
+    finally:
+        c.close()
+
+
+def test_golden_frames(ctx):
+    """Committed oracle outputs (tests/golden/oracle_*.npz, tools/make_fixtures.py)."""
+    import os
+
+    from conftest import GOLDEN
+
+    for name in ("cornell_box", "cornell_pbr"):
+        z = np.load(os.path.join(GOLDEN, f"oracle_{name}.npz"))
+        scene = fixture_scene(name)
+        ctx.build_scene(scene)
+        H, W = z["frames"].shape[1:3]
+        ctx.resize(W, H)
+        ctx.reset_counters()
+        for f in range(z["frames"].shape[0]):
+            ctx.trace_frame(z["camera"], CLEAR, f)
+            assert np.array_equal(ctx.readback().view(np.uint32), z["frames"][f].view(np.uint32))
+        dev = ctx.counters()
+        assert [dev[k] for k in ("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee")] == [int(x) for x in z["counters"]]
+
+
+def test_trace_frames_batch_equals_loop(ctx):
+    scene = fixture_scene("cornell_pbr")
+    cam = _camera_for("cornell_pbr", 1.0)
+    ctx.build_scene(scene)
+    ctx.resize(64, 64)
+    for f in range(4):
+        ctx.trace_frame(cam.ubo(), CLEAR, f)
+    a = ctx.readback()
+    ctx.trace_frames(cam.ubo(), CLEAR, 0, 4)
+    assert np.array_equal(a.view(np.uint32), ctx.readback().view(np.uint32))
+
+
+def test_deeper_paths_and_roulette():
+    """max_depth 8 with roulette from depth 3 (north_star's Sponza setting) — still the oracle's numbers."""
+    scene = fixture_scene("cornell_pbr")
+    cam = _camera_for("cornell_pbr", 1.0)
+    W = H = 96
+    for pipeline in (librt.RT_PIPELINE_WAVEFRONT, librt.RT_PIPELINE_MEGAKERNEL):
+        c = librt.Context(device=0, pipeline=pipeline, max_depth=8, rr_start_depth=3)
+        try:
+            c.build_scene(scene)
+            c.resize(W, H)
+            orc = OracleScene(scene).build_bvh()
+            ref = None
+            for f in range(2):
+                c.trace_frame(cam.ubo(), CLEAR, f)
+                ref = orc.render(cam.ubo(), CLEAR, f, W, H, image=ref, max_depth=8)
+            assert np.array_equal(c.readback().view(np.uint32), ref.view(np.uint32))
+        finally:
+            c.close()
+
+
+def test_strips_union_is_bit_identical():
+    """Screen-tile sharding: two strip contexts together reproduce the single-context image."""
+    scene = fixture_scene("cornell_pbr")
+    W, H = 96, 52  # not a multiple of the strip height
+    cam = _camera_for("cornell_pbr", W / H)
+    full = librt.Context(device=0)
+    full.build_scene(scene)
+    full.resize(W, H)
+    full.trace_frames(cam.ubo(), CLEAR, 0, 2)
+    want = full.readback()
+    full.close()
+    got = np.zeros_like(want)
+    rows = 0
+    for rank in range(3):
+        c = librt.Context(device=0, strip_rows=8, strip_index=rank, strip_count=3)
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+        c.readback(got)
+        rows += c.device_image()[1]
+        c.close()
+    assert rows == H
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("name", ["cornell_pbr", "conference", "conference_room_large_pbr"])
+def test_gbuffer_bit_exact(ctx, name):
+    scene = fixture_scene(name)
+    W, H = 128, 72
+    cam = _camera_for(name, W / H)
+    ctx.build_scene(scene)
+    ctx.resize(W, H)
+    ctx.trace_gbuffer(cam.ubo())
+    got = ctx.readback_gbuffer()
+    ref = OracleScene(scene).build_bvh().gbuffer(cam.ubo(), W, H)
+    for k in ("albedo", "output", "emission"):
+        assert np.array_equal(got[k], ref[k]), k
+    # meshes without normals give NaN normals on both sides (normalize(0)); compare bit patterns
+    assert np.array_equal(got["normal_rough"], ref["normal_rough"])
+    assert np.array_equal(got["position_metal"].view(np.uint32), ref["position_metal"].view(np.uint32))
+    assert got["albedo"][..., :3].any()
+
+
+def test_srgb8_readback(ctx):
+    scene = fixture_scene("cornell_pbr")
+    cam = _camera_for("cornell_pbr", 1.0)
+    ctx.build_scene(scene)
+    ctx.resize(64, 64)
+    ctx.trace_frames(cam.ubo(), CLEAR, 0, 2)
+    lin = ctx.readback().astype(np.float64)[..., :3]
+    got = ctx.readback_srgb8()
+    c = np.clip(lin, 0.0, 1.0)
+    enc = np.where(c <= 0.0031308, 12.92 * c, 1.055 * np.power(c, 1 / 2.4) - 0.055)
+    want = np.rint(enc * 255.0).astype(np.int32)
+    assert np.abs(got[..., :3].astype(np.int32) - want).max() <= 1
+    assert (got[..., :3] == want).mean() > 0.999
+    assert np.all(got[..., 3] == 255)
+
+
+def test_incremental_updates_match_rebuild(ctx):
+    """rt_update_* (gpu_scene.odin:430-601) == rebuilding the edited scene from scratch, and the oracle."""
+    scene = fixture_scene("cornell_pbr")
+    cam = _camera_for("cornell_pbr", 1.0)
+    W = H = 64
+    ctx.build_scene(scene)
+    ctx.resize(W, H)
+    # material edit that turns an object into a second light; a transform edit; a material swap
+    m = scene.materials[1]
+    m2 = rb.Material(m.name, m.albedo, (0.2, 0.5, 1.0), 3.0, m.roughness, m.metallic)
+    scene.update_material(1, m2)
+    ctx.update_material(1, m2)
+    mm = np.asarray(scene.objects[3].transform.model_matrix, np.float32).copy()
+    mm[12] += 0.25
+    scene.objects[3].transform.model_matrix = mm
+    ctx.update_object_transform(3, mm)
+    scene.objects[4].material_index = 2
+    ctx.update_object_material(4, 2)
+    ctx.trace_frames(cam.ubo(), CLEAR, 0, 2)
+    got = ctx.readback()
+    orc = OracleScene(scene).build_bvh()
+    lights = scene.lights()
+    if 4 in lights:
+        orc.set_light_index(4, lights.index(4))  # the only place light_index becomes non-zero (gpu_scene.odin:532-536)
+    ref = orc.render(cam.ubo(), CLEAR, 0, W, H)
+    ref = orc.render(cam.ubo(), CLEAR, 1, W, H, image=ref)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+
+
+def test_error_paths(ctx):
+    c = librt.Context(device=0)
+    cam = rb.Camera()
+    with pytest.raises(librt.RtError) as e:
+        c.trace_frame(cam.ubo(), CLEAR, 0)
+    assert e.value.status == -5  # RT_ERR_NO_SCENE
+    scene = fixture_scene("cornell_box_gltf")
+    c.build_scene(scene)
+    with pytest.raises(librt.RtError) as e:
+        c.trace_frame(cam.ubo(), CLEAR, 0)
+    assert e.value.status == -6  # RT_ERR_NO_TARGET
+    bad = fixture_scene("cornell_box_gltf")
+    bad.meshes[0].indices[0] = 10 ** 6
+    with pytest.raises(librt.RtError) as e:
+        c.build_scene(bad)
+    assert e.value.status == -8  # RT_ERR_INDEX_RANGE
+    bad = fixture_scene("cornell_box_gltf")
+    bad.objects[0].material_index = 99
+    with pytest.raises(librt.RtError):
+        c.build_scene(bad)
+    with pytest.raises(librt.RtError):
+        librt.Context(device=0, max_depth=0)
+    c.close()
