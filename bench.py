@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s and ms/frame of the path-tracing hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (config.workload): BASELINE.json configs[2] — Sponza 1920x1080, depth 8 (roulette from depth 3),
+one step = `--spp-per-step` accumulated frames (default 16, so the default 16 steps are the config's
+256 spp).  The Sponza geometry blob is absent from the reference mount, so the scene is the
+deterministic "sponza-proxy" (raytracer_b200/proxy_scenes.py: same object/triangle/material counts).
+N > 1: screen tiles (8-row strips, rank r owns strip s when s % N == r), scene replicated, no
+collective on the data path; the strips are gathered over NCCL only for the end-to-end number.
+
+  value        Mrays/s (extend + visibility rays actually traced, from device counters of an identical untimed
+               pass) over K steps timed with CUDA events on the library's stream, inputs resident in HBM
+  e2e          the same through the C ABI with HOST buffers: camera UBO from host memory each step and the
+               RGBA32F image read back to (pinned) host memory each step
+  roofline     dominant kernel (wf_extend_kernel): algorithmic bytes / its CUDA-event time
+  cpu_baseline the CPU oracle (a port: the reference has no CPU path) on a bounded sample, rank 0, N = 1
+  --impl reference   times that CPU port with all host threads (the reference's Vulkan path cannot run here)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CLEAR = (0.53, 0.81, 0.92)
+METRIC = "Mrays/s @1080p Sponza(proxy), depth 8"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--max-depth", type=int, default=8)
+    ap.add_argument("--scene", default="sponza-proxy", choices=["sponza-proxy", "cornell_pbr", "soup1m"])
+    ap.add_argument("--pipeline", default="wavefront", choices=["wavefront", "megakernel"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-rows", type=int, default=0, help="rows of one frame the CPU sample renders (0 = auto)")
+    return ap.parse_args()
+
+
+def make_scene(name, W, H):
+    import raytracer_b200 as rb
+    from raytracer_b200 import proxy_scenes
+
+    if name == "sponza-proxy":
+        return proxy_scenes.sponza_proxy(), rb.Camera(aspect=W / H, **proxy_scenes.SPONZA_CAMERA)
+    if name == "soup1m":
+        return proxy_scenes.soup(1_000_000), rb.Camera(aspect=W / H, **proxy_scenes.SOUP_CAMERA)
+    from raytracer_b200.scene_io import load_scene_npz
+
+    scene = load_scene_npz(os.path.join(ROOT, "tests", "golden", "scenes", "cornell_pbr.npz"))
+    return scene, rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+
+
+def cpu_sample(scene, cam, W, H, max_depth, rows, frames=(1,)):
+    """The CPU oracle on `rows` image rows (centred band) of the same workload. Returns (Mrays/s, s, rays, threads)."""
+    from oracle.binding import OracleScene, lib
+
+    orc = OracleScene(scene).build_bvh()
+    y0 = max(0, (H - rows) // 2)
+    y1 = min(H, y0 + rows)
+    img = np.zeros((H, W, 4), np.float32)
+    cnt = np.zeros(6, np.uint64)
+    t0 = time.perf_counter()
+    for f in frames:
+        orc.render(cam.ubo(), CLEAR, f, W, H, image=img, y0=y0, y1=y1, max_depth=max_depth, counters=cnt)
+    dt = time.perf_counter() - t0
+    rays = int(cnt[0] + cnt[1])
+    return rays / dt / 1e6, dt, rays, lib().orc_max_threads(), (y0, y1)
+
+
+def run_reference(args):
+    """--impl reference: the reference's Vulkan/GLSL path cannot run on this box (no graphics stack) and the
+    reference has no CPU implementation; what is timed is the CPU port (oracle/), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    W, H = args.width, args.height
+    scene, cam = make_scene(args.scene, W, H)
+    rows = args.cpu_rows or min(H, 216)  # a fifth of the frame per step keeps K=16 steps within minutes
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample(scene, cam, W, H, args.max_depth, min(rows, 32))
+    tot_rays, tot_s = 0, 0.0
+    threads = 1
+    for k in range(args.steps):
+        _, dt, rays, threads, band = cpu_sample(scene, cam, W, H, args.max_depth, rows, frames=(1 + k,))
+        tot_rays += rays
+        tot_s += dt
+    v = tot_rays / tot_s / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.scene} {W}x{H} depth {args.max_depth} rr 3, {args.spp_per_step} spp per step",
+                       "sample": f"rows {band[0]}..{band[1]} of one frame per step"},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
+                             "sample": f"{args.steps} steps x {rows} rows x {W} px, frames 1..{args.steps}"},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference GLSL/Vulkan path unavailable on this box; CPU port of the same shader math (oracle/)"}
+    print(json.dumps(line), flush=True)
+
+
+class _DevArray:
+    """__cuda_array_interface__ view of a device pointer owned by librt (the strip image)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
+def run_ours(args):
+    import torch
+
+    import raytracer_b200 as rb  # noqa: F401
+    from raytracer_b200 import librt
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_scalar(x, op):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
+        return float(t.item())
+
+    W, H, B, K, Wm = args.width, args.height, args.spp_per_step, args.steps, args.warmup
+    scene, cam = make_scene(args.scene, W, H)
+    pipe = librt.RT_PIPELINE_WAVEFRONT if args.pipeline == "wavefront" else librt.RT_PIPELINE_MEGAKERNEL
+    kw = dict(device=local_rank, max_depth=args.max_depth, rr_start_depth=3, pipeline=pipe, strip_rows=8, strip_index=rank,
+              strip_count=world)
+    ctx = librt.Context(counters=False, **kw)
+    info = ctx.build_scene(scene)
+    ctx.resize(W, H)
+    ubo = cam.ubo()
+    f0 = Wm * B
+
+    # ---- ray counts of the timed frames: identical untimed pass on a counting context --------------------
+    cctx = librt.Context(counters=True, **kw)
+    cctx.build_scene(scene)
+    cctx.resize(W, H)
+    cctx.trace_frames(ubo, CLEAR, f0, K * B)
+    cnt = cctx.counters()
+    cctx.close()
+    rays_local = cnt["extend_rays"] + cnt["shadow_rays"]
+    rays_total = reduce_scalar(float(rays_local), "SUM")
+
+    # ---- device-resident throughput ---------------------------------------------------------------------
+    for s in range(Wm):
+        ctx.trace_frames(ubo, CLEAR, s * B, B)
+    ctx.synchronize()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    ctx.reset_counters()
+    ctx.event_record(0)
+    for s in range(K):
+        ctx.trace_frames(ubo, CLEAR, f0 + s * B, B)
+    ctx.event_record(1)
+    ms = ctx.event_elapsed_ms()
+    ctx.synchronize()
+    barrier()
+    sampler.stop_flag = True
+    launches = ctx.counters()["launches"]
+    ms_max = reduce_scalar(ms, "MAX")
+    value = rays_total / (ms_max * 1e-3) / 1e6
+
+    # ---- per-kernel times (CUDA events around every launch, separate pass over the same frames) -----------
+    roof = None
+    kprof = None
+    if pipe == librt.RT_PIPELINE_WAVEFRONT:
+        ctx.set_profiling(True)
+        for s in range(K):
+            ctx.trace_frames(ubo, CLEAR, f0 + s * B, B)
+        kprof = ctx.kernel_profile()
+        ctx.set_profiling(False)
+        ext = kprof["extend"]
+        ext_nodes, ext_tris = cnt["nodes"] - cnt["shadow_nodes"], cnt["tris"] - cnt["shadow_tris"]
+        # algorithmic bytes of the extend kernel: BVH8 nodes 80 B + triangles 48 B fetched, ray in 32 B, hit out 16 B
+        alg_bytes = ext_nodes * 80 + ext_tris * 48 + cnt["extend_rays"] * 48
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = alg_bytes / (ext["ms"] * 1e-3) / 1e9 if ext["ms"] > 0 else 0.0
+        total_k = sum(v["ms"] for v in kprof.values())
+        roof = {"bound": "hbm", "kernel": "wf_extend_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": "measured" if "hbm_gbs" in peaks else "fallback",
+                "launches": ext["launches"], "avg_launch_ms": ext["ms"] / max(ext["launches"], 1),
+                "alg_bytes_per_launch": alg_bytes / max(ext["launches"], 1),
+                "bytes_per_extend_ray": alg_bytes / max(cnt["extend_rays"], 1),
+                "share_of_step": ext["ms"] / total_k if total_k > 0 else None,
+                "kernel_ms": {k: round(v["ms"], 3) for k, v in kprof.items()}}
+
+    # ---- end to end through the C ABI with host buffers ------------------------------------------------
+    host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
+    gather = None
+    if dist is not None:
+        ptr, rows = ctx.device_image()
+        rows_all = [0] * world
+        dist.all_gather_object(rows_all, rows)
+        max_rows = max(rows_all)
+        mine = torch.zeros((max_rows, W, 4), dtype=torch.float32, device="cuda")
+        view = torch.as_tensor(_DevArray(ptr, (rows, W, 4)), device="cuda") if rows else None
+        glist = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
+        stage = torch.empty((world, max_rows, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
+        row_maps = []
+        for r in range(world):
+            ys = [y for y in range(H) if (y // 8) % world == r]
+            row_maps.append(np.asarray(ys, np.int64))
+
+        def gather():
+            ctx.synchronize()
+            if view is not None:
+                mine[:rows].copy_(view)
+            dist.gather(mine, glist, dst=0)
+            if rank == 0:
+                for r in range(world):
+                    stage[r].copy_(glist[r], non_blocking=True)
+                torch.cuda.synchronize()
+                sn = stage.numpy()
+                for r in range(world):
+                    host[row_maps[r]] = sn[r, :len(row_maps[r])]
+
+    def e2e_step(s):
+        ctx.trace_frames(np.array(ubo, copy=True), CLEAR, f0 + s * B, B)  # camera UBO + clear colour from host memory
+        if gather is None:
+            ctx.readback(host)
+        else:
+            gather()
+
+    for s in range(min(Wm, 3)):
+        e2e_step(s)
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(K):
+        e2e_step(s)
+    ctx.synchronize()
+    barrier()
+    e2e_s = reduce_scalar(time.perf_counter() - t0, "MAX")
+    e2e_value = rays_total / e2e_s / 1e6
+    sampler.join(timeout=1.0)
+
+    # ---- CPU baseline (rank 0, N = 1 only) --------------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        _, dt, _, _, _ = cpu_sample(scene, cam, W, H, args.max_depth, 16)
+        rows = args.cpu_rows or int(max(16, min(H, 16 * 12.0 / max(dt, 1e-3))))
+        v, dt, rays, threads, band = cpu_sample(scene, cam, W, H, args.max_depth, rows)
+        cpu = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
+               "sample": f"rows {band[0]}..{band[1]} x {W} px of frame 1, {rays} rays in {dt:.2f} s (oracle/, OpenMP)"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+                "ms_per_step": ms_max / K, "ms_per_frame": ms_max / (K * B), "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"{args.scene} {W}x{H} depth {args.max_depth} rr 3, {B} spp per step",
+                           "scene": {"triangles": info.n_triangles, "objects": info.n_objects, "lights": info.n_lights,
+                                     "bvh8_nodes": info.n_nodes, "bvh_depth": info.bvh_depth, "build_ms": round(info.build_ms, 3)},
+                           "pipeline": args.pipeline, "partition": f"8-row screen strips over {world} GPU(s), scene replicated",
+                           "l2": "per-step working set (path state + queues + image, > 300 MB at 1080p) exceeds the 126 MB L2; "
+                                 "the BVH (< 20 MB) stays L2-resident frame to frame, as in the reference's use",
+                           "rays_per_step": rays_total / K,
+                           "e2e_includes": "camera UBO from host + trace + RGBA32F image to pinned host memory every step "
+                                           "(NCCL gather of strips to rank 0 first when N > 1); scene build is outside, "
+                                           "as gpu_scene_init is in the reference"},
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 64 * 4 + 12,
+                        "d2h_bytes_per_step": W * H * 16, "ms_per_step": 1e3 * e2e_s / K},
+                "gpu_launches": int(launches), "clocks": sampler.summary()}
+        if roof:
+            line["roofline"] = roof
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

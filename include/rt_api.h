@@ -121,7 +121,9 @@ typedef struct rt_counters {
     uint64_t hits;          /* closest-hit shader invocations */
     uint64_t nee;           /* light samples taken */
     uint64_t frames;        /* rt_trace_frame calls since the last reset */
-    uint64_t reserved;
+    uint64_t shadow_nodes;  /* the part of `nodes` fetched by visibility rays */
+    uint64_t shadow_tris;   /* the part of `tris` fetched by visibility rays */
+    uint64_t launches;      /* kernels of this library launched since the last reset */
 } rt_counters;
 
 typedef struct rt_scene_info {
@@ -223,6 +225,19 @@ RT_API int rt_get_counters(rt_ctx* ctx, rt_counters* out);
 RT_API int rt_reset_counters(rt_ctx* ctx);
 /* device time (ms) of the last rt_trace_frame(s)/rt_restir_frame/rt_trace_gbuffer call */
 RT_API int rt_last_trace_ms(rt_ctx* ctx, float* ms);
+/* a user event pair on the context's stream: record which = 0 (start) / 1 (stop); the elapsed call
+ * synchronises on the stop event.  Lets a caller time any sequence of calls on the device. */
+RT_API int rt_event_record(rt_ctx* ctx, int which);
+RT_API int rt_event_elapsed_ms(rt_ctx* ctx, float* ms);
+/* per-kernel device times of the wavefront pipeline: when enabled, every launch is bracketed by CUDA
+ * events on the launching stream; rt_get_kernel_profile sums them since the last enable/reset. */
+enum { RT_K_RAYGEN = 0, RT_K_EXTEND = 1, RT_K_SHADE = 2, RT_K_SHADOW = 3, RT_K_ACCUMULATE = 4, RT_K_COUNT = 5 };
+typedef struct rt_kernel_profile {
+    float ms[RT_K_COUNT];
+    uint32_t launches[RT_K_COUNT];
+} rt_kernel_profile;
+RT_API int rt_set_profiling(rt_ctx* ctx, int enable);
+RT_API int rt_get_kernel_profile(rt_ctx* ctx, rt_kernel_profile* out);
 
 /* ---- verification hooks (used by tests; same kernels as the frame path) --------------------
  * rays: n x 8 floats (ox,oy,oz,tmin, dx,dy,dz,tmax), host memory.

@@ -533,7 +533,8 @@ static inline uint16_t f32_to_f16_rne(float f) {
     uint32_t x = f2u(f);
     uint32_t sign = (x >> 16) & 0x8000u;
     uint32_t ax = x & 0x7FFFFFFFu;
-    if (ax >= 0x7F800000u) return (uint16_t)(sign | 0x7C00u | ((ax > 0x7F800000u) ? 0x200u : 0u));
+    if (ax > 0x7F800000u) return (uint16_t)0x7E00u;  // NaN -> canonical quiet NaN (x86 and GPU disagree on the sign)
+    if (ax == 0x7F800000u) return (uint16_t)(sign | 0x7C00u);
     if (ax >= 0x477FF000u) return (uint16_t)(sign | 0x7C00u);  // rounds to inf (>= 65520)
     if (ax < 0x33000001u) return (uint16_t)sign;                // rounds to zero (<= 2^-25)
     int exp = (int)(ax >> 23) - 127;

@@ -93,6 +93,7 @@ void rt_destroy(rt_ctx* ctx) {
     if (ctx->wf) wavefront_free(ctx->wf);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (int k = 0; k < 2; k++) if (ctx->user_ev[k]) cudaEventDestroy(ctx->user_ev[k]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -424,6 +425,8 @@ int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     res.image = ctx->image.p;
     res.counters = ctx->counters.p;
     res.wf = ctx->wf;
+    res.prof = &ctx->prof;
+    res.launches = &ctx->launches;
     std::string err;
     begin_timing(ctx);
     for (uint32_t f = 0; f < n_frames; f++) {
@@ -575,7 +578,8 @@ int rt_get_counters(rt_ctx* ctx, rt_counters* out) {
     RT_CUDA_TRY(cudaMemcpyAsync(&c, ctx->counters.p, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     out->extend_rays = c.extend_rays; out->shadow_rays = c.shadow_rays; out->nodes = c.nodes; out->tris = c.tris;
-    out->hits = c.hits; out->nee = c.nee; out->frames = ctx->frames_traced; out->reserved = 0;
+    out->hits = c.hits; out->nee = c.nee; out->frames = ctx->frames_traced;
+    out->shadow_nodes = c.shadow_nodes; out->shadow_tris = c.shadow_tris; out->launches = ctx->launches;
     return RT_OK;
 }
 
@@ -583,6 +587,45 @@ int rt_reset_counters(rt_ctx* ctx) {
     CTX_CHECK(ctx);
     RT_CUDA_TRY(cudaMemsetAsync(ctx->counters.p, 0, sizeof(DevCounters), ctx->stream));
     ctx->frames_traced = 0;
+    ctx->launches = 0;
+    return RT_OK;
+}
+
+int rt_event_record(rt_ctx* ctx, int which) {
+    CTX_CHECK(ctx);
+    if (which < 0 || which > 1) return RT_ERR_INVALID_ARGUMENT;
+    if (!ctx->user_ev[which]) RT_CUDA_TRY(cudaEventCreate(&ctx->user_ev[which]));
+    RT_CUDA_TRY(cudaEventRecord(ctx->user_ev[which], ctx->stream));
+    return RT_OK;
+}
+
+int rt_event_elapsed_ms(rt_ctx* ctx, float* ms) {
+    CTX_CHECK(ctx);
+    if (!ms || !ctx->user_ev[0] || !ctx->user_ev[1]) { set_error("rt_event_elapsed_ms: record both events first"); return RT_ERR_INVALID_ARGUMENT; }
+    RT_CUDA_TRY(cudaEventSynchronize(ctx->user_ev[1]));
+    RT_CUDA_TRY(cudaEventElapsedTime(ms, ctx->user_ev[0], ctx->user_ev[1]));
+    return RT_OK;
+}
+
+int rt_set_profiling(rt_ctx* ctx, int enable) {
+    CTX_CHECK(ctx);
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->prof.enabled = enable != 0;
+    ctx->prof.reset();
+    return RT_OK;
+}
+
+int rt_get_kernel_profile(rt_ctx* ctx, rt_kernel_profile* out) {
+    CTX_CHECK(ctx);
+    if (!out) return RT_ERR_INVALID_ARGUMENT;
+    memset(out, 0, sizeof(*out));
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < ctx->prof.used; i++) {
+        float ms = 0.0f;
+        RT_CUDA_TRY(cudaEventElapsedTime(&ms, ctx->prof.spans[i].a, ctx->prof.spans[i].b));
+        out->ms[ctx->prof.spans[i].k] += ms;
+        out->launches[ctx->prof.spans[i].k]++;
+    }
     return RT_OK;
 }
 

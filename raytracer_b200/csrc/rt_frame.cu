@@ -100,7 +100,7 @@ int launch_trace_rays(const SceneView& sc, const float* d_rays, uint32_t n, bool
 template <bool COUNT>
 __global__ void __launch_bounds__(128) megakernel_frame(SceneView sc, FrameParams fp, float4* image, DevCounters* counters) {
     const uint32_t n_slots = fp.local_rows * fp.width;
-    uint32_t c_ext = 0, c_sh = 0, c_nodes = 0, c_tris = 0, c_hits = 0, c_nee = 0;
+    uint32_t c_ext = 0, c_sh = 0, c_nodes = 0, c_tris = 0, c_hits = 0, c_nee = 0, c_snodes = 0, c_stris = 0;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
         const uint32_t lrow = slot / fp.width, x = slot - lrow * fp.width;
         const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(128) megakernel_frame(SceneView sc, FrameParam
                 const ShadeResult res = shade_hit(sc, ps, h, d, sr, c_nee);
                 if (sr.pending) {
                     c_sh++;
-                    const Hit sh = traverse<true, COUNT>(sc, sr.origin, sr.dir, 0.001f, sr.tmax, sr.light_object, c_nodes, c_tris);
+                    const Hit sh = traverse<true, COUNT>(sc, sr.origin, sr.dir, 0.001f, sr.tmax, sr.light_object, c_snodes, c_stris);
                     if (sh.id == 0xFFFFFFFFu) ps.color = add3(ps.color, sr.contrib);
                 }
                 if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
@@ -137,7 +137,8 @@ __global__ void __launch_bounds__(128) megakernel_frame(SceneView sc, FrameParam
     }
     if (COUNT) {
         warp_add(&counters->extend_rays, c_ext); warp_add(&counters->shadow_rays, c_sh);
-        warp_add(&counters->nodes, c_nodes); warp_add(&counters->tris, c_tris);
+        warp_add(&counters->nodes, c_nodes + c_snodes); warp_add(&counters->tris, c_tris + c_stris);
+        warp_add(&counters->shadow_nodes, c_snodes); warp_add(&counters->shadow_tris, c_stris);
         warp_add(&counters->hits, c_hits); warp_add(&counters->nee, c_nee);
     }
 }
@@ -151,6 +152,7 @@ int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameRes
         megakernel_frame<true><<<grid, 128, 0, stream>>>(sc, fp, res.image, res.counters);
     else
         megakernel_frame<false><<<grid, 128, 0, stream>>>(sc, fp, res.image, res.counters);
+    if (res.launches) (*res.launches)++;
     FRAME_TRY(cudaGetLastError());
     return RT_OK;
 }
@@ -393,6 +395,8 @@ __global__ void __launch_bounds__(128) wf_shadow_kernel(SceneView sc, FrameParam
         warp_add(&counters->shadow_rays, c_rays);
         warp_add(&counters->nodes, c_nodes);
         warp_add(&counters->tris, c_tris);
+        warp_add(&counters->shadow_nodes, c_nodes);
+        warp_add(&counters->shadow_tris, c_tris);
     }
 }
 
@@ -430,20 +434,37 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         g_shd = persistent_grid(wf_shade_kernel<COUNT>, 128);
     }
     const uint32_t gb = (n_slots + 255) / 256;
+    KernelProfiler none;
+    KernelProfiler& pf = res.prof ? *res.prof : none;
+    uint64_t n_launch = 0;
+    pf.begin(RT_K_RAYGEN, stream);
     wf_raygen_kernel<<<gb, 256, 0, stream>>>(fp, v);
+    pf.end(stream);
+    n_launch++;
     uint32_t q_in = 0;
+    // no more blocks than the widest possible queue needs
+    const int need = (int)((n_slots + 127) / 128);
     for (int depth = 0; depth < fp.max_depth; depth++) {
         wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, q_in, depth == 0 ? n_slots : 0xFFFFFFFFu);
         const uint32_t* qi = depth == 0 ? nullptr : w->queue[q_in].p;
-        // no more blocks than the widest possible queue needs
-        const int need = (int)((n_slots + 127) / 128);
+        pf.begin(RT_K_EXTEND, stream);
         wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, res.counters);
+        pf.end(stream);
+        pf.begin(RT_K_SHADE, stream);
         wf_shade_kernel<COUNT><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
                                                                           res.counters);
+        pf.end(stream);
+        pf.begin(RT_K_SHADOW, stream);
         wf_shadow_kernel<COUNT><<<std::min(g_shw, need), 128, 0, stream>>>(sc, fp, v, res.counters);
+        pf.end(stream);
+        n_launch += 4;
         q_in ^= 1u;
     }
+    pf.begin(RT_K_ACCUMULATE, stream);
     wf_accumulate_kernel<<<gb, 256, 0, stream>>>(fp, v, res.image);
+    pf.end(stream);
+    n_launch++;
+    if (res.launches) *res.launches += n_launch;
     FRAME_TRY(cudaGetLastError());
     return RT_OK;
 }

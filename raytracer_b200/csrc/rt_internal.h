@@ -64,10 +64,37 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
 
 // ---- frame kernels (rt_frame.cu) -----------------------------------------------------------
 struct WavefrontBuffers;  // opaque to the API layer
+// CUDA-event brackets around every launch of a kernel class (rt_set_profiling)
+struct KernelProfiler {
+    struct Span { cudaEvent_t a, b; int k; };
+    std::vector<Span> spans;
+    size_t used = 0;
+    bool enabled = false;
+    void begin(int k, cudaStream_t s) {
+        if (!enabled) return;
+        if (used == spans.size()) {
+            Span sp; sp.k = k;
+            cudaEventCreate(&sp.a); cudaEventCreate(&sp.b);
+            spans.push_back(sp);
+        }
+        spans[used].k = k;
+        cudaEventRecord(spans[used].a, s);
+    }
+    void end(cudaStream_t s) {
+        if (!enabled) return;
+        cudaEventRecord(spans[used].b, s);
+        used++;
+    }
+    void reset() { used = 0; }
+    ~KernelProfiler() { for (auto& sp : spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); } }
+};
+
 struct FrameResources {
     float4* image = nullptr;      // local_rows x width RGBA32F running mean
     DevCounters* counters = nullptr;
     WavefrontBuffers* wf = nullptr;
+    KernelProfiler* prof = nullptr;
+    uint64_t* launches = nullptr;  // host-side launch counter
 };
 int wavefront_alloc(WavefrontBuffers** wf, uint32_t n_pixels, std::string& err);
 void wavefront_free(WavefrontBuffers* wf);
@@ -131,6 +158,9 @@ struct rt_ctx {
     bool has_gbuffer = false;
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t user_ev[2] = {nullptr, nullptr};
+    rt::KernelProfiler prof;
+    uint64_t launches = 0;
     float last_ms = 0.0f;
     uint64_t frames_traced = 0;
     bool timing_pending = false;

@@ -154,7 +154,8 @@ RT_HD uint16_t half_bits_rne(float f) {
     uint32_t x = float_bits(f);
     uint32_t sgn = (x >> 16) & 0x8000u;
     uint32_t ax = x & 0x7FFFFFFFu;
-    if (ax >= 0x7F800000u) return (uint16_t)(sgn | 0x7C00u | ((ax > 0x7F800000u) ? 0x200u : 0u));
+    if (ax > 0x7F800000u) return (uint16_t)0x7E00u;  // NaN: canonical quiet NaN (sign and payload are not portable)
+    if (ax == 0x7F800000u) return (uint16_t)(sgn | 0x7C00u);
     if (ax >= 0x477FF000u) return (uint16_t)(sgn | 0x7C00u);
     if (ax < 0x33000001u) return (uint16_t)sgn;
     int e = (int)(ax >> 23) - 127;

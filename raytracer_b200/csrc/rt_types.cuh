@@ -73,7 +73,7 @@ struct Hit {
 };
 
 struct DevCounters {  // mirrors rt_counters
-    unsigned long long extend_rays, shadow_rays, nodes, tris, hits, nee, frames, reserved;
+    unsigned long long extend_rays, shadow_rays, nodes, tris, hits, nee, frames, shadow_nodes, shadow_tris, launches;
 };
 
 // Everything a traversal / shading kernel needs, passed by value.

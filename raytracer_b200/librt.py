@@ -31,7 +31,8 @@ EXPORTS = (
     "rt_update_object_mesh", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_synchronize", "rt_readback",
     "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_trace_gbuffer", "rt_readback_gbuffer",
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
-    "rt_last_trace_ms", "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh",
+    "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_set_profiling", "rt_get_kernel_profile",
+    "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh",
 )
 
 
@@ -53,10 +54,17 @@ class RtObject(C.Structure):
 
 class RtCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee", "frames",
-                                           "reserved")]
+                                           "shadow_nodes", "shadow_tris", "launches")]
 
     def as_dict(self):
-        return {n: int(getattr(self, n)) for n, _ in self._fields_ if n != "reserved"}
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+KERNEL_NAMES = ("raygen", "extend", "shade", "shadow", "accumulate")
+
+
+class RtKernelProfile(C.Structure):
+    _fields_ = [("ms", C.c_float * 5), ("launches", C.c_uint32 * 5)]
 
 
 class RtSceneInfo(C.Structure):
@@ -126,6 +134,10 @@ def load() -> C.CDLL:
     L.rt_get_counters.argtypes = [vp, C.POINTER(RtCounters)]
     L.rt_reset_counters.argtypes = [vp]
     L.rt_last_trace_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.rt_event_record.argtypes = [vp, C.c_int]
+    L.rt_event_elapsed_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.rt_set_profiling.argtypes = [vp, C.c_int]
+    L.rt_get_kernel_profile.argtypes = [vp, C.POINTER(RtKernelProfile)]
     L.rt_trace_rays_closest.argtypes = [vp, f32p, u32, vp, vp]
     L.rt_trace_rays_any.argtypes = [vp, f32p, u32, vp, vp]
     L.rt_get_bvh.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t, vp, vp]
@@ -289,6 +301,22 @@ class Context:
         c = RtCounters()
         self._check(self.L.rt_get_counters(self.h, C.byref(c)))
         return c.as_dict()
+
+    def event_record(self, which: int):
+        self._check(self.L.rt_event_record(self.h, which))
+
+    def event_elapsed_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self.L.rt_event_elapsed_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    def set_profiling(self, enable: bool):
+        self._check(self.L.rt_set_profiling(self.h, int(enable)))
+
+    def kernel_profile(self) -> dict:
+        p = RtKernelProfile()
+        self._check(self.L.rt_get_kernel_profile(self.h, C.byref(p)))
+        return {n: {"ms": float(p.ms[i]), "launches": int(p.launches[i])} for i, n in enumerate(KERNEL_NAMES)}
 
     def reset_counters(self):
         self._check(self.L.rt_reset_counters(self.h))

@@ -37,7 +37,37 @@ SCENES = {
 CLEAR = (0.53, 0.81, 0.92)
 
 
+def sponza_layout():
+    """Per-primitive triangle counts, material indices and the materials as the loader reads them, from the
+    glTF JSON (present) of the Sponza model whose geometry blob is missing: raytracer_b200/data/sponza_layout.npz."""
+    import json
+
+    doc = json.load(open(os.path.join(REF, "models/sponza/sponza.gltf")))
+    acc = doc["accessors"]
+    counts, mats = [], []
+    for m in doc["meshes"]:
+        for p in m["primitives"]:
+            counts.append(acc[p["indices"]]["count"] // 3)
+            mats.append(int(p.get("material", 0)))
+    table = []
+    for m in doc["materials"]:  # scene_loader.odin:80-99 with cgltf defaults
+        pbr = m.get("pbrMetallicRoughness")
+        albedo = (pbr.get("baseColorFactor", (1, 1, 1, 1))[:3] if pbr is not None else (0, 0, 0))
+        rough = pbr.get("roughnessFactor", 1.0) if pbr is not None else 0.0
+        metal = pbr.get("metallicFactor", 1.0) if pbr is not None else 0.0
+        emis = m.get("emissiveFactor", (0, 0, 0))
+        ext = m.get("extensions", {})
+        power = ext["KHR_materials_emissive_strength"].get("emissiveStrength", 1.0) if "KHR_materials_emissive_strength" in ext else 0.0
+        table.append(list(albedo) + list(emis) + [power, rough, metal])
+    out = os.path.join(ROOT, "raytracer_b200", "data")
+    os.makedirs(out, exist_ok=True)
+    np.savez_compressed(os.path.join(out, "sponza_layout.npz"), tri_counts=np.asarray(counts, np.int32),
+                        material_index=np.asarray(mats, np.int32), materials=np.asarray(table, np.float32))
+    print(f"sponza layout: {len(counts)} primitives, {sum(counts)} triangles, {len(table)} materials")
+
+
 def main():
+    sponza_layout()
     gold = os.path.join(ROOT, "tests", "golden")
     os.makedirs(os.path.join(gold, "scenes"), exist_ok=True)
     for name, rel in SCENES.items():
