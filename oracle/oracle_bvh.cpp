@@ -78,7 +78,9 @@ static inline RaySetup ray_setup(V3 o, V3 d) {
     r.kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
     r.kx = r.kz + 1; if (r.kx == 3) r.kx = 0;
     r.ky = r.kx + 1; if (r.ky == 3) r.ky = 0;
-    if (comp(d, r.kz) < 0.0f) std::swap(r.kx, r.ky);
+    // Woop et al. swap kx and ky here when d[kz] < 0 to keep the winding for back-face culling.  Nothing is
+    // culled on this path (simple.rgen:92-104 traces with gl_RayFlagsOpaqueEXT only), and the swap merely
+    // negates U, V, W, det and T together, so it is left out (it could only flip the sign of a zero u or v).
     float dz = comp(d, r.kz);
     r.Sx = comp(d, r.kx) / dz;
     r.Sy = comp(d, r.ky) / dz;

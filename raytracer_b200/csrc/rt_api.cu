@@ -36,6 +36,7 @@ void rt_default_config(rt_config* cfg) {
     cfg->strip_rows = 8;
     cfg->strip_index = 0;
     cfg->strip_count = 1;
+    cfg->frames_in_flight = 8;
 }
 
 const char* rt_last_error(const rt_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
@@ -47,6 +48,8 @@ int rt_create(const rt_config* cfg_in, rt_ctx** out) {
     if (cfg_in) cfg = *cfg_in; else rt_default_config(&cfg);
     if (cfg.strip_rows == 0) cfg.strip_rows = 8;
     if (cfg.strip_count == 0) cfg.strip_count = 1;
+    if (cfg.frames_in_flight == 0) cfg.frames_in_flight = 8;
+    if (cfg.frames_in_flight > 64) cfg.frames_in_flight = 64;
     if (cfg.max_depth < 1 || cfg.rr_start_depth < 1 || cfg.strip_index >= cfg.strip_count ||
         cfg.pipeline > RT_PIPELINE_MEGAKERNEL || !(cfg.radiance_clamp == cfg.radiance_clamp)) {
         g_create_error = "rt_create: invalid configuration";
@@ -362,6 +365,7 @@ static void fill_frame_params(const rt_ctx* ctx, const float* cam, const float* 
     memcpy(fp->inv_proj, cam + 48, 64);
     if (clear) memcpy(fp->clear, clear, 12); else fp->clear[0] = fp->clear[1] = fp->clear[2] = 0.0f;
     fp->frame = frame;
+    fp->n_lanes = 1;
     fp->width = ctx->width;
     fp->height = ctx->height;
     fp->strip_rows = ctx->cfg.strip_rows;
@@ -406,7 +410,13 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     if (ctx->wf) { wavefront_free(ctx->wf); ctx->wf = nullptr; }
     if (ctx->cfg.pipeline == RT_PIPELINE_WAVEFRONT) {
         std::string err;
-        const int rc = wavefront_alloc(&ctx->wf, (uint32_t)n, err);
+        // path state is ~200 B per slot; keep all lanes together under 16 GiB and 2^31 slots
+        uint64_t lanes = ctx->cfg.frames_in_flight;
+        const uint64_t per_lane = std::max<uint64_t>(n, 1) * 200ull;
+        lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, (16ull << 30) / per_lane));
+        lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, 0x7FFFFFFFull / std::max<uint64_t>(n, 1)));
+        ctx->lanes = (uint32_t)lanes;
+        const int rc = wavefront_alloc(&ctx->wf, (uint32_t)(n * lanes), err);
         if (rc != RT_OK) { set_error(err); return rc; }
     }
     return RT_OK;
@@ -429,12 +439,14 @@ int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     res.launches = &ctx->launches;
     std::string err;
     begin_timing(ctx);
-    for (uint32_t f = 0; f < n_frames; f++) {
+    const bool mega = ctx->cfg.pipeline == RT_PIPELINE_MEGAKERNEL;
+    for (uint32_t f = 0; f < n_frames;) {
         FrameParams fp;
         fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f, &fp);
-        rc = (ctx->cfg.pipeline == RT_PIPELINE_MEGAKERNEL) ? launch_frame_megakernel(sc, fp, res, ctx->stream, err)
-                                                           : launch_frame_wavefront(sc, fp, res, ctx->stream, err);
+        fp.n_lanes = mega ? 1u : std::min(ctx->lanes, n_frames - f);
+        rc = mega ? launch_frame_megakernel(sc, fp, res, ctx->stream, err) : launch_frame_wavefront(sc, fp, res, ctx->stream, err);
         if (rc != RT_OK) { set_error(err); return rc; }
+        f += fp.n_lanes;
     }
     ctx->frames_traced += n_frames;
     end_timing(ctx);

@@ -226,12 +226,15 @@ __global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_cou
 }
 
 // raygen: simple.rgen:70-85.  All slots enter bounce 0 (unless roulette is enabled from depth 0).
+// A launch covers fp.n_lanes consecutive frames ("lanes"): slot = lane * pixels + pixel, frame = fp.frame + lane.
 __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView wf) {
-    const uint32_t n_slots = fp.local_rows * fp.width;
+    const uint32_t n_px = fp.local_rows * fp.width;
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= n_slots) return;
-    const uint32_t lrow = slot / fp.width, x = slot - lrow * fp.width;
+    if (slot >= n_px * fp.n_lanes) return;
+    const uint32_t lane_f = slot / n_px, px = slot - lane_f * n_px;
+    const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
     const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+    fp.frame += lane_f;
     PathState ps;
     vec3 o, d;
     raygen_init(fp, x, y, ps, &o, &d);
@@ -243,27 +246,79 @@ __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView w
     wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
 }
 
-// extend: closest hit for every queued path.  Persistent: each warp claims 32 queue entries at a time.
+// ---- persistent ray fetch -------------------------------------------------------------------------
+// A warp claims RT_FETCH_CHUNK queue entries at a time (one atomic) and hands them to its lanes as they
+// run dry: a lane whose ray has finished gets the next entry as soon as RT_REFILL_IDLE lanes are idle,
+// instead of waiting for the slowest ray of its batch (Aila & Laine 2009, "dynamic fetch").
+#define RT_FETCH_CHUNK 128u
+#define RT_REFILL_IDLE 8u
+
+struct WarpFetch {
+    uint32_t next, end;  // the warp's private range of queue indices (warp-uniform)
+    bool drained;        // the global cursor has passed the end of the queue
+};
+
+// Gives every lane with want == true a queue index below n, or 0xFFFFFFFF once the queue is exhausted.
+__device__ __forceinline__ uint32_t warp_fetch(WarpFetch& wfetch, uint32_t* cursor, uint32_t n, bool want) {
+    const uint32_t lane = threadIdx.x & 31u;
+    // short queues are spread over all warps, long ones are claimed in larger pieces (fewer atomics)
+    const uint32_t chunk = (n > gridDim.x * blockDim.x * 4u) ? RT_FETCH_CHUNK : 32u;
+    uint32_t need = __ballot_sync(0xFFFFFFFFu, want);
+    uint32_t idx = 0xFFFFFFFFu;
+    while (need) {
+        if (wfetch.next == wfetch.end) {
+            if (wfetch.drained) break;
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(cursor, chunk);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (base >= n) { wfetch.drained = true; break; }
+            wfetch.next = base;
+            wfetch.end = min(base + chunk, n);
+        }
+        const uint32_t avail = wfetch.end - wfetch.next;
+        const uint32_t rank = __popc(need & ((1u << lane) - 1u));
+        const bool mine = ((need >> lane) & 1u) && rank < avail && idx == 0xFFFFFFFFu;
+        if (mine) idx = wfetch.next + rank;
+        const uint32_t served = __ballot_sync(0xFFFFFFFFu, mine);
+        wfetch.next += __popc(served);
+        need &= ~served;
+    }
+    return idx;
+}
+
+// extend: closest hit for every queued path (traceRayEXT of simple.rgen:92-104).
 template <bool COUNT>
 __global__ void __launch_bounds__(128) wf_extend_kernel(SceneView sc, WfView wf, const uint32_t* queue, uint32_t q_idx,
                                                         DevCounters* counters) {
-    const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = wf.ctrl[q_idx];
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    WarpFetch wfetch;
+    wfetch.next = wfetch.end = 0u;
+    wfetch.drained = false;
+    TravState st;
+    TravStack stk;
+    bool has_ray = false;
+    uint32_t slot = 0;
     for (;;) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(&wf.ctrl[CT_CUR_EXT], 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const uint32_t i = base + lane;
-        if (i < n) {
-            const uint32_t slot = queue ? queue[i] : i;
+        const uint32_t i = warp_fetch(wfetch, &wf.ctrl[CT_CUR_EXT], n, !has_ray);
+        if (i != 0xFFFFFFFFu) {
+            slot = queue ? queue[i] : i;
             const float4 o = wf.ray_o[slot], d = wf.ray_d[slot];
-            const Hit h = traverse<false, COUNT>(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, 10000.0f, 0xFFFFFFFFu,
-                                                 c_nodes, c_tris);
-            wf.hit[slot] = make_uint4(__float_as_uint(h.u), __float_as_uint(h.v), h.id == 0xFFFFFFFFu ? 0xFFFFFFFFu : h.inst,
-                                      h.prim);
+            trav_init(st, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, 10000.0f, 0xFFFFFFFFu);
+            has_ray = true;
             c_rays++;
+        }
+        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) break;
+        // while the queue still has entries, return to the fetch once enough lanes are idle
+        const uint32_t min_active = wfetch.drained ? 1u : (32u - RT_REFILL_IDLE + 1u);
+        while (has_ray) {
+            if (trav_step<false, COUNT>(sc, st, stk, c_nodes, c_tris)) {
+                const Hit& h = st.best;
+                wf.hit[slot] = make_uint4(__float_as_uint(h.u), __float_as_uint(h.v), h.id == 0xFFFFFFFFu ? 0xFFFFFFFFu : h.inst,
+                                          h.prim);
+                has_ray = false;
+            }
+            if (__popc(__activemask()) < min_active) break;
         }
     }
     if (COUNT) {
@@ -364,31 +419,42 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(SceneView sc, FrameParams
 // shadow: isVisibleRQ (simple.rchit:350-385) for every queued NEE sample, then the ordered colour adds
 template <bool COUNT>
 __global__ void __launch_bounds__(128) wf_shadow_kernel(SceneView sc, FrameParams fp, WfView wf, DevCounters* counters) {
-    const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = wf.ctrl[CT_SH];
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    WarpFetch wfetch;
+    wfetch.next = wfetch.end = 0u;
+    wfetch.drained = false;
+    TravState st;
+    TravStack stk;
+    bool has_ray = false;
+    uint32_t entry = 0;
     for (;;) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(&wf.ctrl[CT_CUR_SHW], 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const uint32_t i = base + lane;
-        if (i < n) {
+        const uint32_t i = warp_fetch(wfetch, &wf.ctrl[CT_CUR_SHW], n, !has_ray);
+        if (i != 0xFFFFFFFFu) {
+            entry = i;
             const float4 o = wf.sh_o[i], d = wf.sh_d[i];
-            const Hit h = traverse<true, COUNT>(sc, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, o.w, __float_as_uint(d.w),
-                                                c_nodes, c_tris);
+            trav_init(st, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, o.w, __float_as_uint(d.w));
+            has_ray = true;
             c_rays++;
-            const float4 c = wf.sh_c[i], e = wf.sh_e[i];
-            const uint32_t slot = __float_as_uint(c.w), fl = __float_as_uint(e.w);
-            float4 cv = wf.col[slot];
-            vec3 col = mk3(cv.x, cv.y, cv.z);
-            if (h.id == 0xFFFFFFFFu) col = add3(col, mk3(c.x, c.y, c.z));
-            if (fl & 1u) col = add3(col, mk3(e.x, e.y, e.z));
-            if (fl & 2u) {
-                const float4 tv = wf.thr[slot];
-                col = add3(col, mul3(mk3(tv.x, tv.y, tv.z), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
+        }
+        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) break;
+        const uint32_t min_active = wfetch.drained ? 1u : (32u - RT_REFILL_IDLE + 1u);
+        while (has_ray) {
+            if (trav_step<true, COUNT>(sc, st, stk, c_nodes, c_tris)) {
+                const float4 c = wf.sh_c[entry], e = wf.sh_e[entry];
+                const uint32_t slot = __float_as_uint(c.w), fl = __float_as_uint(e.w);
+                float4 cv = wf.col[slot];
+                vec3 col = mk3(cv.x, cv.y, cv.z);
+                if (st.best.id == 0xFFFFFFFFu) col = add3(col, mk3(c.x, c.y, c.z));
+                if (fl & 1u) col = add3(col, mk3(e.x, e.y, e.z));
+                if (fl & 2u) {
+                    const float4 tv = wf.thr[slot];
+                    col = add3(col, mul3(mk3(tv.x, tv.y, tv.z), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
+                }
+                wf.col[slot] = make_float4(col.x, col.y, col.z, cv.w);
+                has_ray = false;
             }
-            wf.col[slot] = make_float4(col.x, col.y, col.z, cv.w);
+            if (__popc(__activemask()) < min_active) break;
         }
     }
     if (COUNT) {
@@ -401,12 +467,18 @@ __global__ void __launch_bounds__(128) wf_shadow_kernel(SceneView sc, FrameParam
 }
 
 // accumulate: simple.rgen:121-136
+// the lanes of a pixel are folded into the running mean in frame order, so the float result is the one of
+// n_lanes successive single-frame dispatches
 __global__ void __launch_bounds__(256) wf_accumulate_kernel(FrameParams fp, WfView wf, float4* image) {
-    const uint32_t n_slots = fp.local_rows * fp.width;
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= n_slots) return;
-    const float4 c = wf.col[slot];
-    image[slot] = accumulate_pixel(fp.frame ? image[slot] : make_float4(0.f, 0.f, 0.f, 0.f), mk3(c.x, c.y, c.z), fp.clamp, fp.frame);
+    const uint32_t n_px = fp.local_rows * fp.width;
+    const uint32_t px = blockIdx.x * blockDim.x + threadIdx.x;
+    if (px >= n_px) return;
+    float4 acc = fp.frame ? image[px] : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (uint32_t l = 0; l < fp.n_lanes; l++) {
+        const float4 c = wf.col[(size_t)l * n_px + px];
+        acc = accumulate_pixel(acc, mk3(c.x, c.y, c.z), fp.clamp, fp.frame + l);
+    }
+    image[px] = acc;
 }
 
 template <typename K>
@@ -420,7 +492,8 @@ template <bool COUNT>
 static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
                              std::string& err) {
     WavefrontBuffers* w = res.wf;
-    const uint32_t n_slots = fp.local_rows * fp.width;
+    const uint32_t n_px = fp.local_rows * fp.width;
+    const uint32_t n_slots = n_px * fp.n_lanes;
     if (n_slots == 0) return RT_OK;
     if (!w || w->n_slots < n_slots) { err = "wavefront buffers not allocated"; return RT_ERR_NO_TARGET; }
     WfView v;
@@ -434,6 +507,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         g_shd = persistent_grid(wf_shade_kernel<COUNT>, 128);
     }
     const uint32_t gb = (n_slots + 255) / 256;
+    const uint32_t gb_px = (n_px + 255) / 256;
     KernelProfiler none;
     KernelProfiler& pf = res.prof ? *res.prof : none;
     uint64_t n_launch = 0;
@@ -461,7 +535,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         q_in ^= 1u;
     }
     pf.begin(RT_K_ACCUMULATE, stream);
-    wf_accumulate_kernel<<<gb, 256, 0, stream>>>(fp, v, res.image);
+    wf_accumulate_kernel<<<gb_px, 256, 0, stream>>>(fp, v, res.image);
     pf.end(stream);
     n_launch++;
     if (res.launches) *res.launches += n_launch;

@@ -147,6 +147,7 @@ struct rt_ctx {
 
     // target
     uint32_t width = 0, height = 0, local_rows = 0;
+    uint32_t lanes = 1;  // frames traced together by the wavefront pipeline (<= cfg.frames_in_flight)
     rt::DevBuf<float4> image;
     rt::DevBuf<uchar4> srgb;
     rt::DevBuf<rt::DevCounters> counters;

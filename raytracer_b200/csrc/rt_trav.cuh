@@ -14,24 +14,31 @@ struct TravRay {
     float ox, oy, oz;
     float idx, idy, idz;   // 1/d (clamped for |d| < 1e-20)
     float Sx, Sy, Sz;      // watertight shear
-    uint32_t kx, ky, kz;   // watertight axis permutation
+    uint32_t mz0, mz1;     // all-ones when the dominant axis kz is 0 / 1: drives the branch-free axis rotation
     uint32_t rbits;        // sign bits of d: traversal octant
 };
 
-__device__ __forceinline__ float comp3(float x, float y, float z, uint32_t k) { return k == 0 ? x : (k == 1 ? y : z); }
+// bitwise select: m is all-ones or zero (one LOP3; the compiler cannot turn it into a branch)
+__device__ __forceinline__ float bsel(uint32_t m, float a, float b) {
+    return __uint_as_float((__float_as_uint(a) & m) | (__float_as_uint(b) & ~m));
+}
 
+// Woop et al. permute the axes so that kz is the dominant direction and kx, ky follow cyclically, and swap
+// kx, ky when d[kz] < 0 to keep the winding for back-face culling.  Nothing is culled on this path and the
+// swap only negates U, V, W, det and T together, so it is left out here and in the oracle.
 __device__ __forceinline__ TravRay trav_setup(vec3 o, vec3 d) {
     TravRay r;
     r.ox = o.x; r.oy = o.y; r.oz = o.z;
     float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
     uint32_t kz = (ax > ay) ? ((ax > az) ? 0u : 2u) : ((ay > az) ? 1u : 2u);
-    uint32_t kx = (kz == 2u) ? 0u : kz + 1u;
-    uint32_t ky = (kx == 2u) ? 0u : kx + 1u;
-    float dz = comp3(d.x, d.y, d.z, kz);
-    if (dz < 0.0f) { uint32_t t = kx; kx = ky; ky = t; }
-    r.kx = kx; r.ky = ky; r.kz = kz;
-    r.Sx = comp3(d.x, d.y, d.z, kx) / dz;
-    r.Sy = comp3(d.x, d.y, d.z, ky) / dz;
+    r.mz0 = (kz == 0u) ? 0xFFFFFFFFu : 0u;
+    r.mz1 = (kz == 1u) ? 0xFFFFFFFFu : 0u;
+    // rotate (x, y, z) -> (kx, ky, kz) components
+    const float dkx = bsel(r.mz0, d.y, bsel(r.mz1, d.z, d.x));
+    const float dky = bsel(r.mz0, d.z, bsel(r.mz1, d.x, d.y));
+    const float dz = bsel(r.mz0, d.x, bsel(r.mz1, d.y, d.z));
+    r.Sx = dkx / dz;
+    r.Sy = dky / dz;
     r.Sz = 1.0f / dz;
     r.idx = (fabsf(d.x) >= 1e-20f) ? 1.0f / d.x : copysignf(1e20f, d.x);
     r.idy = (fabsf(d.y) >= 1e-20f) ? 1.0f / d.y : copysignf(1e20f, d.y);
@@ -46,10 +53,13 @@ __device__ __forceinline__ bool tri_isect(const TravRay& r, float4 q0, float4 q1
     float ax = q0.x - r.ox, ay = q0.y - r.oy, az = q0.z - r.oz;
     float bx = q1.x - r.ox, by = q1.y - r.oy, bz = q1.z - r.oz;
     float cx = q2.x - r.ox, cy = q2.y - r.oy, cz = q2.z - r.oz;
-    float Akz = comp3(ax, ay, az, r.kz), Bkz = comp3(bx, by, bz, r.kz), Ckz = comp3(cx, cy, cz, r.kz);
-    float Ax = fmaf(-r.Sx, Akz, comp3(ax, ay, az, r.kx)), Ay = fmaf(-r.Sy, Akz, comp3(ax, ay, az, r.ky));
-    float Bx = fmaf(-r.Sx, Bkz, comp3(bx, by, bz, r.kx)), By = fmaf(-r.Sy, Bkz, comp3(bx, by, bz, r.ky));
-    float Cx = fmaf(-r.Sx, Ckz, comp3(cx, cy, cz, r.kx)), Cy = fmaf(-r.Sy, Ckz, comp3(cx, cy, cz, r.ky));
+    const uint32_t m0 = r.mz0, m1 = r.mz1;
+    float Akz = bsel(m0, ax, bsel(m1, ay, az)), Bkz = bsel(m0, bx, bsel(m1, by, bz)), Ckz = bsel(m0, cx, bsel(m1, cy, cz));
+    float Akx = bsel(m0, ay, bsel(m1, az, ax)), Bkx = bsel(m0, by, bsel(m1, bz, bx)), Ckx = bsel(m0, cy, bsel(m1, cz, cx));
+    float Aky = bsel(m0, az, bsel(m1, ax, ay)), Bky = bsel(m0, bz, bsel(m1, bx, by)), Cky = bsel(m0, cz, bsel(m1, cx, cy));
+    float Ax = fmaf(-r.Sx, Akz, Akx), Ay = fmaf(-r.Sy, Akz, Aky);
+    float Bx = fmaf(-r.Sx, Bkz, Bkx), By = fmaf(-r.Sy, Bkz, Bky);
+    float Cx = fmaf(-r.Sx, Ckz, Ckx), Cy = fmaf(-r.Sy, Ckz, Cky);
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -90,94 +100,120 @@ __device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, co
     const uint32_t nX0 = nx ? w3.z : w2.x, nX1 = nx ? w3.w : w2.y, fX0 = nx ? w2.x : w3.z, fX1 = nx ? w2.y : w3.w;
     const uint32_t nY0 = ny ? w4.x : w2.z, nY1 = ny ? w4.y : w2.w, fY0 = ny ? w2.z : w4.x, fY1 = ny ? w2.w : w4.y;
     const uint32_t nZ0 = nz ? w4.z : w3.x, nZ1 = nz ? w4.w : w3.y, fZ0 = nz ? w3.x : w4.z, fZ1 = nz ? w3.y : w4.w;
+    const float2 scx2 = make_float2(scx, scx), scy2 = make_float2(scy, scy), scz2 = make_float2(scz, scz);
+    const float2 orx2 = make_float2(orx, orx), ory2 = make_float2(ory, ory), orz2 = make_float2(orz, orz);
+    // meta bytes, four children at a time: internal children (24..31 in the low five bits) get their slot
+    // XORed with the ray octant; empty children (meta 0) carry no bits and drop out without a test
+    const uint32_t oct4 = r.rbits * 0x01010101u;
     uint32_t mask = 0;
 #pragma unroll
     for (int half = 0; half < 2; half++) {
-        const uint32_t metaw = half ? w1.w : w1.z;
+        const uint32_t meta4 = half ? w1.w : w1.z;
+        const uint32_t inner4 = ((meta4 & (meta4 << 1)) & 0x10101010u) >> 4;
+        const uint32_t idx4 = (meta4 ^ (oct4 & (inner4 * 0xFFu))) & 0x1F1F1F1Fu;
+        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
         const uint32_t nX = half ? nX1 : nX0, fX = half ? fX1 : fX0;
         const uint32_t nY = half ? nY1 : nY0, fY = half ? fY1 : fY0;
         const uint32_t nZ = half ? nZ1 : nZ0, fZ = half ? fZ1 : fZ0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const uint32_t meta = (metaw >> (8 * k)) & 0xFFu;
-            const float tnx = fmaf(byte_f(nX, k), scx, orx), tfx = fmaf(byte_f(fX, k), scx, orx);
-            const float tny = fmaf(byte_f(nY, k), scy, ory), tfy = fmaf(byte_f(fY, k), scy, ory);
-            const float tnz = fmaf(byte_f(nZ, k), scz, orz), tfz = fmaf(byte_f(fZ, k), scz, orz);
-            const float tnear = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-            const float tfar = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-            if (meta != 0u && tnear <= tfar) {
-                const uint32_t sl = (uint32_t)(half * 4 + k);
-                const uint32_t bits = meta >> 5;
-                const uint32_t idx = ((imask >> sl) & 1u) ? (24u + (sl ^ r.rbits)) : (meta & 31u);
-                mask |= bits << idx;
-            }
+            // near and far plane of an axis share scale and offset: one packed FFMA2 (sm_100 f32x2) per axis,
+            // each half rounded exactly like fmaf
+            const float2 tx = __ffma2_rn(make_float2(byte_f(nX, k), byte_f(fX, k)), scx2, orx2);
+            const float2 ty = __ffma2_rn(make_float2(byte_f(nY, k), byte_f(fY, k)), scy2, ory2);
+            const float2 tz = __ffma2_rn(make_float2(byte_f(nZ, k), byte_f(fZ, k)), scz2, orz2);
+            const float tnear = fmaxf(fmaxf(tx.x, ty.x), fmaxf(tz.x, tmin));
+            const float tfar = fminf(fminf(tx.y, ty.y), fminf(tz.y, tmax));
+            const uint32_t hit = ((bits4 >> (8 * k)) & 0xFFu) << ((idx4 >> (8 * k)) & 0xFFu);
+            mask |= (tnear <= tfar) ? hit : 0u;
         }
     }
     return mask;
 }
 
-// One ray per lane, while-while with a (base, mask) group stack.  ANY: stop at the first accepted hit
-// whose instance differs from ignore_inst.  n_nodes / n_tris are incremented when COUNT.
+// One ray per lane with a (base, mask) group stack.  The traversal is a resumable state machine so that the
+// persistent kernels can swap a finished ray for a new one without waiting for the rest of the warp; one
+// step = one node (its eight child boxes), all triangles that node references directly, and a stack pop.
+// The visiting order of a ray depends on the ray alone, so node/triangle counters are reproducible.
+// ANY: stop at the first accepted hit whose instance differs from ignore_inst.
+struct TravState {
+    TravRay r;
+    Hit best;
+    uint2 ng;       // current node group: child_base, hit bits [31:24] | imask [7:0]
+    float tmin;
+    uint32_t ignore_inst;
+    int sp;
+};
+// the group stack lives beside the state (a dynamically indexed member would drag the whole struct into local memory)
+struct TravStack { uint2 e[RT_STACK_SIZE]; };
+
+__device__ __forceinline__ void trav_init(TravState& st, vec3 o, vec3 d, float tmin, float tmax, uint32_t ignore_inst) {
+    st.r = trav_setup(o, d);
+    st.best.t = tmax; st.best.u = 0.0f; st.best.v = 0.0f; st.best.id = 0xFFFFFFFFu; st.best.inst = 0u; st.best.prim = 0u;
+    st.ng = make_uint2(0u, 0x80000000u);  // root group: bit 31, relative index 0
+    st.tmin = tmin;
+    st.ignore_inst = ignore_inst;
+    st.sp = 0;
+}
+
+// returns true when the traversal is complete (st.best holds the answer)
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, TravStack& stk, uint32_t& n_nodes,
+                                          uint32_t& n_tris) {
+    const TravRay& r = st.r;
+    uint2 ng = st.ng;
+    const int bit = 31 - __clz(ng.y);
+    ng.y &= ~(1u << bit);
+    const uint32_t slot = ((uint32_t)bit - 24u) ^ r.rbits;
+    const uint32_t rel = __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
+    const uint32_t node = ng.x + rel;
+    if (ng.y & 0xFF000000u) stk.e[st.sp++] = ng;
+    const uint4* np = sc.nodes + (size_t)node * 5u;
+    const uint4 w0 = __ldg(np), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
+    if (COUNT) n_nodes++;
+    const uint32_t hm = node_hits(w0, w1, w2, w3, w4, r, st.tmin, st.best.t);
+    ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
+    uint32_t tmask = hm & 0x00FFFFFFu;
+    while (tmask) {
+        const int tb = __ffs(tmask) - 1;
+        tmask &= tmask - 1u;
+        const float4* tp = sc.tris + (size_t)(w1.y + (uint32_t)tb) * 3u;
+        const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+        if (COUNT) n_tris++;
+        const uint32_t inst = __float_as_uint(q1.w);
+        if (ANY && inst == st.ignore_inst) continue;
+        float tt, uu, vv;
+        if (!tri_isect(r, q0, q1, q2, &tt, &uu, &vv)) continue;
+        if (!(tt > st.tmin)) continue;
+        const uint32_t id = __float_as_uint(q0.w);
+        if (ANY) {
+            if (tt < st.best.t) {  // best.t stays tmax until the first accepted hit
+                st.best.t = tt; st.best.u = uu; st.best.v = vv; st.best.id = id; st.best.inst = inst; st.best.prim = __float_as_uint(q2.w);
+                return true;
+            }
+        } else {
+            const bool take = (st.best.id == 0xFFFFFFFFu) ? (tt < st.best.t) : ((tt < st.best.t) || (tt == st.best.t && id < st.best.id));
+            if (take) {
+                st.best.t = tt; st.best.u = uu; st.best.v = vv; st.best.id = id; st.best.inst = inst; st.best.prim = __float_as_uint(q2.w);
+            }
+        }
+    }
+    if (!(ng.y & 0xFF000000u)) {
+        if (st.sp == 0) return true;
+        ng = stk.e[--st.sp];
+    }
+    st.ng = ng;
+    return false;
+}
+
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ Hit traverse(const SceneView& sc, vec3 o, vec3 d, float tmin, float tmax,
                                         uint32_t ignore_inst, uint32_t& n_nodes, uint32_t& n_tris) {
-    const TravRay r = trav_setup(o, d);
-    Hit best;
-    best.t = tmax; best.u = 0.0f; best.v = 0.0f; best.id = 0xFFFFFFFFu; best.inst = 0u; best.prim = 0u;
-    uint2 stack[RT_STACK_SIZE];
-    int sp = 0;
-    uint2 ng = make_uint2(0u, 0x80000000u);  // root group: bit 31, relative index 0
-    uint2 tg = make_uint2(0u, 0u);
-    for (;;) {
-        if (ng.y & 0xFF000000u) {
-            const int bit = 31 - __clz(ng.y);
-            ng.y &= ~(1u << bit);
-            const uint32_t slot = ((uint32_t)bit - 24u) ^ r.rbits;
-            const uint32_t rel = __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
-            const uint32_t node = ng.x + rel;
-            if (ng.y & 0xFF000000u) {
-                stack[sp++] = ng;
-            }
-            const uint4* np = sc.nodes + (size_t)node * 5u;
-            const uint4 w0 = __ldg(np), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
-            if (COUNT) n_nodes++;
-            const uint32_t hm = node_hits(w0, w1, w2, w3, w4, r, tmin, best.t);
-            ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
-            tg = make_uint2(w1.y, hm & 0x00FFFFFFu);
-        } else {
-            tg = make_uint2(0u, 0u);
-            ng = make_uint2(0u, 0u);
-        }
-        while (tg.y) {
-            const int bit = __ffs(tg.y) - 1;
-            tg.y &= tg.y - 1u;
-            const float4* tp = sc.tris + (size_t)(tg.x + (uint32_t)bit) * 3u;
-            const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
-            if (COUNT) n_tris++;
-            const uint32_t inst = __float_as_uint(q1.w);
-            if (ANY && inst == ignore_inst) continue;
-            float tt, uu, vv;
-            if (!tri_isect(r, q0, q1, q2, &tt, &uu, &vv)) continue;
-            if (!(tt > tmin)) continue;
-            const uint32_t id = __float_as_uint(q0.w);
-            if (ANY) {
-                if (tt < tmax) {
-                    best.t = tt; best.u = uu; best.v = vv; best.id = id; best.inst = inst; best.prim = __float_as_uint(q2.w);
-                    return best;
-                }
-            } else {
-                const bool take = (best.id == 0xFFFFFFFFu) ? (tt < best.t) : ((tt < best.t) || (tt == best.t && id < best.id));
-                if (take) {
-                    best.t = tt; best.u = uu; best.v = vv; best.id = id; best.inst = inst; best.prim = __float_as_uint(q2.w);
-                }
-            }
-        }
-        if (!(ng.y & 0xFF000000u)) {
-            if (sp == 0) break;
-            ng = stack[--sp];
-        }
-    }
-    return best;
+    TravState st;
+    TravStack stk;
+    trav_init(st, o, d, tmin, tmax, ignore_inst);
+    while (!trav_step<ANY, COUNT>(sc, st, stk, n_nodes, n_tris)) {}
+    return st.best;
 }
 
 }  // namespace rt

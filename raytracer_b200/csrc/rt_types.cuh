@@ -95,7 +95,8 @@ struct FrameParams {
     float inv_view[16];
     float inv_proj[16];
     float clear[3];
-    uint32_t frame;
+    uint32_t frame;                                 // first frame of the launch
+    uint32_t n_lanes;                               // consecutive frames traced together (wavefront pipeline)
     uint32_t width, height;
     uint32_t strip_rows, strip_index, strip_count;  // rows owned: (y / strip_rows) % strip_count == strip_index
     uint32_t local_rows;                            // rows in this context's compact image

@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librt.so")
+LIB_PATH = os.environ.get("RT_LIBRT_PATH") or os.path.join(_HERE, "csrc", "librt.so")  # override: kernel A/B experiments
 
 RT_OK = 0
 STATUS_NAMES = {
@@ -40,7 +40,7 @@ class RtConfig(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_depth", C.c_int32), ("rr_start_depth", C.c_int32),
                 ("radiance_clamp", C.c_float), ("flags", C.c_uint32), ("pipeline", C.c_uint32),
                 ("strip_rows", C.c_uint32), ("strip_index", C.c_uint32), ("strip_count", C.c_uint32),
-                ("reserved", C.c_uint32 * 7)]
+                ("frames_in_flight", C.c_uint32), ("reserved", C.c_uint32 * 6)]
 
 
 class RtMesh(C.Structure):
@@ -154,7 +154,7 @@ class Context:
 
     def __init__(self, device: int = -1, max_depth: int = 3, rr_start_depth: int = 3, radiance_clamp: float = 5.0,
                  counters: bool = True, pipeline: int = RT_PIPELINE_WAVEFRONT, strip_rows: int = 8, strip_index: int = 0,
-                 strip_count: int = 1):
+                 strip_count: int = 1, frames_in_flight: int = 0):
         self.L = load()
         cfg = RtConfig()
         self.L.rt_default_config(C.byref(cfg))
@@ -163,6 +163,8 @@ class Context:
         cfg.flags = RT_FLAG_DIRECT_LIGHTING | RT_FLAG_MIS | (RT_FLAG_COUNTERS if counters else 0)
         cfg.pipeline = pipeline
         cfg.strip_rows, cfg.strip_index, cfg.strip_count = strip_rows, strip_index, strip_count
+        if frames_in_flight:
+            cfg.frames_in_flight = frames_in_flight
         self.cfg = cfg
         h = C.c_void_p()
         rc = self.L.rt_create(C.byref(cfg), C.byref(h))

@@ -1,0 +1,68 @@
+"""Screen-tile sharding across the GPUs of one box — host-side plumbing only.
+
+The reference renders on one GPU.  Here every rank holds the whole scene and BVH and traces the image rows
+y with (y // strip_rows) % world == rank; seeds and camera rays use the full launch size
+(shaders/simple.rgen:71, :41-53), so the union of the ranks' rows is bit-identical to a one-GPU frame.
+The accumulation stays on each GPU across frames; rows only move at readback: one `gather` of the
+compact strip images to rank 0 (NCCL over NVLink on the GPU box, gloo in the CPU tests).
+`torch.distributed` is plumbing here: there is no collective on the per-frame data path.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+
+DEFAULT_STRIP_ROWS = 8
+
+
+def strip_rows_of(rank: int, world: int, height: int, strip_rows: int = DEFAULT_STRIP_ROWS) -> np.ndarray:
+    """Global row indices owned by `rank`, in the order of its compact image (rt_config.strip_*)."""
+    y = np.arange(height, dtype=np.int64)
+    return y[(y // strip_rows) % world == rank]
+
+
+def local_row_count(rank: int, world: int, height: int, strip_rows: int = DEFAULT_STRIP_ROWS) -> int:
+    return int(len(strip_rows_of(rank, world, height, strip_rows)))
+
+
+def assemble(parts, height: int, strip_rows: int = DEFAULT_STRIP_ROWS) -> np.ndarray:
+    """Full (H, W, C) image from per-rank compact strip images (rank order)."""
+    world = len(parts)
+    first = np.asarray(parts[0])
+    out = np.zeros((height,) + first.shape[1:], first.dtype)
+    for r, p in enumerate(parts):
+        rows = strip_rows_of(r, world, height, strip_rows)
+        out[rows] = np.asarray(p)[: len(rows)]
+    return out
+
+
+class StripGather:
+    """Gathers the ranks' compact strip images on rank 0 with one collective.
+
+    `local` tensors may live on the GPU (nccl) or the CPU (gloo).  Ranks own at most one strip more than
+    others, so every rank pads to the largest count and a single fixed-size gather moves everything."""
+
+    def __init__(self, dist, height: int, width: int, channels: int = 4, strip_rows: int = DEFAULT_STRIP_ROWS, device="cpu",
+                 dtype=None):
+        import torch
+
+        self.dist, self.torch = dist, torch
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.height, self.strip_rows = height, strip_rows
+        self.rows = [local_row_count(r, self.world, height, strip_rows) for r in range(self.world)]
+        self.max_rows = max(self.rows)
+        dtype = dtype or torch.float32
+        self.send = torch.zeros((self.max_rows, width, channels), dtype=dtype, device=device)
+        self.recv = [torch.empty_like(self.send) for _ in range(self.world)] if self.rank == 0 else None
+
+    def gather(self, local) -> Optional[list]:
+        """local: (rows[rank], W, C) tensor.  Returns the list of per-rank tensors on rank 0, else None."""
+        n = self.rows[self.rank]
+        if n:
+            self.send[:n].copy_(local[:n])
+        self.dist.gather(self.send, self.recv, dst=0)
+        return self.recv
+
+    def assemble_host(self, parts) -> np.ndarray:
+        return assemble([p[: self.rows[r]].cpu().numpy() for r, p in enumerate(parts)], self.height, self.strip_rows)

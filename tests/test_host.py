@@ -1,0 +1,109 @@
+"""CPU suite, part 2: the host-side mirror of the reference's scene / camera / loader interfaces."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, fixture_scene
+
+import raytracer_b200 as rb
+from raytracer_b200 import multi_gpu, proxy_scenes
+from raytracer_b200.scene_io import load_scene_npz, save_scene_npz
+
+REF = "/root/reference"  # present in the build container only; tests that read it skip elsewhere
+
+
+def test_record_layouts_match_the_reference():
+    assert rb.MATERIAL_DTYPE.itemsize == 44  # gpu_scene.odin:17-21 / ray_common.glsl:3-11
+    assert rb.VERTEX_DTYPE.itemsize == 24    # scene.odin:10-13 / ray_common.glsl:48-51
+    s = fixture_scene("cornell_box")
+    mesh_idx, mat_idx, model = s.packed_objects()
+    assert model.dtype == np.float32 and model.shape == (len(s.objects), 16)
+    assert s.packed_materials().nbytes == 44 * len(s.materials)
+
+
+def test_default_camera_is_the_applications():
+    c = rb.Camera(aspect=1280 / 1020)  # application.odin:52, camera.odin:45-85
+    ubo = c.ubo().reshape(4, 4, 4)     # proj, view, inverse_view, inverse_proj; column-major
+    assert np.allclose(ubo[2][3], [0, 0, -3, 1])          # camera position = translation column of inverse_view
+    assert ubo[0][1][1] < 0                                # proj[1][1] *= -1 (camera.odin:80)
+    assert np.allclose(ubo[0].T @ ubo[3].T, np.eye(4), atol=1e-5)
+    assert np.allclose(ubo[1].T @ ubo[2].T, np.eye(4), atol=1e-5)
+    t = np.tan(np.radians(45.0) / 2)
+    assert np.isclose(ubo[0][1][1], -1 / t, rtol=1e-6) and np.isclose(ubo[0][0][0], 1 / (t * 1280 / 1020), rtol=1e-6)
+
+
+def test_model_matrix_order_is_t_rx_ry_rz_s():
+    m = rb.model_matrix_from_trs((1, 2, 3), (90, 0, 0), (2, 2, 2)).reshape(4, 4).T  # scene.odin:213-224
+    p = m @ np.array([0, 1, 0, 1], np.float32)
+    assert np.allclose(p, [1, 2, 5, 1], atol=1e-5)  # scale 2, rotate +90 deg about x: y -> z, then translate
+
+
+def test_change_log_mirrors_scene_odin():
+    s = rb.Scene()
+    a = s.add_material(rb.Material("a"))
+    m = s.add_mesh(rb.create_plane())
+    s.add_object("o", m, a)
+    s.changes.clear()
+    s.update_material(a, rb.Material("b", roughness=0.2))
+    s.update_object_position(0, (1, 0, 0))
+    s.update_object_material(0, a)
+    s.update_object_mesh(0, m)
+    kinds = [c.type for c in s.changes]
+    T = rb.SceneChangeType
+    assert kinds == [T.Material_Changed, T.Object_Transform_Changed, T.Object_Material_Changed, T.Object_Mesh_Changed]
+
+
+@pytest.mark.parametrize("name,objects,tris,lights", [("cornell_box", 9, 5964, 1), ("cornell_pbr", 9, 8096, 1),
+                                                       ("conference_room_large_pbr", 39, 468, 0), ("conference", None, None, 4),
+                                                       ("multi_dispersion", 51, 9002, 0)])
+def test_fixture_scenes_have_the_surveyed_shape(name, objects, tris, lights):
+    s = fixture_scene(name)
+    if objects is not None:
+        assert len(s.objects) == objects and s.num_instanced_triangles() == tris
+    assert len(s.lights()) == lights
+
+
+def test_scene_npz_round_trip(tmp_path):
+    s = fixture_scene("cornell_pbr")
+    p = str(tmp_path / "x.npz")
+    save_scene_npz(p, s)
+    b = load_scene_npz(p)
+    assert np.array_equal(b.packed_materials(), s.packed_materials())
+    for x, y in zip(b.packed_objects(), s.packed_objects()):
+        assert np.array_equal(x, y)
+    assert all(np.array_equal(m0.vertices, m1.vertices) and np.array_equal(m0.indices, m1.indices) for m0, m1 in zip(b.meshes, s.meshes))
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference mount absent")
+@pytest.mark.parametrize("name,rel", [("cornell_box", "scenes/cornell_box.json"), ("cornell_pbr", "scenes/cornell_pbr.glb")])
+def test_loaders_reproduce_the_committed_fixtures(name, rel):
+    """scene_loader.odin:37-190 (glTF/GLB) and :193-253 (JSON) restated; fixtures were made with them."""
+    s = rb.load_scene(os.path.join(REF, rel))
+    f = fixture_scene(name)
+    assert np.array_equal(s.packed_materials(), f.packed_materials())
+    for x, y in zip(s.packed_objects(), f.packed_objects()):
+        assert np.array_equal(x, y)
+
+
+def test_loader_errors():
+    with pytest.raises(rb.SceneLoadError):
+        rb.load_scene_from_gltf("/nonexistent/file.glb")
+    with pytest.raises(rb.SceneLoadError):
+        rb.load_scene_from_gltf(os.path.join(GOLDEN, "oracle_cornell_box.npz"))  # wrong extension -> Invalid_File
+
+
+def test_sponza_proxy_keeps_the_gltf_layout():
+    s = proxy_scenes.sponza_proxy()
+    assert len(s.objects) == 103 and s.num_instanced_triangles() == 262267 and len(s.materials) == 25 and not s.lights()
+
+
+@pytest.mark.parametrize("world,height,strip", [(1, 17, 8), (2, 1080, 8), (4, 1080, 8), (8, 1080, 8), (8, 61, 4), (3, 5, 8)])
+def test_strip_partition_is_a_partition(world, height, strip):
+    rows = [multi_gpu.strip_rows_of(r, world, height, strip) for r in range(world)]
+    allr = np.sort(np.concatenate(rows))
+    assert np.array_equal(allr, np.arange(height))
+    parts = [np.full((len(r), 3, 1), k, np.int32) for k, r in enumerate(rows)]
+    img = multi_gpu.assemble(parts, height, strip)
+    for k, r in enumerate(rows):
+        assert (img[r] == k).all()

@@ -1,0 +1,63 @@
+"""CPU suite, part 4: the N > 1 host path on world_size-2 gloo.  Each rank renders its own screen strips
+(with the CPU oracle standing in for the GPU, which this container lacks), the strips are gathered on rank 0
+with the same StripGather the GPU path uses, and the assembled image must equal a one-rank frame bit for bit
+(seeds and camera rays use the full launch size)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from conftest import CLEAR, fixture_scene
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, W, H, strip, out_path):
+    import torch
+    import torch.distributed as dist
+
+    from oracle.binding import OracleScene
+    from raytracer_b200 import multi_gpu
+    import raytracer_b200 as rb
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        orc = OracleScene(fixture_scene("cornell_pbr")).build_bvh()
+        cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+        rows = multi_gpu.strip_rows_of(rank, world, H, strip)
+        full = np.zeros((H, W, 4), np.float32)
+        for f in range(2):  # two accumulated frames, each rank only touches its own rows
+            for y0 in rows[::strip] if len(rows) else []:
+                y1 = min(H, int(y0) + strip)
+                orc.render(cam.ubo(), CLEAR, f, W, H, image=full, y0=int(y0), y1=y1)
+        local = torch.from_numpy(full[rows].copy())
+        g = multi_gpu.StripGather(dist, H, W, 4, strip)
+        parts = g.gather(local)
+        if rank == 0:
+            np.save(out_path, g.assemble_host(parts))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,H,strip", [(2, 40, 8), (2, 21, 4)])
+def test_two_rank_strips_assemble_to_the_single_rank_frame(tmp_path, oracle_lib, world, H, strip):
+    import torch.multiprocessing as mp
+
+    import raytracer_b200 as rb
+
+    W = 32
+    out = str(tmp_path / "img.npy")
+    mp.spawn(_worker, args=(world, _free_port(), W, H, strip, out), nprocs=world, join=True)
+    got = np.load(out)
+    orc = oracle_lib.OracleScene(fixture_scene("cornell_pbr")).build_bvh()
+    cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+    ref = None
+    for f in range(2):
+        ref = orc.render(cam.ubo(), CLEAR, f, W, H, image=ref)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))

@@ -1,0 +1,124 @@
+"""CPU suite, part 1: the oracle itself (runs with -m "not gpu").
+
+The reference holds no tests, golden vectors or CPU path, so the pins available are:
+integer-exact RNG against an independent NumPy restatement of shaders/random.glsl:23-53, analytic facts
+(create_sphere counts, furnace bound, brute force vs BVH), and the committed golden frames."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import CLEAR, GOLDEN, fixture_scene, random_rays, soup_scene
+
+import raytracer_b200 as rb
+
+
+def _tea_numpy(a, b):  # shaders/random.glsl:23-37, written independently of oracle_math.h
+    v0, v1, s = np.uint32(a), np.uint32(b), np.uint32(0)
+    with np.errstate(over="ignore"):
+        for _ in range(16):
+            s = np.uint32(s + np.uint32(0x9E3779B9))
+            v0 = np.uint32(v0 + (((v1 << np.uint32(4)) + np.uint32(0xA341316C)) ^ (v1 + s) ^ ((v1 >> np.uint32(5)) + np.uint32(0xC8013EA4))))
+            v1 = np.uint32(v1 + (((v0 << np.uint32(4)) + np.uint32(0xAD90777D)) ^ (v0 + s) ^ ((v0 >> np.uint32(5)) + np.uint32(0x7E95761E))))
+    return int(v0)
+
+
+def test_tea_lcg_against_numpy(oracle_lib):
+    rng = np.random.default_rng(1)
+    for a, b in [(0, 0), (1, 0), (0, 1), (262143, 7), (0xFFFFFFFF, 0xFFFFFFFF)] + [tuple(int(x) for x in rng.integers(0, 2**32, 2)) for _ in range(200)]:
+        assert oracle_lib.tea(a, b) == _tea_numpy(a, b)
+    seed = _tea_numpy(12345, 3)
+    vals, state = oracle_lib.rnd_seq(seed, 64)
+    s = seed
+    for v in vals:  # random.glsl:41-53
+        s = (1664525 * s + 1013904223) & 0xFFFFFFFF
+        assert v == np.float32(s & 0x00FFFFFF) / np.float32(16777216.0)
+    assert state == s
+    assert vals.min() >= 0.0 and vals.max() < 1.0
+
+
+def test_sincos_accuracy(oracle_lib):
+    a = np.linspace(0.0, 2.0 * np.pi, 20001).astype(np.float32)
+    s, c = oracle_lib.sincos(a)
+    assert np.abs(s - np.sin(a.astype(np.float64))).max() < 3e-7
+    assert np.abs(c - np.cos(a.astype(np.float64))).max() < 3e-7
+
+
+def test_create_sphere_and_plane_counts():
+    s = rb.create_sphere()  # scene.odin:250-320: 32 x 32 UV sphere
+    assert len(s.vertices) == 994 and len(s.indices) // 3 == 1984
+    p = rb.create_plane()
+    assert len(p.indices) // 3 == 2
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "cornell_pbr"])
+def test_golden_frames_oracle(oracle_lib, name):
+    """The oracle reproduces the committed golden frames and counters (tools/make_fixtures.py)."""
+    z = np.load(os.path.join(GOLDEN, f"oracle_{name}.npz"))
+    orc = oracle_lib.OracleScene(fixture_scene(name)).build_bvh()
+    H, W = z["frames"].shape[1:3]
+    img, cnt = None, np.zeros(6, np.uint64)
+    for f in range(z["frames"].shape[0]):
+        img = orc.render(z["camera"], CLEAR, f, W, H, image=img, counters=cnt)
+        assert np.array_equal(img.view(np.uint32), z["frames"][f].view(np.uint32))
+    assert [int(x) for x in cnt] == [int(x) for x in z["counters"]]
+    nodes, tris, keys, ids = orc.bvh_arrays()
+    assert len(nodes) == int(z["n_nodes"]) and orc.bvh_depth == int(z["bvh_depth"])
+    assert np.array_equal(ids[:256], z["sorted_ids_head"]) and np.array_equal(keys[:256], z["morton_head"])
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "cornell_pbr", "conference_mirror_chairs"])
+def test_bvh_traversal_equals_brute_force(oracle_lib, name):
+    orc = oracle_lib.OracleScene(fixture_scene(name)).build_bvh()
+    rays = random_rays(4000, seed=3, lo=(-3, -1, -4), hi=(3, 3, 4))
+    t0, i0 = orc.trace_rays(rays, mode="brute")
+    t1, i1 = orc.trace_rays(rays, mode="bvh")
+    assert np.array_equal(i0, i1) and np.array_equal(t0.view(np.uint32), t1.view(np.uint32))
+    assert (i0 != 0xFFFFFFFF).sum() > 100
+    rays[:, 7] = 2.5
+    ig = np.full(len(rays), 5, np.uint32)
+    _, o0 = orc.trace_rays(rays, mode="brute", any_hit=True, ignore_inst=ig)
+    _, o1 = orc.trace_rays(rays, mode="bvh", any_hit=True, ignore_inst=ig)
+    assert np.array_equal(o0, o1)
+
+
+def test_bvh_render_equals_brute_force_render(oracle_lib):
+    scene = fixture_scene("cornell_pbr")
+    orc = oracle_lib.OracleScene(scene).build_bvh()
+    cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=1.0, target=(0.0, 1.0, 0.0))
+    a = orc.render(cam.ubo(), CLEAR, 1, 32, 32, use_bvh=True)
+    b = orc.render(cam.ubo(), CLEAR, 1, 32, 32, use_bvh=False)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+def test_furnace_bound(oracle_lib):
+    """White diffuse closed box, no lights, camera inside: every path ends on the sky term or dies, so the
+    radiance is bounded by the clear colour (simple.rgen:106-109 with throughput <= 1 for albedo <= 1)."""
+    s = rb.Scene()
+    s.add_material(rb.Material("white", albedo=(1.0, 1.0, 1.0), roughness=1.0, metallic=0.0))
+    plane = s.add_mesh(rb.create_plane())
+    for pos, rot in (((0, -2, 0), (-90, 0, 0)), ((0, 2, 0), (90, 0, 0)), ((0, 0, 2), (0, 180, 0)), ((0, 0, -5), (0, 0, 0)),
+                     ((-2, 0, 0), (0, 90, 0)), ((2, 0, 0), (0, -90, 0))):
+        s.add_object("wall", plane, 0, pos, rot, (12, 12, 1))
+    s.changes.clear()
+    orc = oracle_lib.OracleScene(s).build_bvh()
+    img = orc.render(rb.Camera(aspect=1.0).ubo(), CLEAR, 2, 48, 48)
+    assert np.isfinite(img).all()
+    assert (img[..., :3] <= np.asarray(CLEAR, np.float32) * 1.0001 + 1e-6).all()
+
+
+def test_light_tables_follow_reference_rules(oracle_lib):
+    """gpu_scene.odin:366-379: a light is any object whose material has emission_power > 0."""
+    scene = fixture_scene("conference")
+    orc = oracle_lib.OracleScene(scene)
+    assert orc.num_lights == len(scene.lights()) == 4
+    assert oracle_lib.OracleScene(fixture_scene("conference_room_large_pbr")).num_lights == 0
+
+
+def test_soup_oracle_counters_are_sane(oracle_lib):
+    s = soup_scene(3000)
+    orc = oracle_lib.OracleScene(s).build_bvh()
+    cnt = np.zeros(6, np.uint64)
+    orc.render(rb.Camera(position=(0.5, 0.5, -2.0), target=(0.5, 0.5, 0.5)).ubo(), CLEAR, 1, 32, 32, counters=cnt)
+    ext, sh, nodes, tris, hits, nee = (int(x) for x in cnt)
+    assert 32 * 32 <= ext <= 3 * 32 * 32 and hits <= ext and nee <= hits and sh <= nee and nodes >= ext
