@@ -246,8 +246,8 @@ def run_ours(args):
         ctx.set_profiling(False)
         ext = kprof["extend"]
         ext_nodes, ext_tris = cnt["nodes"] - cnt["shadow_nodes"], cnt["tris"] - cnt["shadow_tris"]
-        # algorithmic bytes of the extend kernel: BVH8 nodes 80 B + triangles 48 B fetched, ray in 32 B, hit out 16 B
-        alg_bytes = ext_nodes * 80 + ext_tris * 48 + cnt["extend_rays"] * 48
+        # algorithmic bytes of the extend kernel: BVH8 nodes 128 B + triangles 48 B fetched, ray in 32 B, hit out 16 B
+        alg_bytes = ext_nodes * 128 + ext_tris * 48 + cnt["extend_rays"] * 48
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))

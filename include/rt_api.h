@@ -120,7 +120,7 @@ typedef struct rt_material {
 typedef struct rt_counters {
     uint64_t extend_rays;   /* closest-hit rays issued (traceRayEXT, simple.rgen:92-104) */
     uint64_t shadow_rays;   /* visibility rays issued (isVisibleRQ, simple.rchit:350-385) */
-    uint64_t nodes;         /* BVH8 nodes fetched (80 B each) */
+    uint64_t nodes;         /* BVH8 nodes fetched (128 B each) */
     uint64_t tris;          /* triangles fetched (48 B each) */
     uint64_t hits;          /* closest-hit shader invocations */
     uint64_t nee;           /* light samples taken */
@@ -250,7 +250,7 @@ RT_API int rt_get_kernel_profile(rt_ctx* ctx, rt_kernel_profile* out);
 RT_API int rt_trace_rays_closest(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id);
 RT_API int rt_trace_rays_any(rt_ctx* ctx, const float* rays, uint32_t n, const uint32_t* ignore_inst, uint32_t* out_occluded);
 /* BVH download for the bit-exact comparison with the deterministic CPU twin.
- * nodes: n_nodes x 80 B, tris: n_triangles x 48 B, morton/sorted ids: n_triangles each; NULL skips. */
+ * nodes: n_nodes x 128 B, tris: n_triangles x 48 B, morton/sorted ids: n_triangles each; NULL skips. */
 RT_API int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t tris_bytes, uint64_t* morton,
                uint32_t* sorted_ids);
 

@@ -122,10 +122,10 @@ class OracleScene:
         return self.L.orc_bvh_depth(self.h)
 
     def bvh_arrays(self):
-        """(nodes uint8[n,80], tris uint8[m,48], morton u64[T], sorted_ids u32[T])."""
+        """(nodes uint8[n,128], tris uint8[m,48], morton u64[T], sorted_ids u32[T])."""
         nn = self.L.orc_num_nodes(self.h)
         nt = self.num_tris
-        nodes = np.zeros((nn, 80), np.uint8)
+        nodes = np.zeros((nn, 128), np.uint8)
         tris = np.zeros((nt, 48), np.uint8)
         keys = np.zeros(nt, np.uint64)
         ids = np.zeros(nt, np.uint32)

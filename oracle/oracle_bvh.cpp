@@ -190,9 +190,23 @@ static Box bin_box_rec(BinTree& bt, uint32_t node) {
     return b;
 }
 
+// binary16 <-> small non-negative integers (exact up to 2048): written out so the oracle needs no half type
+static inline uint16_t half_of_int(int q) {
+    if (q <= 0) return 0;
+    int e = 31 - __builtin_clz((uint32_t)q);              // q = 1.m x 2^e, e <= 11
+    uint32_t man = ((uint32_t)q << (10 - e)) & 0x3FFu;    // q <= 2048 loses no bits
+    return (uint16_t)(((uint32_t)(e + 15) << 10) | man);
+}
+static inline float int_of_half(uint16_t h) {
+    if (h == 0) return 0.0f;
+    int e = (int)(h >> 10) - 15;
+    uint32_t man = (h & 0x3FFu) | 0x400u;
+    return (float)man * u2f((uint32_t)(e - 10 + 127) << 23);
+}
+
 static void quantize_axis(float lo, float hi, int* e_out, float* p_out) {
     float ext = hi - lo;
-    float f = ext / 252.0f;
+    float f = ext / ORC_QSTEPS;
     uint32_t bits = f2u(f);
     int e = (int)((bits >> 23) & 0xFFu) - 127 + ((bits & 0x7FFFFFu) ? 1 : 0);
     float mag = gmax(fabsf(lo), fabsf(hi));
@@ -212,7 +226,7 @@ void build_bvh8(Scene& s) {
     s.has_bvh = true;
     if (n == 0) {
         Node8 nd; memset(&nd, 0, sizeof(nd));
-        for (int a = 0; a < 3; a++) { nd.e[a] = 127; for (int c = 0; c < 8; c++) { nd.qlo[a][c] = 255; nd.qhi[a][c] = 0; } }
+        for (int a = 0; a < 3; a++) { nd.e[a] = 127; for (int c = 0; c < 8; c++) { nd.q[a][0][c] = half_of_int(ORC_QMAX); nd.q[a][1][c] = half_of_int(0); } }
         s.nodes.push_back(nd);
         return;
     }
@@ -367,7 +381,7 @@ void build_bvh8(Scene& s) {
                 int c = child_in_slot[sl];
                 if (c < 0) {
                     nd.meta[sl] = 0;
-                    for (int a = 0; a < 3; a++) { nd.qlo[a][sl] = 255; nd.qhi[a][sl] = 0; }
+                    for (int a = 0; a < 3; a++) { nd.q[a][0][sl] = half_of_int(ORC_QMAX); nd.q[a][1][sl] = half_of_int(0); }
                     continue;
                 }
                 const Box& cb = bt.box[ch[c]];
@@ -375,8 +389,8 @@ void build_bvh8(Scene& s) {
                 for (int a = 0; a < 3; a++) {
                     int ql = (int)floorf((clo[a] - nd.p[a]) * inv_scale[a]) - 1;
                     int qh = (int)ceilf((chi[a] - nd.p[a]) * inv_scale[a]) + 1;
-                    nd.qlo[a][sl] = (uint8_t)std::min(std::max(ql, 0), 255);
-                    nd.qhi[a][sl] = (uint8_t)std::min(std::max(qh, 0), 255);
+                    nd.q[a][0][sl] = half_of_int(std::min(std::max(ql, 0), ORC_QMAX));
+                    nd.q[a][1][sl] = half_of_int(std::min(std::max(qh, 0), ORC_QMAX));
                 }
                 uint32_t cn = bt.cnt(ch[c]);
                 if (!bt.is_leaf(ch[c]) && cn > 3) {
@@ -445,8 +459,8 @@ static inline uint32_t node_hits(const Node8& nd, const TravRay& r, float tmin, 
         float tn[3], tf[3];
         for (int a = 0; a < 3; a++) {
             bool negd = (r.rbits >> a) & 1u;
-            float qn = (float)(negd ? nd.qhi[a][sl] : nd.qlo[a][sl]);
-            float qf = (float)(negd ? nd.qlo[a][sl] : nd.qhi[a][sl]);
+            float qn = int_of_half(nd.q[a][negd ? 1 : 0][sl]);
+            float qf = int_of_half(nd.q[a][negd ? 0 : 1][sl]);
             tn[a] = fmaf(qn, sc[a], orr[a]);
             tf[a] = fmaf(qf, sc[a], orr[a]);
         }

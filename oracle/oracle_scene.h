@@ -44,7 +44,9 @@ struct Hit {
     uint32_t id;     // flat triangle id, 0xFFFFFFFF = miss
 };
 
-// 80-byte compressed wide node (own layout)
+// 128-byte compressed wide node (own layout): grid coordinates of the child boxes as binary16
+#define ORC_QMAX 2046
+#define ORC_QSTEPS 2044.0f
 struct Node8 {
     float p[3];
     uint8_t e[3];
@@ -52,10 +54,9 @@ struct Node8 {
     uint32_t child_base;
     uint32_t tri_base;
     uint8_t meta[8];
-    uint8_t qlo[3][8];
-    uint8_t qhi[3][8];
+    uint16_t q[3][2][8];  // [axis][0 = lo, 1 = hi][slot]
 };
-static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
+static_assert(sizeof(Node8) == 128, "Node8 must be 128 bytes");
 
 struct BvhTri {  // 48 B: three float4
     float p0[3]; uint32_t id;

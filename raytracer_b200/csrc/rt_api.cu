@@ -683,7 +683,7 @@ int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t 
     CTX_CHECK(ctx);
     const int rc = flush_scene(ctx);
     if (rc != RT_OK) return rc;
-    const size_t nb = (size_t)ctx->bvh.n_nodes * 80, tb = (size_t)ctx->n_tris * 48;
+    const size_t nb = (size_t)ctx->bvh.n_nodes * sizeof(Node8), tb = (size_t)ctx->n_tris * 48;
     if ((nodes && nodes_bytes < nb) || (tris && tris_bytes < tb)) { set_error("rt_get_bvh: buffer too small"); return RT_ERR_INVALID_ARGUMENT; }
     if (nodes) RT_CUDA_TRY(cudaMemcpyAsync(nodes, ctx->bvh.nodes.p, nb, cudaMemcpyDeviceToHost, ctx->stream));
     if (tris && tb) RT_CUDA_TRY(cudaMemcpyAsync(tris, ctx->bvh.tris.p, tb, cudaMemcpyDeviceToHost, ctx->stream));

@@ -419,9 +419,12 @@ __global__ void collapse_kernel(TreeView bt, const uint32_t* level, uint32_t n_l
     n_tri[w] = nt;
 }
 
+// binary16 bits of an integer 0..2048 (exact)
+__device__ __forceinline__ uint16_t half_of_int(int q) { return half_bits_rne((float)q); }
+
 __device__ __forceinline__ void quantize_axis(float lo, float hi, int* e_out, float* p_out) {
     const float ext = hi - lo;
-    const float f = ext / 252.0f;
+    const float f = ext / RT_QSTEPS;
     const uint32_t bits = __float_as_uint(f);
     int e = (int)((bits >> 23) & 0xFFu) - 127 + ((bits & 0x7FFFFFu) ? 1 : 0);
     const float mag = glsl_max(fabsf(lo), fabsf(hi));
@@ -462,7 +465,7 @@ __global__ void emit_kernel(TreeView bt, const uint32_t* level, uint32_t n_level
         const uint32_t c = child_slots[(size_t)w * 8 + sl];
         if (c == 0xFFFFFFFFu) {
             nd.meta[sl] = 0;
-            for (int a = 0; a < 3; a++) { nd.qlo[a][sl] = 255; nd.qhi[a][sl] = 0; }
+            for (int a = 0; a < 3; a++) { nd.q[a][0][sl] = half_of_int(RT_QMAX); nd.q[a][1][sl] = half_of_int(0); }
             continue;
         }
         const float4 cl = bt.lo[c], chh = bt.hi[c];
@@ -470,8 +473,8 @@ __global__ void emit_kernel(TreeView bt, const uint32_t* level, uint32_t n_level
         for (int a = 0; a < 3; a++) {
             const int ql = (int)floorf((clo[a] - nd.p[a]) * inv_scale[a]) - 1;
             const int qh = (int)ceilf((chi[a] - nd.p[a]) * inv_scale[a]) + 1;
-            nd.qlo[a][sl] = (uint8_t)min(max(ql, 0), 255);
-            nd.qhi[a][sl] = (uint8_t)min(max(qh, 0), 255);
+            nd.q[a][0][sl] = half_of_int(min(max(ql, 0), RT_QMAX));
+            nd.q[a][1][sl] = half_of_int(min(max(qh, 0), RT_QMAX));
         }
         const uint32_t cn = bt.cnt(c);
         if (!bt.is_leaf(c) && cn > 3u) {
@@ -496,7 +499,7 @@ __global__ void emit_kernel(TreeView bt, const uint32_t* level, uint32_t n_level
     const uint4* src = reinterpret_cast<const uint4*>(&nd);
     uint4* dst = reinterpret_cast<uint4*>(nodes + level_first + w);
 #pragma unroll
-    for (int k = 0; k < 5; k++) dst[k] = src[k];
+    for (int k = 0; k < (int)RT_NODE_WORDS; k++) dst[k] = src[k];
     if (w == n_level - 1) {  // level totals for the host loop
         scratch->level_int = int_prefix[w] + n_int;
         scratch->level_tris = tri_prefix[w] + tri_off;
@@ -508,7 +511,7 @@ __global__ void empty_root_kernel(Node8* nodes) {
     memset(&nd, 0, sizeof(nd));
     for (int a = 0; a < 3; a++) {
         nd.e[a] = 127;
-        for (int c = 0; c < 8; c++) { nd.qlo[a][c] = 255; nd.qhi[a][c] = 0; }
+        for (int c = 0; c < 8; c++) { nd.q[a][0][c] = half_of_int(RT_QMAX); nd.q[a][1][c] = half_of_int(0); }
     }
     nodes[0] = nd;
 }
@@ -532,7 +535,7 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
     BUILD_TRY(cudaEventCreate(&ev1));
     BUILD_TRY(cudaEventRecord(ev0, stream));
     const uint32_t max_nodes = n / 3 + 2;  // every wide node below the root covers > 3 triangles: W(n) <= (n-1)/3
-    BUILD_TRY(out.nodes.alloc((size_t)max_nodes * 5));
+    BUILD_TRY(out.nodes.alloc((size_t)max_nodes * RT_NODE_WORDS));
     BUILD_TRY(out.tris.alloc((size_t)n * 3));
     BUILD_TRY(out.morton.alloc(n));
     BUILD_TRY(out.sorted_ids.alloc(n));

@@ -251,7 +251,12 @@ __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView w
 // run dry: a lane whose ray has finished gets the next entry as soon as RT_REFILL_IDLE lanes are idle,
 // instead of waiting for the slowest ray of its batch (Aila & Laine 2009, "dynamic fetch").
 #define RT_FETCH_CHUNK 128u
+#ifndef RT_REFILL_IDLE
 #define RT_REFILL_IDLE 8u
+#endif
+#ifndef RT_TRAV_MIN_BLOCKS
+#define RT_TRAV_MIN_BLOCKS 7  /* 72 registers: the occupancy sweep in profiles/ favours 7 blocks of 128 */
+#endif
 
 struct WarpFetch {
     uint32_t next, end;  // the warp's private range of queue indices (warp-uniform)
@@ -288,7 +293,7 @@ __device__ __forceinline__ uint32_t warp_fetch(WarpFetch& wfetch, uint32_t* curs
 
 // extend: closest hit for every queued path (traceRayEXT of simple.rgen:92-104).
 template <bool COUNT>
-__global__ void __launch_bounds__(128) wf_extend_kernel(SceneView sc, WfView wf, const uint32_t* queue, uint32_t q_idx,
+__global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_extend_kernel(SceneView sc, WfView wf, const uint32_t* queue, uint32_t q_idx,
                                                         DevCounters* counters) {
     const uint32_t n = wf.ctrl[q_idx];
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
@@ -418,7 +423,7 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(SceneView sc, FrameParams
 
 // shadow: isVisibleRQ (simple.rchit:350-385) for every queued NEE sample, then the ordered colour adds
 template <bool COUNT>
-__global__ void __launch_bounds__(128) wf_shadow_kernel(SceneView sc, FrameParams fp, WfView wf, DevCounters* counters) {
+__global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_shadow_kernel(SceneView sc, FrameParams fp, WfView wf, DevCounters* counters) {
     const uint32_t n = wf.ctrl[CT_SH];
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     WarpFetch wfetch;

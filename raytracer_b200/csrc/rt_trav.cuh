@@ -6,7 +6,13 @@
 // lowest flat triangle id, so the result is independent of traversal order.  The ray/triangle test is
 // the watertight test of Woop, Benthin & Wald (2013) with the evaluation order fixed below.
 #pragma once
+#include <cuda_fp16.h>
+
 #include "rt_types.cuh"
+
+#ifndef RT_USE_FFMA2
+#define RT_USE_FFMA2 1
+#endif
 
 namespace rt {
 
@@ -80,26 +86,23 @@ __device__ __forceinline__ bool tri_isect(const TravRay& r, float4 q0, float4 q1
     return true;
 }
 
-__device__ __forceinline__ float byte_f(uint32_t w, int k) { return (float)((w >> (8 * k)) & 0xFFu); }
+// binary16 -> binary32 of the low / high half of a word: HADD2.F32 with an operand selector (FMA pipe)
+__device__ __forceinline__ float half_lo(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w & 0xFFFFu))); }
+__device__ __forceinline__ float half_hi(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w >> 16))); }
 
-// Slab test of the 8 quantised child boxes.  Result: bits [31:24] = internal children that are hit, at
-// position 24 + (slot ^ octant) (so the highest bit is the nearest octant); bits [23:0] = triangles.
-__device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, const uint4 w2, const uint4 w3,
-                                              const uint4 w4, const TravRay& r, float tmin, float tmax) {
+// Slab test of the 8 quantised child boxes.  nx/fx .. nz/fz: the near and far plane words of each axis (8 grid
+// coordinates each), already chosen by the ray's sign.  Result: bits [31:24] = internal children that are
+// hit, at position 24 + (slot ^ octant) (so the highest bit is the nearest octant); bits [23:0] = triangles.
+__device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, const uint4 nx, const uint4 fx, const uint4 ny,
+                                              const uint4 fy, const uint4 nz, const uint4 fz, const TravRay& r, float tmin,
+                                              float tmax) {
     const uint32_t ew = w0.w;  // e.x e.y e.z imask
     const float scx = __uint_as_float((ew & 0xFFu) << 23) * r.idx;
     const float scy = __uint_as_float(((ew >> 8) & 0xFFu) << 23) * r.idy;
     const float scz = __uint_as_float(((ew >> 16) & 0xFFu) << 23) * r.idz;
-    const uint32_t imask = ew >> 24;
     const float orx = (__uint_as_float(w0.x) - r.ox) * r.idx;
     const float ory = (__uint_as_float(w0.y) - r.oy) * r.idy;
     const float orz = (__uint_as_float(w0.z) - r.oz) * r.idz;
-    // near/far byte planes per axis, chosen by the ray's sign
-    const bool nx = r.rbits & 1u, ny = r.rbits & 2u, nz = r.rbits & 4u;
-    // qlo.x = w2.xy, qlo.y = w2.zw, qlo.z = w3.xy, qhi.x = w3.zw, qhi.y = w4.xy, qhi.z = w4.zw
-    const uint32_t nX0 = nx ? w3.z : w2.x, nX1 = nx ? w3.w : w2.y, fX0 = nx ? w2.x : w3.z, fX1 = nx ? w2.y : w3.w;
-    const uint32_t nY0 = ny ? w4.x : w2.z, nY1 = ny ? w4.y : w2.w, fY0 = ny ? w2.z : w4.x, fY1 = ny ? w2.w : w4.y;
-    const uint32_t nZ0 = nz ? w4.z : w3.x, nZ1 = nz ? w4.w : w3.y, fZ0 = nz ? w3.x : w4.z, fZ1 = nz ? w3.y : w4.w;
     const float2 scx2 = make_float2(scx, scx), scy2 = make_float2(scy, scy), scz2 = make_float2(scz, scz);
     const float2 orx2 = make_float2(orx, orx), ory2 = make_float2(ory, ory), orz2 = make_float2(orz, orz);
     // meta bytes, four children at a time: internal children (24..31 in the low five bits) get their slot
@@ -112,16 +115,22 @@ __device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, co
         const uint32_t inner4 = ((meta4 & (meta4 << 1)) & 0x10101010u) >> 4;
         const uint32_t idx4 = (meta4 ^ (oct4 & (inner4 * 0xFFu))) & 0x1F1F1F1Fu;
         const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
-        const uint32_t nX = half ? nX1 : nX0, fX = half ? fX1 : fX0;
-        const uint32_t nY = half ? nY1 : nY0, fY = half ? fY1 : fY0;
-        const uint32_t nZ = half ? nZ1 : nZ0, fZ = half ? fZ1 : fZ0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
+            // children 2j, 2j+1 of an axis share word j of its plane vector
+            const int j = half * 2 + (k >> 1);
+            const uint32_t wnx = j == 0 ? nx.x : (j == 1 ? nx.y : (j == 2 ? nx.z : nx.w));
+            const uint32_t wfx = j == 0 ? fx.x : (j == 1 ? fx.y : (j == 2 ? fx.z : fx.w));
+            const uint32_t wny = j == 0 ? ny.x : (j == 1 ? ny.y : (j == 2 ? ny.z : ny.w));
+            const uint32_t wfy = j == 0 ? fy.x : (j == 1 ? fy.y : (j == 2 ? fy.z : fy.w));
+            const uint32_t wnz = j == 0 ? nz.x : (j == 1 ? nz.y : (j == 2 ? nz.z : nz.w));
+            const uint32_t wfz = j == 0 ? fz.x : (j == 1 ? fz.y : (j == 2 ? fz.z : fz.w));
+            const bool hi = (k & 1) != 0;
             // near and far plane of an axis share scale and offset: one packed FFMA2 (sm_100 f32x2) per axis,
             // each half rounded exactly like fmaf
-            const float2 tx = __ffma2_rn(make_float2(byte_f(nX, k), byte_f(fX, k)), scx2, orx2);
-            const float2 ty = __ffma2_rn(make_float2(byte_f(nY, k), byte_f(fY, k)), scy2, ory2);
-            const float2 tz = __ffma2_rn(make_float2(byte_f(nZ, k), byte_f(fZ, k)), scz2, orz2);
+            const float2 tx = __ffma2_rn(make_float2(hi ? half_hi(wnx) : half_lo(wnx), hi ? half_hi(wfx) : half_lo(wfx)), scx2, orx2);
+            const float2 ty = __ffma2_rn(make_float2(hi ? half_hi(wny) : half_lo(wny), hi ? half_hi(wfy) : half_lo(wfy)), scy2, ory2);
+            const float2 tz = __ffma2_rn(make_float2(hi ? half_hi(wnz) : half_lo(wnz), hi ? half_hi(wfz) : half_lo(wfz)), scz2, orz2);
             const float tnear = fmaxf(fmaxf(tx.x, ty.x), fmaxf(tz.x, tmin));
             const float tfar = fminf(fminf(tx.y, ty.y), fminf(tz.y, tmax));
             const uint32_t hit = ((bits4 >> (8 * k)) & 0xFFu) << ((idx4 >> (8 * k)) & 0xFFu);
@@ -168,10 +177,15 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
     const uint32_t rel = __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
     const uint32_t node = ng.x + rel;
     if (ng.y & 0xFF000000u) stk.e[st.sp++] = ng;
-    const uint4* np = sc.nodes + (size_t)node * 5u;
-    const uint4 w0 = __ldg(np), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
+    const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
+    // near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one
+    const uint32_t sx = r.rbits & 1u, sy = (r.rbits >> 1) & 1u, sz = r.rbits >> 2;
+    const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
+    const uint4 nx = __ldg(np + 2 + sx), fx = __ldg(np + 3 - sx);
+    const uint4 ny = __ldg(np + 4 + sy), fy = __ldg(np + 5 - sy);
+    const uint4 nz = __ldg(np + 6 + sz), fz = __ldg(np + 7 - sz);
     if (COUNT) n_nodes++;
-    const uint32_t hm = node_hits(w0, w1, w2, w3, w4, r, st.tmin, st.best.t);
+    const uint32_t hm = node_hits(w0, w1, nx, fx, ny, fy, nz, fz, r, st.tmin, st.best.t);
     ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
     uint32_t tmask = hm & 0x00FFFFFFu;
     while (tmask) {

@@ -17,12 +17,19 @@
 
 namespace rt {
 
-// 80-byte compressed 8-wide node: five 16-byte words, fetched with five LDG.128.
+// 128-byte compressed 8-wide node = one cache line = eight 16-byte words:
 //   word 0: p.x p.y p.z | e.x e.y e.z imask
 //   word 1: child_base tri_base meta[0..3] meta[4..7]
-//   word 2: qlo.x[8] qlo.y[8]      word 3: qlo.z[8] qhi.x[8]      word 4: qhi.y[8] qhi.z[8]
-// Child box on axis a = p[a] + 2^(e[a]-127) * [qlo, qhi].  meta: 0 = empty slot; internal child =
-// 0x20 | (24 + slot) (one bit, position = slot); leaf = unary triangle count << 5 | offset from tri_base.
+//   word 2: lo.x[8]   word 3: hi.x[8]   word 4: lo.y[8]   word 5: hi.y[8]   word 6: lo.z[8]   word 7: hi.z[8]
+// Child box on axis a = p[a] + 2^(e[a]-127) * [lo, hi], the grid coordinates lo/hi in 0..RT_QMAX stored as
+// binary16 (exact for integers <= 2048).  binary16 rather than bytes because the B200 converts half->float on
+// the FMA pipe (HADD2.F32, free .H0/.H1 operand select) while byte->float (I2F.U8) runs on the 16-lane XU
+// pipe, which the profile of the byte format showed to be the busiest pipe of the traversal (profiles/).
+// The near / far plane of an axis is picked by ADDRESS (word 2 + 2a + sign), not by a select per node.
+// meta: 0 = empty slot; internal child = 0x20 | (24 + slot) (one bit, position = slot); leaf = unary
+// triangle count << 5 | offset from tri_base.
+#define RT_QMAX 2046
+#define RT_QSTEPS 2044.0f
 struct __align__(16) Node8 {
     float p[3];
     uint8_t e[3];
@@ -30,10 +37,10 @@ struct __align__(16) Node8 {
     uint32_t child_base;
     uint32_t tri_base;
     uint8_t meta[8];
-    uint8_t qlo[3][8];
-    uint8_t qhi[3][8];
+    uint16_t q[3][2][8];  // [axis][0 = lo, 1 = hi][slot], binary16 bits
 };
-static_assert(sizeof(Node8) == 80, "Node8 is 80 bytes");
+static_assert(sizeof(Node8) == 128, "Node8 is 128 bytes");
+#define RT_NODE_WORDS 8u
 
 // 48-byte triangle: three float4 (world-space vertices + ids), fetched with three LDG.128.
 struct __align__(16) BvhTri {
@@ -78,7 +85,7 @@ struct DevCounters {  // mirrors rt_counters
 
 // Everything a traversal / shading kernel needs, passed by value.
 struct SceneView {
-    const uint4* nodes;        // Node8 as 5 x uint4
+    const uint4* nodes;        // Node8 as 8 x uint4
     const float4* tris;        // BvhTri as 3 x float4
     const DevObject* objects;
     const DevLight* lights;

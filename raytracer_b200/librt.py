@@ -23,6 +23,7 @@ RT_FLAG_DIRECT_LIGHTING, RT_FLAG_MIS, RT_FLAG_COUNTERS = 1, 2, 4
 RT_FLAG_DEFAULT = 7
 RT_PIPELINE_WAVEFRONT, RT_PIPELINE_MEGAKERNEL = 0, 1
 RT_RESTIR_TEMPORAL, RT_RESTIR_SPATIAL = 1, 2
+NODE_BYTES, TRI_BYTES = 128, 48  # Node8 / BvhTri records of rt_get_bvh
 
 # every entry point include/rt_api.h declares (checked against the header and `nm -D` by the tests)
 EXPORTS = (
@@ -339,7 +340,7 @@ class Context:
 
     def get_bvh(self):
         info = self.scene_info()
-        nodes = np.zeros((info.n_nodes, 80), np.uint8)
+        nodes = np.zeros((info.n_nodes, NODE_BYTES), np.uint8)
         tris = np.zeros((info.n_triangles, 48), np.uint8)
         keys = np.zeros(info.n_triangles, np.uint64)
         ids = np.zeros(info.n_triangles, np.uint32)
