@@ -291,10 +291,27 @@ __device__ __forceinline__ uint32_t warp_fetch(WarpFetch& wfetch, uint32_t* curs
     return idx;
 }
 
+// First bounce: every slot is live and there is no queue, so the i-th ray is chosen here.  Consecutive rays
+// are the pixels of a 4-wide x 8-tall screen tile rather than of a 32 x 1 row segment: the rays of a warp
+// then share more of their path through the BVH (measured: -4 % extend time).  Rows that do not fill a band
+// of 8 keep the linear order.
+#define RT_TILE_W 4u
+#define RT_TILE_H (32u / RT_TILE_W)
+__device__ __forceinline__ uint32_t primary_slot(uint32_t i, uint32_t width, uint32_t n_px) {
+    const uint32_t lane_f = i / n_px, r = i - lane_f * n_px;
+    const uint32_t band_px = width * RT_TILE_H;
+    const uint32_t band = r / band_px, b = r - band * band_px;
+    const uint32_t wt = (width / RT_TILE_W) * 32u;  // pixels of the band covered by whole tiles
+    if ((band + 1u) * band_px > n_px || b >= wt) return i;
+    const uint32_t tile = b >> 5, t = b & 31u;
+    const uint32_t x = tile * RT_TILE_W + (t % RT_TILE_W), y = band * RT_TILE_H + (t / RT_TILE_W);
+    return lane_f * n_px + y * width + x;
+}
+
 // extend: closest hit for every queued path (traceRayEXT of simple.rgen:92-104).
 template <bool COUNT>
 __global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_extend_kernel(SceneView sc, WfView wf, const uint32_t* queue, uint32_t q_idx,
-                                                        DevCounters* counters) {
+                                                        uint32_t width, uint32_t n_px, DevCounters* counters) {
     const uint32_t n = wf.ctrl[q_idx];
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     WarpFetch wfetch;
@@ -307,7 +324,7 @@ __global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_extend_kernel(Scen
     for (;;) {
         const uint32_t i = warp_fetch(wfetch, &wf.ctrl[CT_CUR_EXT], n, !has_ray);
         if (i != 0xFFFFFFFFu) {
-            slot = queue ? queue[i] : i;
+            slot = queue ? queue[i] : primary_slot(i, width, n_px);
             const float4 o = wf.ray_o[slot], d = wf.ray_d[slot];
             trav_init(st, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, 10000.0f, 0xFFFFFFFFu);
             has_ray = true;
@@ -527,7 +544,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, q_in, depth == 0 ? n_slots : 0xFFFFFFFFu);
         const uint32_t* qi = depth == 0 ? nullptr : w->queue[q_in].p;
         pf.begin(RT_K_EXTEND, stream);
-        wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, res.counters);
+        wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, fp.width, n_px, res.counters);
         pf.end(stream);
         pf.begin(RT_K_SHADE, stream);
         wf_shade_kernel<COUNT><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
