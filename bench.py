@@ -135,7 +135,7 @@ def run_reference(args):
         return
     W, H = args.width, args.height
     scene, cam = make_scene(args.scene, W, H)
-    rows = args.cpu_rows or min(H, 216)  # a fifth of the frame per step keeps K=16 steps within minutes
+    rows = args.cpu_rows or H  # one whole frame per step (~0.5 s on 16 cores): K = 16 steps stay well within minutes
     for _ in range(min(args.warmup, 1)):
         cpu_sample(scene, cam, W, H, args.max_depth, min(rows, 32))
     tot_rays, tot_s = 0, 0.0
@@ -198,7 +198,7 @@ def run_ours(args):
     scene, cam = make_scene(args.scene, W, H)
     pipe = librt.RT_PIPELINE_WAVEFRONT if args.pipeline == "wavefront" else librt.RT_PIPELINE_MEGAKERNEL
     kw = dict(device=local_rank, max_depth=args.max_depth, rr_start_depth=3, pipeline=pipe, strip_rows=8, strip_index=rank,
-              strip_count=world)
+              strip_count=world, frames_in_flight=min(max(B, 1), 32))
     ctx = librt.Context(counters=False, **kw)
     info = ctx.build_scene(scene)
     ctx.resize(W, H)
@@ -256,8 +256,14 @@ def run_ours(args):
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = alg_bytes / (ext["ms"] * 1e-3) / 1e9 if ext["ms"] > 0 else 0.0
         total_k = sum(v["ms"] for v in kprof.values())
+        traffic = None
+        try:  # dram__bytes_read+write per ray of the last committed `ncu --set full` capture of this kernel
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_kernel"]
+            traffic = tj["dram_bytes_per_ray"] * cnt["extend_rays"] / max(ext["launches"], 1)
+        except Exception:
+            pass
         roof = {"bound": "hbm", "kernel": "wf_extend_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": "measured" if "hbm_gbs" in peaks else "fallback",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": "measured" if "hbm_gbs" in peaks else "fallback",
                 "launches": ext["launches"], "avg_launch_ms": ext["ms"] / max(ext["launches"], 1),
                 "alg_bytes_per_launch": alg_bytes / max(ext["launches"], 1),
                 "bytes_per_extend_ray": alg_bytes / max(cnt["extend_rays"], 1),
@@ -268,27 +274,20 @@ def run_ours(args):
     host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
     gather = None
     if dist is not None:
+        from raytracer_b200 import multi_gpu
+
         ptr, rows = ctx.device_image()
-        rows_all = [0] * world
-        dist.all_gather_object(rows_all, rows)
-        max_rows = max(rows_all)
-        mine = torch.zeros((max_rows, W, 4), dtype=torch.float32, device="cuda")
-        view = torch.as_tensor(_DevArray(ptr, (rows, W, 4)), device="cuda") if rows else None
-        glist = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
-        stage = torch.empty((world, max_rows, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
-        row_maps = []
-        for r in range(world):
-            ys = [y for y in range(H) if (y // 8) % world == r]
-            row_maps.append(np.asarray(ys, np.int64))
+        view = torch.as_tensor(_DevArray(ptr, (rows, W, 4)), device="cuda") if rows else torch.empty((0, W, 4), device="cuda")
+        sg = multi_gpu.StripGather(dist, H, W, 4, 8, device="cuda")
+        stage = torch.empty((world, sg.max_rows, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
+        row_maps = [multi_gpu.strip_rows_of(r, world, H, 8) for r in range(world)]
 
         def gather():
             ctx.synchronize()
-            if view is not None:
-                mine[:rows].copy_(view)
-            dist.gather(mine, glist, dst=0)
+            parts = sg.gather(view)
             if rank == 0:
                 for r in range(world):
-                    stage[r].copy_(glist[r], non_blocking=True)
+                    stage[r].copy_(parts[r], non_blocking=True)
                 torch.cuda.synchronize()
                 sn = stage.numpy()
                 for r in range(world):
@@ -316,11 +315,13 @@ def run_ours(args):
     # ---- CPU baseline (rank 0, N = 1 only) --------------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        _, dt, _, _, _ = cpu_sample(scene, cam, W, H, args.max_depth, 16)
-        rows = args.cpu_rows or int(max(16, min(H, 16 * 12.0 / max(dt, 1e-3))))
-        v, dt, rays, threads, band = cpu_sample(scene, cam, W, H, args.max_depth, rows)
+        # bounded sample: whole frames 1..n of the same workload, n sized for ~15 s of CPU work
+        _, dt, _, _, _ = cpu_sample(scene, cam, W, H, args.max_depth, args.cpu_rows or H)
+        n = int(max(1, min(64, round(15.0 / max(dt, 1e-3)))))
+        v, dt, rays, threads, band = cpu_sample(scene, cam, W, H, args.max_depth, args.cpu_rows or H, frames=tuple(range(1, n + 1)))
         cpu = {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
-               "sample": f"rows {band[0]}..{band[1]} x {W} px of frame 1, {rays} rays in {dt:.2f} s (oracle/, OpenMP)"}
+               "sample": f"frames 1..{n}, rows {band[0]}..{band[1]} x {W} px, {rays} rays in {dt:.2f} s "
+                         f"(oracle/ CPU restatement, OpenMP; the reference has no CPU path)"}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
