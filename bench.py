@@ -279,19 +279,14 @@ def run_ours(args):
         ptr, rows = ctx.device_image()
         view = torch.as_tensor(_DevArray(ptr, (rows, W, 4)), device="cuda") if rows else torch.empty((0, W, 4), device="cuda")
         sg = multi_gpu.StripGather(dist, H, W, 4, 8, device="cuda")
-        stage = torch.empty((world, sg.max_rows, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
-        row_maps = [multi_gpu.strip_rows_of(r, world, H, 8) for r in range(world)]
+        host_t = torch.from_numpy(host)
 
         def gather():
             ctx.synchronize()
             parts = sg.gather(view)
             if rank == 0:
-                for r in range(world):
-                    stage[r].copy_(parts[r], non_blocking=True)
+                host_t.copy_(sg.assemble_device(parts), non_blocking=True)  # one D2H of the assembled frame
                 torch.cuda.synchronize()
-                sn = stage.numpy()
-                for r in range(world):
-                    host[row_maps[r]] = sn[r, :len(row_maps[r])]
 
     def e2e_step(s):
         ctx.trace_frames(np.array(ubo, copy=True), CLEAR, f0 + s * B, B)  # camera UBO + clear colour from host memory

@@ -64,5 +64,17 @@ class StripGather:
         self.dist.gather(self.send, self.recv, dst=0)
         return self.recv
 
+    def assemble_device(self, parts):
+        """Full (H, W, C) image on rank 0's device from the gathered parts (one scatter per rank, no host pass)."""
+        torch = self.torch
+        if getattr(self, "_full", None) is None:
+            self._full = torch.empty((self.height,) + tuple(self.send.shape[1:]), dtype=self.send.dtype, device=self.send.device)
+            self._row_idx = [torch.as_tensor(strip_rows_of(r, self.world, self.height, self.strip_rows), device=self.send.device)
+                             for r in range(self.world)]
+        for r, p in enumerate(parts):
+            if self.rows[r]:
+                self._full.index_copy_(0, self._row_idx[r], p[: self.rows[r]])
+        return self._full
+
     def assemble_host(self, parts) -> np.ndarray:
         return assemble([p[: self.rows[r]].cpu().numpy() for r, p in enumerate(parts)], self.height, self.strip_rows)

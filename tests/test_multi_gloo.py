@@ -40,7 +40,9 @@ def _worker(rank, world, port, W, H, strip, out_path):
         g = multi_gpu.StripGather(dist, H, W, 4, strip)
         parts = g.gather(local)
         if rank == 0:
-            np.save(out_path, g.assemble_host(parts))
+            a, b = g.assemble_host(parts), g.assemble_device(parts).numpy()
+            assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+            np.save(out_path, a)
     finally:
         dist.destroy_process_group()
 
