@@ -12,6 +12,8 @@ namespace orc {
 struct Cfg { int max_depth; float clamp; int use_bvh; };
 void render_rows(const Scene& s, const Cfg& cfg, const float* cam, const float* clear, uint32_t frame, uint32_t W,
                  uint32_t H, uint32_t y0, uint32_t y1, float* image_rgba, Counters* total);
+void direct_reference_rows(const Scene& s, int use_bvh, const float* cam, const float* clear, uint32_t W, uint32_t H,
+                           uint32_t y0, uint32_t y1, int spt, float* image_rgba);
 void gbuffer_rows(const Scene& s, int use_bvh, const float* cam, uint32_t W, uint32_t H, uint32_t y0, uint32_t y1,
                   uint8_t* albedo_rgba8, uint16_t* normal_rough_f16, float* position_metal_f32, uint16_t* emission_f16,
                   uint8_t* output_rgba8);
@@ -94,6 +96,13 @@ int orc_gbuffer(void* h, const float* cam64, uint32_t W, uint32_t H, uint32_t y0
     Scene* s = (Scene*)h;
     if (use_bvh && !s->has_bvh) build_bvh8(*s);
     gbuffer_rows(*s, use_bvh, cam64, W, H, y0, y1, albedo, normal_rough, position_metal, emission, output);
+    return 0;
+}
+
+int orc_direct_reference(void* h, const float* cam64, const float* clear3, uint32_t W, uint32_t H, int use_bvh, int spt, float* image_rgba) {
+    Scene* s = (Scene*)h;
+    if (use_bvh && !s->has_bvh) build_bvh8(*s);
+    direct_reference_rows(*s, use_bvh, cam64, clear3, W, H, 0, H, spt, image_rgba);
     return 0;
 }
 

@@ -609,6 +609,98 @@ void gbuffer_rows(const Scene& s, int use_bvh, const float* cam, uint32_t W, uin
 }
 
 // exported for unit tests of the BSDF pieces
+// --------------------------------------------------------------------------------------------
+// Ground truth for the ReSTIR DI path (the reference has no resampling algorithm to restate):
+// direct lighting of the primary hit of restir.rgen's un-jittered corner ray, integrated by brute force —
+// every triangle of every light, `spt` x `spt` stratified points each, one occlusion test per point
+// (brute force or BVH, the same contract as isVisibleRQ).  Output: linear RGB, alpha 1; emissive
+// surfaces add their own emission, misses return the clear colour.  No clamp.
+// --------------------------------------------------------------------------------------------
+void direct_reference_rows(const Scene& s, int use_bvh, const float* cam, const float* clear, uint32_t W, uint32_t H,
+                           uint32_t y0, uint32_t y1, int spt, float* image_rgba) {
+    const float* iv = cam + 32;
+    const float* ip = cam + 48;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int y = (int)y0; y < (int)y1; y++) {
+        for (uint32_t x = 0; x < W; x++) {
+            float ux = (float)x / (float)W, uy = (float)y / (float)H;
+            float dx = ux * 2.0f - 1.0f, dy = uy * 2.0f - 1.0f;
+            V3 origin = v3(iv[12], iv[13], iv[14]);
+            V3 target = v3(((ip[0] * dx + ip[4] * dy) + ip[8]) + ip[12], ((ip[1] * dx + ip[5] * dy) + ip[9]) + ip[13],
+                           ((ip[2] * dx + ip[6] * dy) + ip[10]) + ip[14]);
+            V3 dir = xform_dir(iv, normalize(target));
+            Hit h = use_bvh ? closest_bvh(s, origin, dir, 0.001f, 10000.0f, nullptr) : closest_brute(s, origin, dir, 0.001f, 10000.0f);
+            float* px = image_rgba + 4 * ((size_t)y * W + x);
+            px[3] = 1.0f;
+            if (h.id == 0xFFFFFFFFu) { px[0] = clear[0]; px[1] = clear[1]; px[2] = clear[2]; continue; }
+            const FlatTri& ft = s.tris[h.id];
+            const Object& object = s.objects[ft.inst];
+            const Material& m = s.materials[object.material_index];
+            const Mesh& mesh = s.meshes[object.mesh_index];
+            const Vertex& v0 = mesh.v[mesh.idx[3 * ft.prim]];
+            const Vertex& v1 = mesh.v[mesh.idx[3 * ft.prim + 1]];
+            const Vertex& v2 = mesh.v[mesh.idx[3 * ft.prim + 2]];
+            const float bx = (1.0f - h.u) - h.v, by = h.u, bz = h.v;
+            V3 worldPos = xform_point(object.model, (vpos(v0) * bx + vpos(v1) * by) + vpos(v2) * bz);
+            V3 N = normalize(mul_nm(object.nrm, normalize((vnrm(v0) * bx + vnrm(v1) * by) + vnrm(v2) * bz)));
+            V3 wo_w = neg(normalize(dir));
+            if (!(dot(N, wo_w) > 0.0f)) N = neg(N);
+            Basis basis = createBasis(N);
+            V3 wo = worldToLocal(wo_w, basis);
+            double acc[3] = {0, 0, 0};
+            for (size_t li = 0; li < s.lights.size(); li++) {
+                const Light& L = s.lights[li];
+                if (L.object_index == ft.inst) continue;
+                const Object& lo = s.objects[L.object_index];
+                const Material& lm = s.materials[lo.material_index];
+                const Mesh& lmesh = s.meshes[lo.mesh_index];
+                V3 Le = v3(lm.emission_color[0], lm.emission_color[1], lm.emission_color[2]) * lm.emission_power;
+                for (uint32_t t = 0; t < L.num_triangles; t++) {
+                    V3 w0 = xform_point(L.transform, vpos(lmesh.v[lmesh.idx[3 * t]]));
+                    V3 w1 = xform_point(L.transform, vpos(lmesh.v[lmesh.idx[3 * t + 1]]));
+                    V3 w2 = xform_point(L.transform, vpos(lmesh.v[lmesh.idx[3 * t + 2]]));
+                    V3 cr = cross(w1 - w0, w2 - w0);
+                    float area = 0.5f * length(cr);
+                    if (!(area > 0.0f)) continue;
+                    V3 ln = normalize(cr);
+                    for (int a = 0; a < spt; a++)
+                        for (int b = 0; b < spt; b++) {
+                            float r1 = ((float)a + 0.5f) / (float)spt, r2 = ((float)b + 0.5f) / (float)spt;
+                            float sq = sqrtf(r1);
+                            float bu = 1.0f - sq, bv = sq * (1.0f - r2), bw = sq * r2;
+                            V3 yp = (w0 * bu + w1 * bv) + w2 * bw;
+                            V3 to = yp - worldPos;
+                            float d2 = dot(to, to);
+                            if (!(d2 > 1e-12f)) continue;
+                            float d = sqrtf(d2);
+                            V3 wi_w = to / d;
+                            float cos_y = fabsf(dot(ln, wi_w));
+                            V3 wi = worldToLocal(wi_w, basis);
+                            if (!(wi.z > 1e-4f) || !(cos_y > 1e-6f)) continue;
+                            // visibility exactly as isVisibleRQ sets the ray up (simple.rchit:350-371)
+                            V3 from = worldPos + (N * 0.001f) * signf(dot(N, normalize(yp - worldPos)));
+                            V3 sdir = yp - from;
+                            float sdist = length(sdir);
+                            if (!(sdist > 0.0f)) continue;
+                            sdir = sdir / sdist;
+                            bool occ = use_bvh ? occluded_bvh(s, from, sdir, 0.001f, sdist * 0.999f, L.object_index, nullptr)
+                                               : occluded_brute(s, from, sdir, 0.001f, sdist * 0.999f, L.object_index);
+                            if (occ) continue;
+                            V3 f = evaluateFullBRDF(wo, wi, m);
+                            float g = (wi.z * cos_y) / d2 * (area / (float)(spt * spt));
+                            acc[0] += (double)(f.x * Le.x * g); acc[1] += (double)(f.y * Le.y * g); acc[2] += (double)(f.z * Le.z * g);
+                        }
+                }
+            }
+            if (m.emission_power > 0.0f) {
+                acc[0] += m.emission_color[0] * m.emission_power; acc[1] += m.emission_color[1] * m.emission_power;
+                acc[2] += m.emission_color[2] * m.emission_power;
+            }
+            px[0] = (float)acc[0]; px[1] = (float)acc[1]; px[2] = (float)acc[2];
+        }
+    }
+}
+
 void unit_sample_brdf(const Material& m, V3 wo, float rx, float ry, uint32_t* seed, float out[8]) {
     BSDFSample b = sampleBRDF(wo, m, rx, ry, *seed);
     out[0] = b.direction.x; out[1] = b.direction.y; out[2] = b.direction.z;

@@ -194,10 +194,11 @@ static int rebuild_bvh(rt_ctx* ctx) {
     return RT_OK;
 }
 
-static int flush_scene(rt_ctx* ctx) {
+int rt_flush_scene(rt_ctx* ctx) {
     if (!ctx->has_scene) { set_error("no scene: call rt_build_scene first"); return RT_ERR_NO_SCENE; }
     if (ctx->tables_dirty || ctx->geometry_dirty) {
         const bool geo = ctx->geometry_dirty;
+        ctx->rs_history = false;  // reservoirs refer to the old light tables
         int rc = upload_tables(ctx);
         if (rc != RT_OK) return rc;
         if (geo) { rc = rebuild_bvh(ctx); if (rc != RT_OK) return rc; }
@@ -205,7 +206,7 @@ static int flush_scene(rt_ctx* ctx) {
     return RT_OK;
 }
 
-static SceneView scene_view(const rt_ctx* ctx) {
+SceneView rt_scene_view(const rt_ctx* ctx) {
     SceneView sc;
     sc.nodes = ctx->bvh.nodes.p;
     sc.tris = ctx->bvh.tris.p;
@@ -275,13 +276,13 @@ int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const 
     ctx->has_scene = true;
     ctx->tables_dirty = true;
     ctx->geometry_dirty = true;
-    return flush_scene(ctx);
+    return rt_flush_scene(ctx);
 }
 
 int rt_scene_info_get(rt_ctx* ctx, rt_scene_info* out) {
     CTX_CHECK(ctx);
     if (!out) return RT_ERR_INVALID_ARGUMENT;
-    const int rc = flush_scene(ctx);
+    const int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     memset(out, 0, sizeof(*out));
     out->n_triangles = ctx->n_tris;
@@ -360,7 +361,7 @@ static uint32_t count_local_rows(const rt_config& c, uint32_t height) {
     return n;
 }
 
-static void fill_frame_params(const rt_ctx* ctx, const float* cam, const float* clear, uint32_t frame, FrameParams* fp) {
+void rt_fill_frame_params(const rt_ctx* ctx, const float* cam, const float* clear, uint32_t frame, FrameParams* fp) {
     memcpy(fp->inv_view, cam + 32, 64);  // Camera_UBO: proj, view, inverse_view, inverse_proj (camera.odin:15-20)
     memcpy(fp->inv_proj, cam + 48, 64);
     if (clear) memcpy(fp->clear, clear, 12); else fp->clear[0] = fp->clear[1] = fp->clear[2] = 0.0f;
@@ -378,13 +379,13 @@ static void fill_frame_params(const rt_ctx* ctx, const float* cam, const float* 
     fp->flags = ctx->cfg.flags;
 }
 
-static int require_target(rt_ctx* ctx) {
+int rt_require_target(rt_ctx* ctx) {
     if (ctx->width == 0 || ctx->height == 0) { set_error("no target: call rt_resize first"); return RT_ERR_NO_TARGET; }
     return RT_OK;
 }
 
-static void begin_timing(rt_ctx* ctx) { cudaEventRecord(ctx->ev0, ctx->stream); }
-static void end_timing(rt_ctx* ctx) {
+void rt_begin_timing(rt_ctx* ctx) { cudaEventRecord(ctx->ev0, ctx->stream); }
+void rt_end_timing(rt_ctx* ctx) {
     cudaEventRecord(ctx->ev1, ctx->stream);
     ctx->timing_pending = true;
 }
@@ -407,6 +408,8 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     RT_CUDA_TRY(cudaMemsetAsync(ctx->image.p, 0, std::max<size_t>(n, 1) * sizeof(float4), ctx->stream));
     ctx->srgb.release();
     ctx->has_gbuffer = false;
+    ctx->rs_history = false;
+    ctx->rs_surf.release(); ctx->rs_cur.release(); ctx->rs_hist[0].release(); ctx->rs_hist[1].release();
     if (ctx->wf) { wavefront_free(ctx->wf); ctx->wf = nullptr; }
     if (ctx->cfg.pipeline == RT_PIPELINE_WAVEFRONT) {
         std::string err;
@@ -426,11 +429,11 @@ int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
                     uint32_t n_frames) {
     CTX_CHECK(ctx);
     if (!camera_ubo || !clear_color) { set_error("rt_trace_frame: null argument"); return RT_ERR_INVALID_ARGUMENT; }
-    int rc = flush_scene(ctx);
+    int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
-    rc = require_target(ctx);
+    rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
-    const SceneView sc = scene_view(ctx);
+    const SceneView sc = rt_scene_view(ctx);
     FrameResources res;
     res.image = ctx->image.p;
     res.counters = ctx->counters.p;
@@ -438,18 +441,18 @@ int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     res.prof = &ctx->prof;
     res.launches = &ctx->launches;
     std::string err;
-    begin_timing(ctx);
+    rt_begin_timing(ctx);
     const bool mega = ctx->cfg.pipeline == RT_PIPELINE_MEGAKERNEL;
     for (uint32_t f = 0; f < n_frames;) {
         FrameParams fp;
-        fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f, &fp);
+        rt_fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f, &fp);
         fp.n_lanes = mega ? 1u : std::min(ctx->lanes, n_frames - f);
         rc = mega ? launch_frame_megakernel(sc, fp, res, ctx->stream, err) : launch_frame_wavefront(sc, fp, res, ctx->stream, err);
         if (rc != RT_OK) { set_error(err); return rc; }
         f += fp.n_lanes;
     }
     ctx->frames_traced += n_frames;
-    end_timing(ctx);
+    rt_end_timing(ctx);
     return RT_OK;
 }
 
@@ -497,14 +500,14 @@ static int scatter_rows_to_host(rt_ctx* ctx, const void* d_src, void* dst, size_
 
 int rt_readback(rt_ctx* ctx, float* dst, size_t bytes) {
     CTX_CHECK(ctx);
-    const int rc = require_target(ctx);
+    const int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     return scatter_rows_to_host(ctx, ctx->image.p, dst, bytes, sizeof(float4));
 }
 
 int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst, size_t bytes) {
     CTX_CHECK(ctx);
-    int rc = require_target(ctx);
+    int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     const size_t n = (size_t)ctx->local_rows * ctx->width;
     RT_CUDA_TRY(ctx->srgb.ensure(n));
@@ -516,7 +519,7 @@ int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst, size_t bytes) {
 
 int rt_device_image(rt_ctx* ctx, void** device_ptr, uint32_t* local_rows) {
     CTX_CHECK(ctx);
-    const int rc = require_target(ctx);
+    const int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     if (device_ptr) *device_ptr = ctx->image.p;
     if (local_rows) *local_rows = ctx->local_rows;
@@ -525,7 +528,7 @@ int rt_device_image(rt_ctx* ctx, void** device_ptr, uint32_t* local_rows) {
 
 int rt_upload_accum(rt_ctx* ctx, const float* src, size_t bytes) {
     CTX_CHECK(ctx);
-    const int rc = require_target(ctx);
+    const int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     const size_t row = (size_t)ctx->width * sizeof(float4);
     if (!src || bytes < row * ctx->height) { set_error("rt_upload_accum: source too small"); return RT_ERR_INVALID_ARGUMENT; }
@@ -544,9 +547,9 @@ int rt_upload_accum(rt_ctx* ctx, const float* src, size_t bytes) {
 int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]) {
     CTX_CHECK(ctx);
     if (!camera_ubo) return RT_ERR_INVALID_ARGUMENT;
-    int rc = flush_scene(ctx);
+    int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
-    rc = require_target(ctx);
+    rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     const size_t n = (size_t)ctx->local_rows * ctx->width;
     RT_CUDA_TRY(ctx->g_albedo.ensure(n));
@@ -555,14 +558,14 @@ int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]) {
     RT_CUDA_TRY(ctx->g_emission.ensure(n));
     RT_CUDA_TRY(ctx->g_position.ensure(n));
     FrameParams fp;
-    fill_frame_params(ctx, camera_ubo, nullptr, 0, &fp);
+    rt_fill_frame_params(ctx, camera_ubo, nullptr, 0, &fp);
     GBufferImages g;
     g.albedo = ctx->g_albedo.p; g.output = ctx->g_output.p; g.normal_rough = ctx->g_normal.p;
     g.emission = ctx->g_emission.p; g.position_metal = ctx->g_position.p;
     std::string err;
-    begin_timing(ctx);
-    rc = launch_gbuffer(scene_view(ctx), fp, g, (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->stream, err);
-    end_timing(ctx);
+    rt_begin_timing(ctx);
+    rc = launch_gbuffer(rt_scene_view(ctx), fp, g, (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->stream, err);
+    rt_end_timing(ctx);
     if (rc != RT_OK) { set_error(err); return rc; }
     ctx->has_gbuffer = true;
     return RT_OK;
@@ -644,7 +647,7 @@ int rt_get_kernel_profile(rt_ctx* ctx, rt_kernel_profile* out) {
 // ---- verification hooks ----------------------------------------------------------------------------
 static int trace_rays_common(rt_ctx* ctx, const float* rays, uint32_t n, bool any, const uint32_t* ignore, float* out_tuv,
                              uint32_t* out_id) {
-    int rc = flush_scene(ctx);
+    int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     if (n == 0) return RT_OK;
     if (!rays || !out_id || (!any && !out_tuv)) { set_error("rt_trace_rays: null argument"); return RT_ERR_INVALID_ARGUMENT; }
@@ -659,7 +662,7 @@ static int trace_rays_common(rt_ctx* ctx, const float* rays, uint32_t n, bool an
         RT_CUDA_TRY(cudaMemcpyAsync(d_ig.p, ignore, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
     }
     std::string err;
-    rc = launch_trace_rays(scene_view(ctx), d_rays.p, n, any, (any && ignore) ? d_ig.p : nullptr, d_tuv.p, d_id.p,
+    rc = launch_trace_rays(rt_scene_view(ctx), d_rays.p, n, any, (any && ignore) ? d_ig.p : nullptr, d_tuv.p, d_id.p,
                            (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->stream, err);
     if (rc != RT_OK) { set_error(err); return rc; }
     RT_CUDA_TRY(cudaMemcpyAsync(out_id, d_id.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -681,7 +684,7 @@ int rt_trace_rays_any(rt_ctx* ctx, const float* rays, uint32_t n, const uint32_t
 int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t tris_bytes, uint64_t* morton,
                uint32_t* sorted_ids) {
     CTX_CHECK(ctx);
-    const int rc = flush_scene(ctx);
+    const int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     const size_t nb = (size_t)ctx->bvh.n_nodes * sizeof(Node8), tb = (size_t)ctx->n_tris * 48;
     if ((nodes && nodes_bytes < nb) || (tris && tris_bytes < tb)) { set_error("rt_get_bvh: buffer too small"); return RT_ERR_INVALID_ARGUMENT; }

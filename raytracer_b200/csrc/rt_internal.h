@@ -157,6 +157,12 @@ struct rt_ctx {
     rt::DevBuf<ushort4> g_normal, g_emission;
     rt::DevBuf<float4> g_position;
     bool has_gbuffer = false;
+    // ReSTIR DI (rt_restir.cu): primary surfaces, this frame's reservoirs, the history
+    rt::DevBuf<float4> rs_surf;
+    rt::DevBuf<rt_reservoir> rs_cur, rs_hist[2];
+    int rs_flip = 0;
+    bool rs_history = false;   // rs_hist[rs_flip] holds last frame's reservoirs for rs_cam
+    float rs_cam[64] = {0};
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t user_ev[2] = {nullptr, nullptr};
@@ -168,4 +174,12 @@ struct rt_ctx {
 
     void set_error(const std::string& s) { error = s; }
 };
+
+// shared by the translation units behind the C ABI (rt_api.cu)
+int rt_flush_scene(rt_ctx* ctx);
+int rt_require_target(rt_ctx* ctx);
+rt::SceneView rt_scene_view(const rt_ctx* ctx);
+void rt_fill_frame_params(const rt_ctx* ctx, const float* cam, const float* clear, uint32_t frame, rt::FrameParams* fp);
+void rt_begin_timing(rt_ctx* ctx);
+void rt_end_timing(rt_ctx* ctx);
 
