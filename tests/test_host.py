@@ -107,3 +107,31 @@ def test_strip_partition_is_a_partition(world, height, strip):
     img = multi_gpu.assemble(parts, height, strip)
     for k, r in enumerate(rows):
         assert (img[r] == k).all()
+
+
+def test_png_round_trip_and_ssim_restatement(tmp_path):
+    """image_io.ssim restates skimage's structural_similarity(channel_axis=2) (ssim_compare.py:20); checked here
+    against a direct windowed evaluation of the same formula."""
+    from raytracer_b200.image_io import read_png, ssim, write_pfm, write_png
+
+    rng = np.random.default_rng(0)
+    a = (rng.random((24, 31, 3)) * 255).astype(np.uint8)
+    b = a.copy()
+    b[5:15, 8:20] = (b[5:15, 8:20].astype(np.int32) * 2 // 3).astype(np.uint8)
+    p = str(tmp_path / "a.png")
+    write_png(p, a)
+    assert np.array_equal(read_png(p), a)
+    write_pfm(str(tmp_path / "a.pfm"), a.astype(np.float32) / 255)
+    assert ssim(a, a) == 1.0
+    c1, c2, acc = (0.01 * 255) ** 2, (0.03 * 255) ** 2, []
+    for ch in range(3):
+        x, y = a[..., ch].astype(np.float64), b[..., ch].astype(np.float64)
+        for i in range(3, 24 - 3):
+            for j in range(3, 31 - 3):
+                wx, wy = x[i - 3:i + 4, j - 3:j + 4].ravel(), y[i - 3:i + 4, j - 3:j + 4].ravel()
+                ux, uy = wx.mean(), wy.mean()
+                vx, vy = wx.var(ddof=1), wy.var(ddof=1)
+                vxy = ((wx - ux) * (wy - uy)).sum() / 48.0
+                acc.append(((2 * ux * uy + c1) * (2 * vxy + c2)) / ((ux * ux + uy * uy + c1) * (vx + vy + c2)))
+    assert abs(ssim(a, b) - float(np.mean(acc))) < 1e-9
+    assert 0.5 < ssim(a, b) < 1.0
