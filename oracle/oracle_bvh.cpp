@@ -64,36 +64,45 @@ int scene_finalize(Scene& s) {
 // --------------------------------------------------------------------------------------------
 // watertight ray/triangle test (Woop, Benthin, Wald 2013), evaluation order per DESIGN.md §3
 // --------------------------------------------------------------------------------------------
+// The shear of Woop et al. is applied as an affine map so that no component has to be picked per triangle:
+//   x' = mx . p - cx,  y' = my . p - cy   with   mx = e_kx - Sx e_kz,  my = e_ky - Sy e_kz,  c* = m* . o.
+// Every dot product is the chain fmaf(p.z, m.z, fmaf(p.y, m.y, fmaf(p.x, m.x, -c))) (c itself:
+// fmaf(o.z, m.z, fmaf(o.y, m.y, o.x * m.x))); entries that are exactly 0 or 1 contribute exactly.
 struct RaySetup {
-    V3 o;
-    int kx, ky, kz;
-    float Sx, Sy, Sz;
+    float mx[3], my[3];
+    float cx, cy;
+    int kz;
+    float o_kz, inv_d_kz;  // origin and 1/d along the dominant axis (1/d exactly as the slab test's idir)
 };
 static inline float comp(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+static inline float chain(const float m[3], V3 p, float c) { return fmaf(p.z, m[2], fmaf(p.y, m[1], fmaf(p.x, m[0], -c))); }
+static inline float chain0(const float m[3], V3 p) { return fmaf(p.z, m[2], fmaf(p.y, m[1], p.x * m[0])); }
 
 static inline RaySetup ray_setup(V3 o, V3 d) {
     RaySetup r;
-    r.o = o;
     float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-    r.kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
-    r.kx = r.kz + 1; if (r.kx == 3) r.kx = 0;
-    r.ky = r.kx + 1; if (r.ky == 3) r.ky = 0;
+    int kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
+    int kx = kz + 1; if (kx == 3) kx = 0;
+    int ky = kx + 1; if (ky == 3) ky = 0;
     // Woop et al. swap kx and ky here when d[kz] < 0 to keep the winding for back-face culling.  Nothing is
     // culled on this path (simple.rgen:92-104 traces with gl_RayFlagsOpaqueEXT only), and the swap merely
     // negates U, V, W, det and T together, so it is left out (it could only flip the sign of a zero u or v).
-    float dz = comp(d, r.kz);
-    r.Sx = comp(d, r.kx) / dz;
-    r.Sy = comp(d, r.ky) / dz;
-    r.Sz = 1.0f / dz;
+    float dz = comp(d, kz);
+    for (int i = 0; i < 3; i++) r.mx[i] = r.my[i] = 0.0f;
+    r.mx[kx] = 1.0f; r.mx[kz] = -(comp(d, kx) / dz);
+    r.my[ky] = 1.0f; r.my[kz] = -(comp(d, ky) / dz);
+    r.kz = kz;
+    r.o_kz = comp(o, kz);
+    r.inv_d_kz = (fabsf(dz) >= 1e-20f) ? 1.0f / dz : copysignf(1e20f, dz);
+    r.cx = chain0(r.mx, o);
+    r.cy = chain0(r.my, o);
     return r;
 }
 
 static inline bool tri_isect(const RaySetup& r, V3 p0, V3 p1, V3 p2, float* t, float* u, float* v) {
-    V3 A = p0 - r.o, B = p1 - r.o, C = p2 - r.o;
-    float Akz = comp(A, r.kz), Bkz = comp(B, r.kz), Ckz = comp(C, r.kz);
-    float Ax = fmaf(-r.Sx, Akz, comp(A, r.kx)), Ay = fmaf(-r.Sy, Akz, comp(A, r.ky));
-    float Bx = fmaf(-r.Sx, Bkz, comp(B, r.kx)), By = fmaf(-r.Sy, Bkz, comp(B, r.ky));
-    float Cx = fmaf(-r.Sx, Ckz, comp(C, r.kx)), Cy = fmaf(-r.Sy, Ckz, comp(C, r.ky));
+    float Ax = chain(r.mx, p0, r.cx), Ay = chain(r.my, p0, r.cy);
+    float Bx = chain(r.mx, p1, r.cx), By = chain(r.my, p1, r.cy);
+    float Cx = chain(r.mx, p2, r.cx), Cy = chain(r.my, p2, r.cy);
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -105,10 +114,11 @@ static inline bool tri_isect(const RaySetup& r, V3 p0, V3 p1, V3 p2, float* t, f
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
     float det = (U + V) + W;
     if (det == 0.0f) return false;
-    float Az = r.Sz * Akz, Bz = r.Sz * Bkz, Cz = r.Sz * Ckz;
-    float T = (U * Az + V * Bz) + W * Cz;
+    // distance from the hit point's coordinate along the dominant axis: t = (p_kz - o_kz) / d_kz
+    float Az = comp(p0, r.kz), Bz = comp(p1, r.kz), Cz = comp(p2, r.kz);
+    float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
     float inv = 1.0f / det;
-    *t = T * inv;
+    *t = (T * inv - r.o_kz) * r.inv_d_kz;
     *u = V * inv;
     *v = W * inv;
     return true;

@@ -19,15 +19,13 @@ namespace rt {
 struct TravRay {
     float ox, oy, oz;
     float idx, idy, idz;   // 1/d (clamped for |d| < 1e-20)
-    float Sx, Sy, Sz;      // watertight shear
-    uint32_t mz0, mz1;     // all-ones when the dominant axis kz is 0 / 1: drives the branch-free axis rotation
-    uint32_t rbits;        // sign bits of d: traversal octant
+    // Watertight shear as an affine map: row pairs (mx_i, my_i) for i = x, y, z with
+    // mx = e_kx - Sx e_kz, my = e_ky - Sy e_kz, and cxy = (mx . o, my . o).
+    // The entries that are exactly 0 or 1 make the fmaf chains below reproduce "pick a component" without
+    // any per-triangle selects (the selects cost 54 ALU-pipe instructions per triangle before).
+    float2 px, py, pz, cxy;
+    uint32_t rbits;        // bits 0..2: sign bits of d (traversal octant); bits 3..4: dominant axis kz
 };
-
-// bitwise select: m is all-ones or zero (one LOP3; the compiler cannot turn it into a branch)
-__device__ __forceinline__ float bsel(uint32_t m, float a, float b) {
-    return __uint_as_float((__float_as_uint(a) & m) | (__float_as_uint(b) & ~m));
-}
 
 // Woop et al. permute the axes so that kz is the dominant direction and kx, ky follow cyclically, and swap
 // kx, ky when d[kz] < 0 to keep the winding for back-face culling.  Nothing is culled on this path and the
@@ -36,51 +34,55 @@ __device__ __forceinline__ TravRay trav_setup(vec3 o, vec3 d) {
     TravRay r;
     r.ox = o.x; r.oy = o.y; r.oz = o.z;
     float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-    uint32_t kz = (ax > ay) ? ((ax > az) ? 0u : 2u) : ((ay > az) ? 1u : 2u);
-    r.mz0 = (kz == 0u) ? 0xFFFFFFFFu : 0u;
-    r.mz1 = (kz == 1u) ? 0xFFFFFFFFu : 0u;
+    const uint32_t kz = (ax > ay) ? ((ax > az) ? 0u : 2u) : ((ay > az) ? 1u : 2u);
     // rotate (x, y, z) -> (kx, ky, kz) components
-    const float dkx = bsel(r.mz0, d.y, bsel(r.mz1, d.z, d.x));
-    const float dky = bsel(r.mz0, d.z, bsel(r.mz1, d.x, d.y));
-    const float dz = bsel(r.mz0, d.x, bsel(r.mz1, d.y, d.z));
-    r.Sx = dkx / dz;
-    r.Sy = dky / dz;
-    r.Sz = 1.0f / dz;
+    const float dkx = kz == 0u ? d.y : (kz == 1u ? d.z : d.x);
+    const float dky = kz == 0u ? d.z : (kz == 1u ? d.x : d.y);
+    const float dz = kz == 0u ? d.x : (kz == 1u ? d.y : d.z);
+    const float nSx = -(dkx / dz), nSy = -(dky / dz);
+    // axis i is kx when i == (kz + 1) % 3, ky when i == (kz + 2) % 3
+    r.px = kz == 0u ? make_float2(nSx, nSy) : (kz == 1u ? make_float2(0.0f, 1.0f) : make_float2(1.0f, 0.0f));
+    r.py = kz == 0u ? make_float2(1.0f, 0.0f) : (kz == 1u ? make_float2(nSx, nSy) : make_float2(0.0f, 1.0f));
+    r.pz = kz == 0u ? make_float2(0.0f, 1.0f) : (kz == 1u ? make_float2(1.0f, 0.0f) : make_float2(nSx, nSy));
+    r.cxy.x = fmaf(o.z, r.pz.x, fmaf(o.y, r.py.x, o.x * r.px.x));
+    r.cxy.y = fmaf(o.z, r.pz.y, fmaf(o.y, r.py.y, o.x * r.px.y));
     r.idx = (fabsf(d.x) >= 1e-20f) ? 1.0f / d.x : copysignf(1e20f, d.x);
     r.idy = (fabsf(d.y) >= 1e-20f) ? 1.0f / d.y : copysignf(1e20f, d.y);
     r.idz = (fabsf(d.z) >= 1e-20f) ? 1.0f / d.z : copysignf(1e20f, d.z);
-    r.rbits = (__float_as_uint(d.x) >> 31) | ((__float_as_uint(d.y) >> 31) << 1) | ((__float_as_uint(d.z) >> 31) << 2);
+    r.rbits = (__float_as_uint(d.x) >> 31) | ((__float_as_uint(d.y) >> 31) << 1) | ((__float_as_uint(d.z) >> 31) << 2) | (kz << 3);
     return r;
+}
+
+// sheared (x, y) of a vertex: three packed FFMA2 (sm_100 fma.rn.f32x2), each half rounded exactly like fmaf
+__device__ __forceinline__ float2 shear_xy(const TravRay& r, float4 q) {
+    float2 a = __ffma2_rn(make_float2(q.x, q.x), r.px, make_float2(-r.cxy.x, -r.cxy.y));
+    a = __ffma2_rn(make_float2(q.y, q.y), r.py, a);
+    return __ffma2_rn(make_float2(q.z, q.z), r.pz, a);
 }
 
 // Watertight intersection; returns false when the ray misses the triangle's plane projection.
 __device__ __forceinline__ bool tri_isect(const TravRay& r, float4 q0, float4 q1, float4 q2, float* t, float* u,
                                           float* v) {
-    float ax = q0.x - r.ox, ay = q0.y - r.oy, az = q0.z - r.oz;
-    float bx = q1.x - r.ox, by = q1.y - r.oy, bz = q1.z - r.oz;
-    float cx = q2.x - r.ox, cy = q2.y - r.oy, cz = q2.z - r.oz;
-    const uint32_t m0 = r.mz0, m1 = r.mz1;
-    float Akz = bsel(m0, ax, bsel(m1, ay, az)), Bkz = bsel(m0, bx, bsel(m1, by, bz)), Ckz = bsel(m0, cx, bsel(m1, cy, cz));
-    float Akx = bsel(m0, ay, bsel(m1, az, ax)), Bkx = bsel(m0, by, bsel(m1, bz, bx)), Ckx = bsel(m0, cy, bsel(m1, cz, cx));
-    float Aky = bsel(m0, az, bsel(m1, ax, ay)), Bky = bsel(m0, bz, bsel(m1, bx, by)), Cky = bsel(m0, cz, bsel(m1, cx, cy));
-    float Ax = fmaf(-r.Sx, Akz, Akx), Ay = fmaf(-r.Sy, Akz, Aky);
-    float Bx = fmaf(-r.Sx, Bkz, Bkx), By = fmaf(-r.Sy, Bkz, Bky);
-    float Cx = fmaf(-r.Sx, Ckz, Ckx), Cy = fmaf(-r.Sy, Ckz, Cky);
-    float U = Cx * By - Cy * Bx;
-    float V = Ax * Cy - Ay * Cx;
-    float W = Bx * Ay - By * Ax;
+    const float2 A = shear_xy(r, q0), B = shear_xy(r, q1), C = shear_xy(r, q2);
+    float U = C.x * B.y - C.y * B.x;
+    float V = A.x * C.y - A.y * C.x;
+    float W = B.x * A.y - B.y * A.x;
     if (U == 0.0f || V == 0.0f || W == 0.0f) {  // edge case: redo the edge functions in binary64
-        U = (float)__dsub_rn(__dmul_rn((double)Cx, (double)By), __dmul_rn((double)Cy, (double)Bx));
-        V = (float)__dsub_rn(__dmul_rn((double)Ax, (double)Cy), __dmul_rn((double)Ay, (double)Cx));
-        W = (float)__dsub_rn(__dmul_rn((double)Bx, (double)Ay), __dmul_rn((double)By, (double)Ax));
+        U = (float)__dsub_rn(__dmul_rn((double)C.x, (double)B.y), __dmul_rn((double)C.y, (double)B.x));
+        V = (float)__dsub_rn(__dmul_rn((double)A.x, (double)C.y), __dmul_rn((double)A.y, (double)C.x));
+        W = (float)__dsub_rn(__dmul_rn((double)B.x, (double)A.y), __dmul_rn((double)B.y, (double)A.x));
     }
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
     float det = (U + V) + W;
     if (det == 0.0f) return false;
-    float Az = r.Sz * Akz, Bz = r.Sz * Bkz, Cz = r.Sz * Ckz;
-    float T = (U * Az + V * Bz) + W * Cz;
+    // distance: the hit point's coordinate along the dominant axis (barycentric mix of the three vertices),
+    // then t = (p_kz - o_kz) / d_kz.  Only lanes that pass the edge test get here.
+    const bool k0 = (r.rbits & 0x18u) == 0u, k1 = (r.rbits & 0x08u) != 0u;
+    const float Az = k0 ? q0.x : (k1 ? q0.y : q0.z), Bz = k0 ? q1.x : (k1 ? q1.y : q1.z), Cz = k0 ? q2.x : (k1 ? q2.y : q2.z);
+    const float okz = k0 ? r.ox : (k1 ? r.oy : r.oz), ikz = k0 ? r.idx : (k1 ? r.idy : r.idz);
+    float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
     float inv = 1.0f / det;
-    *t = T * inv;
+    *t = (T * inv - okz) * ikz;
     *u = V * inv;
     *v = W * inv;
     return true;
@@ -107,7 +109,7 @@ __device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, co
     const float2 orx2 = make_float2(orx, orx), ory2 = make_float2(ory, ory), orz2 = make_float2(orz, orz);
     // meta bytes, four children at a time: internal children (24..31 in the low five bits) get their slot
     // XORed with the ray octant; empty children (meta 0) carry no bits and drop out without a test
-    const uint32_t oct4 = r.rbits * 0x01010101u;
+    const uint32_t oct4 = (r.rbits & 7u) * 0x01010101u;
     uint32_t mask = 0;
 #pragma unroll
     for (int half = 0; half < 2; half++) {
@@ -173,13 +175,13 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
     uint2 ng = st.ng;
     const int bit = 31 - __clz(ng.y);
     ng.y &= ~(1u << bit);
-    const uint32_t slot = ((uint32_t)bit - 24u) ^ r.rbits;
+    const uint32_t slot = ((uint32_t)bit - 24u) ^ (r.rbits & 7u);
     const uint32_t rel = __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
     const uint32_t node = ng.x + rel;
     if (ng.y & 0xFF000000u) stk.e[st.sp++] = ng;
     const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
     // near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one
-    const uint32_t sx = r.rbits & 1u, sy = (r.rbits >> 1) & 1u, sz = r.rbits >> 2;
+    const uint32_t sx = r.rbits & 1u, sy = (r.rbits >> 1) & 1u, sz = (r.rbits >> 2) & 1u;
     const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
     const uint4 nx = __ldg(np + 2 + sx), fx = __ldg(np + 3 - sx);
     const uint4 ny = __ldg(np + 4 + sy), fy = __ldg(np + 5 - sy);
