@@ -206,7 +206,8 @@ def run_ours(args):
     f0 = Wm * B
 
     # ---- ray counts of the timed frames: identical untimed pass on a counting context --------------------
-    cctx = librt.Context(counters=True, **kw)
+    # per-ray primary traversal here: node / triangle counts then follow the per-ray work definition
+    cctx = librt.Context(counters=True, per_ray_primary=True, **kw)
     cctx.build_scene(scene)
     cctx.resize(W, H)
     cctx.trace_frames(ubo, CLEAR, f0, K * B)

@@ -215,12 +215,15 @@ struct WfView {
 #define CT_CUR_EXT 3
 #define CT_CUR_SHD 4
 #define CT_CUR_SHW 5
+#define CT_FB 6       /* rays the packet kernel handed back to the per-ray kernel */
+#define CT_CUR_PKT 7  /* packet cursor */
 
 __global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_count) {
     // before a bounce: the out queue, the shadow queue and the cursors are empty
     const uint32_t t = threadIdx.x;
     if (t == 0) {
         ctrl[q_in ^ 1u] = 0; ctrl[CT_SH] = 0; ctrl[CT_CUR_EXT] = 0; ctrl[CT_CUR_SHD] = 0; ctrl[CT_CUR_SHW] = 0;
+        ctrl[CT_FB] = 0; ctrl[CT_CUR_PKT] = 0;
         if (q_in_count != 0xFFFFFFFFu) ctrl[q_in] = q_in_count;
     }
 }
@@ -342,6 +345,146 @@ __global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_extend_kernel(Scen
             }
             if (__popc(__activemask()) < min_active) break;
         }
+    }
+    if (COUNT) {
+        warp_add(&counters->extend_rays, c_rays);
+        warp_add(&counters->nodes, c_nodes);
+        warp_add(&counters->tris, c_tris);
+    }
+}
+
+// ---- primary rays as packets ------------------------------------------------------------------------
+// The 32 primary rays a warp takes (a 4 x 8 screen tile of one frame, see primary_slot) leave the same point
+// and differ by a fraction of a degree, so the warp walks the BVH ONCE with a shared group stack instead of 32
+// times: lane (l & 7) tests child box (l & 7) against the interval hull of the packet's 32 reciprocal
+// directions (Wald et al.'s interval-arithmetic slab test: conservative for every ray of the packet), the hit
+// bits are OR-reduced over the warp (REDUX), and every triangle the hull reaches is tested by all 32 lanes,
+// each against its own ray with the same watertight tri_isect and the same (t, id) acceptance rule as the
+// per-ray kernel.  Closest hits do not depend on which extra triangles were tested, so the hit records are
+// bit-identical to per-ray traversal (tests/test_gpu_parity.py::test_packet_primary_*).  On the Sponza
+// proxy a packet visits 19.2 nodes and 11.0 triangles where one ray visits 17.4 and 6.2
+// (tools/packet_proto.py): ~3x fewer warp instructions for the first bounce, at full SIMD width.
+// Packets whose rays do not share origin bits and direction signs (tiles across an axis plane) are handed to
+// the per-ray kernel through a queue.
+#ifndef RT_PKT_MIN_BLOCKS
+#define RT_PKT_MIN_BLOCKS 8
+#endif
+#define RT_PKT_MARGIN 2e-6f  /* relative widening of the hull's [tnear, tfar]: covers the rounding of this test */
+
+// min / max over the warp of floats that all carry the sign `neg` (unsigned order of the bit patterns)
+__device__ __forceinline__ float warp_fmin_signed(float v, bool neg) {
+    const uint32_t b = __float_as_uint(v);
+    return __uint_as_float(neg ? __reduce_max_sync(0xFFFFFFFFu, b) : __reduce_min_sync(0xFFFFFFFFu, b));
+}
+__device__ __forceinline__ float warp_fmax_signed(float v, bool neg) {
+    const uint32_t b = __float_as_uint(v);
+    return __uint_as_float(neg ? __reduce_min_sync(0xFFFFFFFFu, b) : __reduce_max_sync(0xFFFFFFFFu, b));
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kernel(SceneView sc, WfView wf, uint32_t* fb_queue,
+                                                                                  uint32_t width, uint32_t n_px,
+                                                                                  DevCounters* counters) {
+    const uint32_t n = wf.ctrl[CT_Q0];
+    const uint32_t n_groups = (n + 31u) >> 5;
+    const uint32_t lane = threadIdx.x & 31u, c = lane & 7u;
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    uint2 stk[RT_STACK_SIZE];
+    for (;;) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(&wf.ctrl[CT_CUR_PKT], 1u);
+        g = __shfl_sync(0xFFFFFFFFu, g, 0);
+        if (g >= n_groups) break;
+        const uint32_t i = g * 32u + lane;
+        const bool valid = i < n;
+        const uint32_t slot = primary_slot(valid ? i : n - 1u, width, n_px);
+        const float4 o4 = wf.ray_o[slot], d4 = wf.ray_d[slot];
+        const uint32_t sb = (__float_as_uint(d4.x) >> 31) | ((__float_as_uint(d4.y) >> 31) << 1) | ((__float_as_uint(d4.z) >> 31) << 2);
+        // (every lane executes every shuffle: no short-circuit around a *_sync call)
+        const uint32_t sb0 = __shfl_sync(0xFFFFFFFFu, sb, 0);
+        const uint32_t ox0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.x), 0);
+        const uint32_t oy0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.y), 0);
+        const uint32_t oz0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.z), 0);
+        const bool ok = sb == sb0 && __float_as_uint(o4.x) == ox0 && __float_as_uint(o4.y) == oy0 && __float_as_uint(o4.z) == oz0 &&
+                        fabsf(d4.x) >= 1e-20f && fabsf(d4.y) >= 1e-20f && fabsf(d4.z) >= 1e-20f;  // the last three also reject NaN
+        if (!__all_sync(0xFFFFFFFFu, ok)) {
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, valid);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&wf.ctrl[CT_FB], (uint32_t)__popc(bal));
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (valid) fb_queue[base + __popc(bal & ((1u << lane) - 1u))] = slot;
+            continue;
+        }
+        if (COUNT && valid) c_rays++;
+        const TravRay r = trav_setup(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+        const uint32_t oct = sb;
+        const bool s0 = (oct & 1u) != 0u, s1 = (oct & 2u) != 0u, s2 = (oct & 4u) != 0u;
+        // hull of the reciprocal directions
+        const float ilx = warp_fmin_signed(r.idx, s0), ihx = warp_fmax_signed(r.idx, s0);
+        const float ily = warp_fmin_signed(r.idy, s1), ihy = warp_fmax_signed(r.idy, s1);
+        const float ilz = warp_fmin_signed(r.idz, s2), ihz = warp_fmax_signed(r.idz, s2);
+        Hit best;
+        best.t = 10000.0f; best.u = 0.0f; best.v = 0.0f; best.id = 0xFFFFFFFFu; best.inst = 0u; best.prim = 0u;
+        uint2 ng = make_uint2(0u, 0x80000000u);
+        int sp = 0;
+        for (;;) {
+            // pop the nearest child of the current group (warp-uniform)
+            const int bit = 31 - __clz(ng.y);
+            ng.y &= ~(1u << bit);
+            const uint32_t sl = ((uint32_t)bit - 24u) ^ oct;
+            const uint32_t node = ng.x + __popc(ng.y & 0xFFu & ((1u << sl) - 1u));
+            if (ng.y & 0xFF000000u) stk[sp++] = ng;
+            const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
+            const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
+            const unsigned short* qp = reinterpret_cast<const unsigned short*>(np + 2) + c;  // q[axis][lo/hi][slot]
+            const float qxl = __half2float(__ushort_as_half(__ldg(qp))), qxh = __half2float(__ushort_as_half(__ldg(qp + 8)));
+            const float qyl = __half2float(__ushort_as_half(__ldg(qp + 16))), qyh = __half2float(__ushort_as_half(__ldg(qp + 24)));
+            const float qzl = __half2float(__ushort_as_half(__ldg(qp + 32))), qzh = __half2float(__ushort_as_half(__ldg(qp + 40)));
+            if (COUNT && lane == 0) c_nodes++;
+            const uint32_t ew = w0.w;
+            const float scx = __uint_as_float((ew & 0xFFu) << 23), scy = __uint_as_float(((ew >> 8) & 0xFFu) << 23),
+                        scz = __uint_as_float(((ew >> 16) & 0xFFu) << 23);
+            // child box relative to the common origin
+            const float lx = fmaf(qxl, scx, __uint_as_float(w0.x)) - r.ox, hx = fmaf(qxh, scx, __uint_as_float(w0.x)) - r.ox;
+            const float ly = fmaf(qyl, scy, __uint_as_float(w0.y)) - r.oy, hy = fmaf(qyh, scy, __uint_as_float(w0.y)) - r.oy;
+            const float lz = fmaf(qzl, scz, __uint_as_float(w0.z)) - r.oz, hz = fmaf(qzh, scz, __uint_as_float(w0.z)) - r.oz;
+            const float nx = s0 ? hx : lx, fx = s0 ? lx : hx;
+            const float ny = s1 ? hy : ly, fy = s1 ? ly : hy;
+            const float nz = s2 ? hz : lz, fz = s2 ? lz : hz;
+            float tn = fmaxf(fmaxf(fminf(nx * ilx, nx * ihx), fminf(ny * ily, ny * ihy)), fminf(nz * ilz, nz * ihz));
+            float tf = fminf(fminf(fmaxf(fx * ilx, fx * ihx), fmaxf(fy * ily, fy * ihy)), fmaxf(fz * ilz, fz * ihz));
+            tn -= fabsf(tn) * RT_PKT_MARGIN;
+            tf += fabsf(tf) * RT_PKT_MARGIN;
+            const float tmaxp = __uint_as_float(__reduce_max_sync(0xFFFFFFFFu, __float_as_uint(best.t)));  // best.t > 0
+            const uint32_t meta = ((c < 4u ? w1.z : w1.w) >> (8u * (c & 3u))) & 0xFFu;
+            const uint32_t idx = (meta & 31u) ^ (((meta & 0x18u) == 0x18u) ? oct : 0u);
+            const bool hit = fmaxf(tn, 0.001f) <= fminf(tf, tmaxp);
+            const uint32_t hm = __reduce_or_sync(0xFFFFFFFFu, hit ? ((meta >> 5) << idx) : 0u);
+            ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
+            uint32_t tmask = hm & 0x00FFFFFFu;
+            while (tmask) {  // warp-uniform
+                const int tb = __ffs(tmask) - 1;
+                tmask &= tmask - 1u;
+                const float4* tp = sc.tris + (size_t)(w1.y + (uint32_t)tb) * 3u;
+                const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                if (COUNT && lane == 0) c_tris++;
+                float tt, uu, vv;
+                if (!tri_isect(r, q0, q1, q2, &tt, &uu, &vv)) continue;
+                if (!(tt > 0.001f)) continue;
+                const uint32_t id = __float_as_uint(q0.w);
+                const bool take = (best.id == 0xFFFFFFFFu) ? (tt < best.t) : ((tt < best.t) || (tt == best.t && id < best.id));
+                if (take) {
+                    best.t = tt; best.u = uu; best.v = vv; best.id = id; best.inst = __float_as_uint(q1.w); best.prim = __float_as_uint(q2.w);
+                }
+            }
+            if (!(ng.y & 0xFF000000u)) {
+                if (sp == 0) break;
+                ng = stk[--sp];
+            }
+        }
+        if (valid)
+            wf.hit[slot] = make_uint4(__float_as_uint(best.u), __float_as_uint(best.v), best.id == 0xFFFFFFFFu ? 0xFFFFFFFFu : best.inst,
+                                      best.prim);
     }
     if (COUNT) {
         warp_add(&counters->extend_rays, c_rays);
@@ -522,8 +665,9 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     v.ray_o = w->ray_o.p; v.ray_d = w->ray_d.p; v.thr = w->thr.p; v.col = w->col.p; v.prev = w->prev.p;
     v.seeds = w->seeds.p; v.hit = w->hit.p; v.sh_o = w->sh_o.p; v.sh_d = w->sh_d.p; v.sh_c = w->sh_c.p; v.sh_e = w->sh_e.p;
     v.ctrl = w->ctrl.p;
-    static int g_ext = 0, g_shw = 0, g_shd = 0;
+    static int g_ext = 0, g_shw = 0, g_shd = 0, g_pkt = 0;
     if (!g_ext) {
+        g_pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128);
         g_ext = persistent_grid(wf_extend_kernel<COUNT>, 128);
         g_shw = persistent_grid(wf_shadow_kernel<COUNT>, 128);
         g_shd = persistent_grid(wf_shade_kernel<COUNT>, 128);
@@ -544,7 +688,16 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, q_in, depth == 0 ? n_slots : 0xFFFFFFFFu);
         const uint32_t* qi = depth == 0 ? nullptr : w->queue[q_in].p;
         pf.begin(RT_K_EXTEND, stream);
-        wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, fp.width, n_px, res.counters);
+        if (depth == 0 && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
+            // packets first; what they hand back (tiles across an axis plane) goes through the per-ray kernel
+            wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, v, w->queue[0].p, fp.width, n_px,
+                                                                                     res.counters);
+            wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, w->queue[0].p, CT_FB, fp.width, n_px,
+                                                                               res.counters);
+            n_launch++;
+        } else {
+            wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, fp.width, n_px, res.counters);
+        }
         pf.end(stream);
         pf.begin(RT_K_SHADE, stream);
         wf_shade_kernel<COUNT><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,

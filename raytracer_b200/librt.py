@@ -19,7 +19,7 @@ STATUS_NAMES = {
     0: "RT_OK", -1: "RT_ERR_INVALID_ARGUMENT", -2: "RT_ERR_NO_DEVICE", -3: "RT_ERR_CUDA", -4: "RT_ERR_OUT_OF_MEMORY",
     -5: "RT_ERR_NO_SCENE", -6: "RT_ERR_NO_TARGET", -7: "RT_ERR_BVH_TOO_DEEP", -8: "RT_ERR_INDEX_RANGE",
 }
-RT_FLAG_DIRECT_LIGHTING, RT_FLAG_MIS, RT_FLAG_COUNTERS = 1, 2, 4
+RT_FLAG_DIRECT_LIGHTING, RT_FLAG_MIS, RT_FLAG_COUNTERS, RT_FLAG_PER_RAY_PRIMARY = 1, 2, 4, 8
 RT_FLAG_DEFAULT = 7
 RT_PIPELINE_WAVEFRONT, RT_PIPELINE_MEGAKERNEL = 0, 1
 RT_RESTIR_TEMPORAL, RT_RESTIR_SPATIAL = 1, 2
@@ -155,13 +155,14 @@ class Context:
 
     def __init__(self, device: int = -1, max_depth: int = 3, rr_start_depth: int = 3, radiance_clamp: float = 5.0,
                  counters: bool = True, pipeline: int = RT_PIPELINE_WAVEFRONT, strip_rows: int = 8, strip_index: int = 0,
-                 strip_count: int = 1, frames_in_flight: int = 0):
+                 strip_count: int = 1, frames_in_flight: int = 0, per_ray_primary: bool = False):
         self.L = load()
         cfg = RtConfig()
         self.L.rt_default_config(C.byref(cfg))
         cfg.device, cfg.max_depth, cfg.rr_start_depth = device, max_depth, rr_start_depth
         cfg.radiance_clamp = radiance_clamp
-        cfg.flags = RT_FLAG_DIRECT_LIGHTING | RT_FLAG_MIS | (RT_FLAG_COUNTERS if counters else 0)
+        cfg.flags = (RT_FLAG_DIRECT_LIGHTING | RT_FLAG_MIS | (RT_FLAG_COUNTERS if counters else 0) |
+                     (RT_FLAG_PER_RAY_PRIMARY if per_ray_primary else 0))
         cfg.pipeline = pipeline
         cfg.strip_rows, cfg.strip_index, cfg.strip_count = strip_rows, strip_index, strip_count
         if frames_in_flight:

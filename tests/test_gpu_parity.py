@@ -130,7 +130,8 @@ def test_closest_hit_ties_shared_edges(ctx):
     assert (ids != 0xFFFFFFFF).mean() > 0.9 and ids[ids != 0xFFFFFFFF].max() < 2 * (g - 1) ** 2
 
 
-@pytest.mark.parametrize("pipeline", [librt.RT_PIPELINE_WAVEFRONT, librt.RT_PIPELINE_MEGAKERNEL])
+# "packets": primary rays traced as 32-ray packets (the default); "per_ray": RT_FLAG_PER_RAY_PRIMARY
+@pytest.mark.parametrize("pipeline", ["packets", "per_ray", "megakernel"])
 @pytest.mark.parametrize("name", ["cornell_box", "cornell_pbr", "conference", "conference_mirror_chairs",
                                   "multi_dispersion", "cornell_box_gltf"])
 def test_frames_bit_exact(name, pipeline):
@@ -138,7 +139,8 @@ def test_frames_bit_exact(name, pipeline):
     scene = fixture_scene(name)
     W, H = 160, 96
     cam = _camera_for(name, W / H)
-    c = librt.Context(device=0, pipeline=pipeline)
+    c = librt.Context(device=0, pipeline=librt.RT_PIPELINE_MEGAKERNEL if pipeline == "megakernel" else librt.RT_PIPELINE_WAVEFRONT,
+                      per_ray_primary=pipeline == "per_ray")
     try:
         c.build_scene(scene)
         c.resize(W, H)
@@ -152,18 +154,24 @@ def test_frames_bit_exact(name, pipeline):
             bad = (got.view(np.uint32) != ref.view(np.uint32)).any(axis=2)
             assert not bad.any(), f"frame {f}: {int(bad.sum())} pixels differ, max abs {np.abs(got - ref).max()}"
         dev = c.counters()
-        assert [dev[k] for k in ("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee")] == [int(x) for x in cnt]
+        if pipeline == "packets":  # one node / triangle fetch per packet instead of one per ray
+            assert [dev[k] for k in ("extend_rays", "shadow_rays", "hits", "nee")] == [int(cnt[i]) for i in (0, 1, 4, 5)]
+            assert dev["nodes"] < int(cnt[2]) and dev["tris"] < int(cnt[3])
+        else:
+            assert [dev[k] for k in ("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee")] == [int(x) for x in cnt]
         assert ref[..., :3].max() > 0.05
     finally:
         c.close()
 
 
-def test_golden_frames(ctx):
+@pytest.mark.parametrize("per_ray", [False, True])
+def test_golden_frames(per_ray):
     """Committed oracle outputs (tests/golden/oracle_*.npz, tools/make_fixtures.py)."""
     import os
 
     from conftest import GOLDEN
 
+    ctx = librt.Context(device=0, per_ray_primary=per_ray)
     for name in ("cornell_box", "cornell_pbr"):
         z = np.load(os.path.join(GOLDEN, f"oracle_{name}.npz"))
         scene = fixture_scene(name)
@@ -175,7 +183,34 @@ def test_golden_frames(ctx):
             ctx.trace_frame(z["camera"], CLEAR, f)
             assert np.array_equal(ctx.readback().view(np.uint32), z["frames"][f].view(np.uint32))
         dev = ctx.counters()
-        assert [dev[k] for k in ("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee")] == [int(x) for x in z["counters"]]
+        keys = ("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee") if per_ray else ("extend_rays", "shadow_rays", "hits", "nee")
+        want = {k: int(x) for k, x in zip(("extend_rays", "shadow_rays", "nodes", "tris", "hits", "nee"), z["counters"])}
+        assert [dev[k] for k in keys] == [want[k] for k in keys]
+    ctx.close()
+
+
+def test_packet_primary_matches_per_ray_1080p():
+    """Full-size check of the packet kernel: sponza-proxy 1920x1080 depth 8, jittered frames in flight, an
+    off-axis and an axis-crossing camera (tiles whose rays change sign fall back to the per-ray kernel)."""
+    import bench
+
+    scene, cam = bench.make_scene("sponza-proxy", 1920, 1080)
+    cams = [cam, rb.Camera(position=(-10.0, 2.0, 0.0), aspect=1920 / 1080, target=(0.0, 2.0, 0.0))]
+    imgs = []
+    for per_ray in (False, True):
+        c = librt.Context(device=0, max_depth=8, rr_start_depth=3, per_ray_primary=per_ray, frames_in_flight=4)
+        c.build_scene(scene)
+        c.resize(1920, 1080)
+        out = []
+        for cm in cams:
+            c.trace_frames(cm.ubo(), CLEAR, 0, 4)
+            out.append(c.readback().copy())
+        imgs.append(out)
+        cnt = c.counters()
+        c.close()
+    for a, b in zip(*imgs):
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        assert a[..., :3].max() > 0.05
 
 
 def test_trace_frames_batch_equals_loop(ctx):

@@ -28,13 +28,15 @@ def main():
     ap.add_argument("--repeat", type=int, default=1)
     ap.add_argument("--kprof", action="store_true", help="per-kernel CUDA-event times (serialises launches)")
     ap.add_argument("--lanes", type=int, default=0, help="frames_in_flight (0 = library default)")
+    ap.add_argument("--per-ray", action="store_true", help="RT_FLAG_PER_RAY_PRIMARY: no primary-ray packets")
     a = ap.parse_args()
     import bench
     from raytracer_b200 import librt
 
     scene, cam = bench.make_scene(a.scene, a.width, a.height)
     pipe = librt.RT_PIPELINE_WAVEFRONT if a.pipeline == "wavefront" else librt.RT_PIPELINE_MEGAKERNEL
-    ctx = librt.Context(counters=a.counters, device=0, max_depth=a.depth, rr_start_depth=3, pipeline=pipe, frames_in_flight=a.lanes)
+    ctx = librt.Context(counters=a.counters, device=0, max_depth=a.depth, rr_start_depth=3, pipeline=pipe, frames_in_flight=a.lanes,
+                        per_ray_primary=a.per_ray)
     info = ctx.build_scene(scene)
     ctx.resize(a.width, a.height)
     ubo = cam.ubo()
