@@ -241,11 +241,10 @@ __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView w
     PathState ps;
     vec3 o, d;
     raygen_init(fp, x, y, ps, &o, &d);
+    // throughput, colour and previous-hit state start from constants: the first shade launch (FIRST = true)
+    // supplies them itself instead of reading them back (saves 48 B written here and 48 B read there per ray)
     wf.ray_o[slot] = make_float4(o.x, o.y, o.z, 0.0f);
     wf.ray_d[slot] = make_float4(d.x, d.y, d.z, 0.0f);
-    wf.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
-    wf.col[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    wf.prev[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(PF_FIRST));
     wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
 }
 
@@ -354,22 +353,26 @@ __global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_extend_kernel(Scen
 }
 
 // ---- primary rays as packets ------------------------------------------------------------------------
-// The 32 primary rays a warp takes (a 4 x 8 screen tile of one frame, see primary_slot) leave the same point
-// and differ by a fraction of a degree, so the warp walks the BVH ONCE with a shared group stack instead of 32
-// times: lane (l & 7) tests child box (l & 7) against the interval hull of the packet's 32 reciprocal
-// directions (Wald et al.'s interval-arithmetic slab test: conservative for every ray of the packet), the hit
-// bits are OR-reduced over the warp (REDUX), and every triangle the hull reaches is tested by all 32 lanes,
-// each against its own ray with the same watertight tri_isect and the same (t, id) acceptance rule as the
-// per-ray kernel.  Closest hits do not depend on which extra triangles were tested, so the hit records are
-// bit-identical to per-ray traversal (tests/test_gpu_parity.py::test_packet_primary_*).  On the Sponza
-// proxy a packet visits 19.2 nodes and 11.0 triangles where one ray visits 17.4 and 6.2
-// (tools/packet_proto.py): ~3x fewer warp instructions for the first bounce, at full SIMD width.
+// The primary rays of a screen tile leave the same point and differ by a fraction of a degree, so a warp walks
+// the BVH ONCE for RT_PKT_RPL x 32 of them (RT_PKT_RPL horizontally adjacent 4 x 8 tiles of one frame, see
+// primary_slot) with a shared group stack instead of once per ray: lane (l & 7) tests child box (l & 7)
+// against the interval hull of the packet's reciprocal directions (Wald et al.'s interval-arithmetic slab
+// test: conservative for every ray of the packet; the hull is widened by RT_PKT_MARGIN to cover the rounding of
+// this test), the hit bits are OR-reduced over the warp (REDUX), and every triangle the hull reaches is
+// tested by all 32 lanes, each against its own RT_PKT_RPL rays with the same watertight edge test and the same
+// (t, id) acceptance rule as the per-ray kernel.  Closest hits do not depend on which extra triangles were
+// tested, so the hit records are bit-identical to per-ray traversal
+// (tests/test_gpu_parity.py::test_packet_primary_matches_per_ray_1080p).  On the Sponza proxy a 16 x 8 packet
+// visits 21.8 nodes and 17.9 triangles where ONE ray visits 17.4 and 6.2 (tools/packet_proto.py).
 // Packets whose rays do not share origin bits and direction signs (tiles across an axis plane) are handed to
 // the per-ray kernel through a queue.
-#ifndef RT_PKT_MIN_BLOCKS
-#define RT_PKT_MIN_BLOCKS 8
+#ifndef RT_PKT_RPL
+#define RT_PKT_RPL 4
 #endif
-#define RT_PKT_MARGIN 2e-6f  /* relative widening of the hull's [tnear, tfar]: covers the rounding of this test */
+#ifndef RT_PKT_MIN_BLOCKS
+#define RT_PKT_MIN_BLOCKS (RT_PKT_RPL == 1 ? 8 : (RT_PKT_RPL == 2 ? 5 : 3))
+#endif
+#define RT_PKT_MARGIN 4e-6f
 
 // min / max over the warp of floats that all carry the sign `neg` (unsigned order of the bit patterns)
 __device__ __forceinline__ float warp_fmin_signed(float v, bool neg) {
@@ -385,8 +388,9 @@ template <bool COUNT>
 __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kernel(SceneView sc, WfView wf, uint32_t* fb_queue,
                                                                                   uint32_t width, uint32_t n_px,
                                                                                   DevCounters* counters) {
+    constexpr int R = RT_PKT_RPL;
     const uint32_t n = wf.ctrl[CT_Q0];
-    const uint32_t n_groups = (n + 31u) >> 5;
+    const uint32_t n_groups = (n + 32u * R - 1u) / (32u * R);
     const uint32_t lane = threadIdx.x & 31u, c = lane & 7u;
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     uint2 stk[RT_STACK_SIZE];
@@ -395,36 +399,69 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
         if (lane == 0) g = atomicAdd(&wf.ctrl[CT_CUR_PKT], 1u);
         g = __shfl_sync(0xFFFFFFFFu, g, 0);
         if (g >= n_groups) break;
-        const uint32_t i = g * 32u + lane;
-        const bool valid = i < n;
-        const uint32_t slot = primary_slot(valid ? i : n - 1u, width, n_px);
-        const float4 o4 = wf.ray_o[slot], d4 = wf.ray_d[slot];
-        const uint32_t sb = (__float_as_uint(d4.x) >> 31) | ((__float_as_uint(d4.y) >> 31) << 1) | ((__float_as_uint(d4.z) >> 31) << 2);
-        // (every lane executes every shuffle: no short-circuit around a *_sync call)
-        const uint32_t sb0 = __shfl_sync(0xFFFFFFFFu, sb, 0);
-        const uint32_t ox0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.x), 0);
-        const uint32_t oy0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.y), 0);
-        const uint32_t oz0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.z), 0);
-        const bool ok = sb == sb0 && __float_as_uint(o4.x) == ox0 && __float_as_uint(o4.y) == oy0 && __float_as_uint(o4.z) == oz0 &&
-                        fabsf(d4.x) >= 1e-20f && fabsf(d4.y) >= 1e-20f && fabsf(d4.z) >= 1e-20f;  // the last three also reject NaN
+        // ---- the packet's rays: ray k of this lane is entry g * 32 R + 32 k + lane of the tiled pixel order
+        uint32_t slot[R];
+        Shear sh[R];
+        float ikz[R], bt[R], bu[R], bv[R];
+        uint32_t bid[R], btri[R];
+        uint32_t kzs = 0u, valid = 0u;
+        float ox, oy, oz;
+        float ilx, ihx, ily, ihy, ilz, ihz;
+        uint32_t oct;
+        bool ok = true;
+        {
+            uint32_t sb0 = 0, ox0 = 0, oy0 = 0, oz0 = 0;
+#pragma unroll
+            for (int k = 0; k < R; k++) {
+                const uint32_t i = (g * R + (uint32_t)k) * 32u + lane;
+                if (i < n) valid |= 1u << k;
+                slot[k] = primary_slot(i < n ? i : n - 1u, width, n_px);
+                const float4 o4 = wf.ray_o[slot[k]], d4 = wf.ray_d[slot[k]];
+                const uint32_t sb = (__float_as_uint(d4.x) >> 31) | ((__float_as_uint(d4.y) >> 31) << 1) | ((__float_as_uint(d4.z) >> 31) << 2);
+                if (k == 0) {  // every lane executes every shuffle: no short-circuit around a *_sync call
+                    sb0 = __shfl_sync(0xFFFFFFFFu, sb, 0);
+                    ox0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.x), 0);
+                    oy0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.y), 0);
+                    oz0 = __shfl_sync(0xFFFFFFFFu, __float_as_uint(o4.z), 0);
+                }
+                ok = ok && sb == sb0 && __float_as_uint(o4.x) == ox0 && __float_as_uint(o4.y) == oy0 && __float_as_uint(o4.z) == oz0 &&
+                     fabsf(d4.x) >= 1e-20f && fabsf(d4.y) >= 1e-20f && fabsf(d4.z) >= 1e-20f;  // the last three also reject NaN
+                const TravRay r = trav_setup(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+                sh[k] = r.sh;
+                const uint32_t kz = (r.rbits >> 3) & 3u;
+                kzs |= kz << (2 * k);
+                ikz[k] = kz == 0u ? r.idx : (kz == 1u ? r.idy : r.idz);
+                // per-lane part of the hull
+                ilx = k == 0 ? r.idx : fminf(ilx, r.idx); ihx = k == 0 ? r.idx : fmaxf(ihx, r.idx);
+                ily = k == 0 ? r.idy : fminf(ily, r.idy); ihy = k == 0 ? r.idy : fmaxf(ihy, r.idy);
+                ilz = k == 0 ? r.idz : fminf(ilz, r.idz); ihz = k == 0 ? r.idz : fmaxf(ihz, r.idz);
+                bt[k] = 10000.0f; bu[k] = 0.0f; bv[k] = 0.0f; bid[k] = 0xFFFFFFFFu; btri[k] = 0u;
+            }
+            ox = __uint_as_float(ox0); oy = __uint_as_float(oy0); oz = __uint_as_float(oz0);
+            oct = sb0;
+        }
         if (!__all_sync(0xFFFFFFFFu, ok)) {
-            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, valid);
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(&wf.ctrl[CT_FB], (uint32_t)__popc(bal));
-            base = __shfl_sync(0xFFFFFFFFu, base, 0);
-            if (valid) fb_queue[base + __popc(bal & ((1u << lane) - 1u))] = slot;
+#pragma unroll
+            for (int k = 0; k < R; k++) {
+                const bool v = (valid >> k) & 1u;
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, v);
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&wf.ctrl[CT_FB], (uint32_t)__popc(bal));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (v) fb_queue[base + __popc(bal & ((1u << lane) - 1u))] = slot[k];
+            }
             continue;
         }
-        if (COUNT && valid) c_rays++;
-        const TravRay r = trav_setup(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
-        const uint32_t oct = sb;
+        if (COUNT) c_rays += __popc(valid);
         const bool s0 = (oct & 1u) != 0u, s1 = (oct & 2u) != 0u, s2 = (oct & 4u) != 0u;
-        // hull of the reciprocal directions
-        const float ilx = warp_fmin_signed(r.idx, s0), ihx = warp_fmax_signed(r.idx, s0);
-        const float ily = warp_fmin_signed(r.idy, s1), ihy = warp_fmax_signed(r.idy, s1);
-        const float ilz = warp_fmin_signed(r.idz, s2), ihz = warp_fmax_signed(r.idz, s2);
-        Hit best;
-        best.t = 10000.0f; best.u = 0.0f; best.v = 0.0f; best.id = 0xFFFFFFFFu; best.inst = 0u; best.prim = 0u;
+        // hull of the reciprocal directions, widened so that the products below err on the safe side
+        ilx = warp_fmin_signed(ilx, s0); ihx = warp_fmax_signed(ihx, s0);
+        ily = warp_fmin_signed(ily, s1); ihy = warp_fmax_signed(ihy, s1);
+        ilz = warp_fmin_signed(ilz, s2); ihz = warp_fmax_signed(ihz, s2);
+        ilx -= fabsf(ilx) * RT_PKT_MARGIN; ihx += fabsf(ihx) * RT_PKT_MARGIN;
+        ily -= fabsf(ily) * RT_PKT_MARGIN; ihy += fabsf(ihy) * RT_PKT_MARGIN;
+        ilz -= fabsf(ilz) * RT_PKT_MARGIN; ihz += fabsf(ihz) * RT_PKT_MARGIN;
+        float tmaxp = 10000.0f;  // max over the packet of the rays' current closest distances
         uint2 ng = make_uint2(0u, 0x80000000u);
         int sp = 0;
         for (;;) {
@@ -435,7 +472,9 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
             const uint32_t node = ng.x + __popc(ng.y & 0xFFu & ((1u << sl) - 1u));
             if (ng.y & 0xFF000000u) stk[sp++] = ng;
             const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
-            const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
+            const uint4 w0 = __ldg(np);
+            const uint2 w1 = __ldg(reinterpret_cast<const uint2*>(np + 1));  // child_base, tri_base
+            const uint32_t meta = __ldg(reinterpret_cast<const unsigned char*>(np) + 24 + c);
             const unsigned short* qp = reinterpret_cast<const unsigned short*>(np + 2) + c;  // q[axis][lo/hi][slot]
             const float qxl = __half2float(__ushort_as_half(__ldg(qp))), qxh = __half2float(__ushort_as_half(__ldg(qp + 8)));
             const float qyl = __half2float(__ushort_as_half(__ldg(qp + 16))), qyh = __half2float(__ushort_as_half(__ldg(qp + 24)));
@@ -445,46 +484,65 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
             const float scx = __uint_as_float((ew & 0xFFu) << 23), scy = __uint_as_float(((ew >> 8) & 0xFFu) << 23),
                         scz = __uint_as_float(((ew >> 16) & 0xFFu) << 23);
             // child box relative to the common origin
-            const float lx = fmaf(qxl, scx, __uint_as_float(w0.x)) - r.ox, hx = fmaf(qxh, scx, __uint_as_float(w0.x)) - r.ox;
-            const float ly = fmaf(qyl, scy, __uint_as_float(w0.y)) - r.oy, hy = fmaf(qyh, scy, __uint_as_float(w0.y)) - r.oy;
-            const float lz = fmaf(qzl, scz, __uint_as_float(w0.z)) - r.oz, hz = fmaf(qzh, scz, __uint_as_float(w0.z)) - r.oz;
-            const float nx = s0 ? hx : lx, fx = s0 ? lx : hx;
-            const float ny = s1 ? hy : ly, fy = s1 ? ly : hy;
-            const float nz = s2 ? hz : lz, fz = s2 ? lz : hz;
-            float tn = fmaxf(fmaxf(fminf(nx * ilx, nx * ihx), fminf(ny * ily, ny * ihy)), fminf(nz * ilz, nz * ihz));
-            float tf = fminf(fminf(fmaxf(fx * ilx, fx * ihx), fmaxf(fy * ily, fy * ihy)), fmaxf(fz * ilz, fz * ihz));
-            tn -= fabsf(tn) * RT_PKT_MARGIN;
-            tf += fabsf(tf) * RT_PKT_MARGIN;
-            const float tmaxp = __uint_as_float(__reduce_max_sync(0xFFFFFFFFu, __float_as_uint(best.t)));  // best.t > 0
-            const uint32_t meta = ((c < 4u ? w1.z : w1.w) >> (8u * (c & 3u))) & 0xFFu;
+            const float rx = __uint_as_float(w0.x) - ox, ry = __uint_as_float(w0.y) - oy, rz = __uint_as_float(w0.z) - oz;
+            const float lx = fmaf(qxl, scx, rx), hx = fmaf(qxh, scx, rx);
+            const float ly = fmaf(qyl, scy, ry), hy = fmaf(qyh, scy, ry);
+            const float lz = fmaf(qzl, scz, rz), hz = fmaf(qzh, scz, rz);
+            // entry / exit of the hull per axis: extremes of the four plane x reciprocal-direction products
+            const float tn = fmaxf(fmaxf(fminf(fminf(lx * ilx, lx * ihx), fminf(hx * ilx, hx * ihx)),
+                                         fminf(fminf(ly * ily, ly * ihy), fminf(hy * ily, hy * ihy))),
+                                   fminf(fminf(lz * ilz, lz * ihz), fminf(hz * ilz, hz * ihz)));
+            const float tf = fminf(fminf(fmaxf(fmaxf(lx * ilx, lx * ihx), fmaxf(hx * ilx, hx * ihx)),
+                                         fmaxf(fmaxf(ly * ily, ly * ihy), fmaxf(hy * ily, hy * ihy))),
+                                   fmaxf(fmaxf(lz * ilz, lz * ihz), fmaxf(hz * ilz, hz * ihz)));
             const uint32_t idx = (meta & 31u) ^ (((meta & 0x18u) == 0x18u) ? oct : 0u);
             const bool hit = fmaxf(tn, 0.001f) <= fminf(tf, tmaxp);
             const uint32_t hm = __reduce_or_sync(0xFFFFFFFFu, hit ? ((meta >> 5) << idx) : 0u);
             ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
             uint32_t tmask = hm & 0x00FFFFFFu;
-            while (tmask) {  // warp-uniform
-                const int tb = __ffs(tmask) - 1;
-                tmask &= tmask - 1u;
-                const float4* tp = sc.tris + (size_t)(w1.y + (uint32_t)tb) * 3u;
-                const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
-                if (COUNT && lane == 0) c_tris++;
-                float tt, uu, vv;
-                if (!tri_isect(r, q0, q1, q2, &tt, &uu, &vv)) continue;
-                if (!(tt > 0.001f)) continue;
-                const uint32_t id = __float_as_uint(q0.w);
-                const bool take = (best.id == 0xFFFFFFFFu) ? (tt < best.t) : ((tt < best.t) || (tt == best.t && id < best.id));
-                if (take) {
-                    best.t = tt; best.u = uu; best.v = vv; best.id = id; best.inst = __float_as_uint(q1.w); best.prim = __float_as_uint(q2.w);
-                }
+            if (tmask) {
+                do {  // warp-uniform
+                    const int tb = __ffs(tmask) - 1;
+                    tmask &= tmask - 1u;
+                    const uint32_t ti = w1.y + (uint32_t)tb;
+                    const float4* tp = sc.tris + (size_t)ti * 3u;
+                    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                    if (COUNT && lane == 0) c_tris++;
+                    const uint32_t id = __float_as_uint(q0.w);
+#pragma unroll
+                    for (int k = 0; k < R; k++) {
+                        float U, V, W, det;
+                        if (tri_edges(sh[k], q0, q1, q2, &U, &V, &W, &det)) {
+                            const uint32_t kz = (kzs >> (2 * k)) & 3u;
+                            float tt, uu, vv;
+                            tri_finish(U, V, W, det, q0, q1, q2, kz, kz == 0u ? ox : (kz == 1u ? oy : oz), ikz[k], &tt, &uu, &vv);
+                            const bool take = (tt > 0.001f) && ((bid[k] == 0xFFFFFFFFu) ? (tt < bt[k]) : ((tt < bt[k]) || (tt == bt[k] && id < bid[k])));
+                            if (take) { bt[k] = tt; bu[k] = uu; bv[k] = vv; bid[k] = id; btri[k] = ti; }
+                        }
+                    }
+                } while (tmask);
+                float m = bt[0];
+#pragma unroll
+                for (int k = 1; k < R; k++) m = fmaxf(m, bt[k]);
+                tmaxp = __uint_as_float(__reduce_max_sync(0xFFFFFFFFu, __float_as_uint(m)));  // distances are positive
             }
             if (!(ng.y & 0xFF000000u)) {
                 if (sp == 0) break;
                 ng = stk[--sp];
             }
         }
-        if (valid)
-            wf.hit[slot] = make_uint4(__float_as_uint(best.u), __float_as_uint(best.v), best.id == 0xFFFFFFFFu ? 0xFFFFFFFFu : best.inst,
-                                      best.prim);
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            if ((valid >> k) & 1u) {
+                uint32_t inst = 0xFFFFFFFFu, prim = 0u;
+                if (bid[k] != 0xFFFFFFFFu) {
+                    const float* tq = reinterpret_cast<const float*>(sc.tris + (size_t)btri[k] * 3u);
+                    inst = __float_as_uint(__ldg(tq + 7));
+                    prim = __float_as_uint(__ldg(tq + 11));
+                }
+                wf.hit[slot[k]] = make_uint4(__float_as_uint(bu[k]), __float_as_uint(bv[k]), inst, prim);
+            }
+        }
     }
     if (COUNT) {
         warp_add(&counters->extend_rays, c_rays);
@@ -496,8 +554,11 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
 // shade: simple.rmiss / simple.rchit for every queued path + the ray-gen loop tail (simple.rgen:106-118).
 // Colour terms are added in the reference's order: NEE, emissive, sky.  When the NEE term waits for
 // its visibility ray, the later terms travel with the shadow-queue entry and wf_shadow_kernel adds them.
-template <bool COUNT>
-__global__ void __launch_bounds__(128) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
+#ifndef RT_SHADE_MIN_BLOCKS
+#define RT_SHADE_MIN_BLOCKS 6  /* 80 registers: measured 0.219 -> 0.195 ms/frame against 4 blocks of 128 registers */
+#endif
+template <bool COUNT, bool FIRST>
+__global__ void __launch_bounds__(128, RT_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
                                                        uint32_t q_idx, uint32_t* q_out, int depth, DevCounters* counters) {
     const uint32_t n = wf.ctrl[q_idx];
     uint32_t c_hits = 0, c_nee = 0;
@@ -516,7 +577,9 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(SceneView sc, FrameParams
         if (i < n) {
             slot = q_in ? q_in[i] : i;
             const uint4 hrec = wf.hit[slot];
-            const float4 tv = wf.thr[slot], cv = wf.col[slot];
+            // first bounce: the payload initialisation of simple.rgen:76-85
+            const float4 tv = FIRST ? make_float4(1.0f, 1.0f, 1.0f, 1.0f) : wf.thr[slot];
+            const float4 cv = FIRST ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : wf.col[slot];
             ps.throughput = mk3(tv.x, tv.y, tv.z);
             ps.prev_brdf_pdf = tv.w;
             ps.color = mk3(cv.x, cv.y, cv.z);
@@ -524,7 +587,8 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(SceneView sc, FrameParams
             if (hrec.z == 0xFFFFFFFFu) {  // simple.rmiss:26-29 -> simple.rgen:106-109
                 sky = true;
             } else {
-                const float4 pv = wf.prev[slot], dv = wf.ray_d[slot];
+                const float4 pv = FIRST ? make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(PF_FIRST)) : wf.prev[slot];
+                const float4 dv = wf.ray_d[slot];
                 const uint2 sd = wf.seeds[slot];
                 const uint32_t fl = __float_as_uint(pv.w);
                 ps.prev_hit_pos = mk3(pv.x, pv.y, pv.z);
@@ -566,7 +630,8 @@ __global__ void __launch_bounds__(128) wf_shade_kernel(SceneView sc, FrameParams
         const uint32_t si = queue_push(&wf.ctrl[CT_SH], push_shadow);
         if (push_shadow) {
             // a sky term is only pending when the hit shader ended the path, in which case the throughput
-            // in the state array is still the one the term needs
+            // in the state array is still the one the term needs (on the first bounce it has not been stored yet)
+            if (FIRST && sky) wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_brdf_pdf);
             wf.sh_o[si] = make_float4(sr.origin.x, sr.origin.y, sr.origin.z, sr.tmax);
             wf.sh_d[si] = make_float4(sr.dir.x, sr.dir.y, sr.dir.z, __uint_as_float(sr.light_object));
             wf.sh_c[si] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, __uint_as_float(slot));
@@ -670,7 +735,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         g_pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128);
         g_ext = persistent_grid(wf_extend_kernel<COUNT>, 128);
         g_shw = persistent_grid(wf_shadow_kernel<COUNT>, 128);
-        g_shd = persistent_grid(wf_shade_kernel<COUNT>, 128);
+        g_shd = persistent_grid(wf_shade_kernel<COUNT, false>, 128);
     }
     const uint32_t gb = (n_slots + 255) / 256;
     const uint32_t gb_px = (n_px + 255) / 256;
@@ -700,8 +765,12 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         }
         pf.end(stream);
         pf.begin(RT_K_SHADE, stream);
-        wf_shade_kernel<COUNT><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
-                                                                          res.counters);
+        if (depth == 0)
+            wf_shade_kernel<COUNT, true><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
+                                                                                    res.counters);
+        else
+            wf_shade_kernel<COUNT, false><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
+                                                                                     res.counters);
         pf.end(stream);
         pf.begin(RT_K_SHADOW, stream);
         wf_shadow_kernel<COUNT><<<std::min(g_shw, need), 128, 0, stream>>>(sc, fp, v, res.counters);

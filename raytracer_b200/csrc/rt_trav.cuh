@@ -16,6 +16,10 @@
 
 namespace rt {
 
+// The per-ray part of the watertight test on its own, so that the packet kernel can keep several rays per lane
+// without the slab-test members of TravRay.
+struct Shear { float2 px, py, pz, cxy; };
+
 struct TravRay {
     float ox, oy, oz;
     float idx, idy, idz;   // 1/d (clamped for |d| < 1e-20)
@@ -23,7 +27,7 @@ struct TravRay {
     // mx = e_kx - Sx e_kz, my = e_ky - Sy e_kz, and cxy = (mx . o, my . o).
     // The entries that are exactly 0 or 1 make the fmaf chains below reproduce "pick a component" without
     // any per-triangle selects (the selects cost 54 ALU-pipe instructions per triangle before).
-    float2 px, py, pz, cxy;
+    Shear sh;
     uint32_t rbits;        // bits 0..2: sign bits of d (traversal octant); bits 3..4: dominant axis kz
 };
 
@@ -41,11 +45,11 @@ __device__ __forceinline__ TravRay trav_setup(vec3 o, vec3 d) {
     const float dz = kz == 0u ? d.x : (kz == 1u ? d.y : d.z);
     const float nSx = -(dkx / dz), nSy = -(dky / dz);
     // axis i is kx when i == (kz + 1) % 3, ky when i == (kz + 2) % 3
-    r.px = kz == 0u ? make_float2(nSx, nSy) : (kz == 1u ? make_float2(0.0f, 1.0f) : make_float2(1.0f, 0.0f));
-    r.py = kz == 0u ? make_float2(1.0f, 0.0f) : (kz == 1u ? make_float2(nSx, nSy) : make_float2(0.0f, 1.0f));
-    r.pz = kz == 0u ? make_float2(0.0f, 1.0f) : (kz == 1u ? make_float2(1.0f, 0.0f) : make_float2(nSx, nSy));
-    r.cxy.x = fmaf(o.z, r.pz.x, fmaf(o.y, r.py.x, o.x * r.px.x));
-    r.cxy.y = fmaf(o.z, r.pz.y, fmaf(o.y, r.py.y, o.x * r.px.y));
+    r.sh.px = kz == 0u ? make_float2(nSx, nSy) : (kz == 1u ? make_float2(0.0f, 1.0f) : make_float2(1.0f, 0.0f));
+    r.sh.py = kz == 0u ? make_float2(1.0f, 0.0f) : (kz == 1u ? make_float2(nSx, nSy) : make_float2(0.0f, 1.0f));
+    r.sh.pz = kz == 0u ? make_float2(0.0f, 1.0f) : (kz == 1u ? make_float2(1.0f, 0.0f) : make_float2(nSx, nSy));
+    r.sh.cxy.x = fmaf(o.z, r.sh.pz.x, fmaf(o.y, r.sh.py.x, o.x * r.sh.px.x));
+    r.sh.cxy.y = fmaf(o.z, r.sh.pz.y, fmaf(o.y, r.sh.py.y, o.x * r.sh.px.y));
     r.idx = (fabsf(d.x) >= 1e-20f) ? 1.0f / d.x : copysignf(1e20f, d.x);
     r.idy = (fabsf(d.y) >= 1e-20f) ? 1.0f / d.y : copysignf(1e20f, d.y);
     r.idz = (fabsf(d.z) >= 1e-20f) ? 1.0f / d.z : copysignf(1e20f, d.z);
@@ -54,15 +58,15 @@ __device__ __forceinline__ TravRay trav_setup(vec3 o, vec3 d) {
 }
 
 // sheared (x, y) of a vertex: three packed FFMA2 (sm_100 fma.rn.f32x2), each half rounded exactly like fmaf
-__device__ __forceinline__ float2 shear_xy(const TravRay& r, float4 q) {
+__device__ __forceinline__ float2 shear_xy(const Shear& r, float4 q) {
     float2 a = __ffma2_rn(make_float2(q.x, q.x), r.px, make_float2(-r.cxy.x, -r.cxy.y));
     a = __ffma2_rn(make_float2(q.y, q.y), r.py, a);
     return __ffma2_rn(make_float2(q.z, q.z), r.pz, a);
 }
 
-// Watertight intersection; returns false when the ray misses the triangle's plane projection.
-__device__ __forceinline__ bool tri_isect(const TravRay& r, float4 q0, float4 q1, float4 q2, float* t, float* u,
-                                          float* v) {
+// Edge functions of the sheared triangle; false when the ray misses.  det = (U + V) + W is non-zero on success.
+__device__ __forceinline__ bool tri_edges(const Shear& r, float4 q0, float4 q1, float4 q2, float* pU, float* pV, float* pW,
+                                          float* pdet) {
     const float2 A = shear_xy(r, q0), B = shear_xy(r, q1), C = shear_xy(r, q2);
     float U = C.x * B.y - C.y * B.x;
     float V = A.x * C.y - A.y * C.x;
@@ -73,18 +77,33 @@ __device__ __forceinline__ bool tri_isect(const TravRay& r, float4 q0, float4 q1
         W = (float)__dsub_rn(__dmul_rn((double)B.x, (double)A.y), __dmul_rn((double)B.y, (double)A.x));
     }
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
-    float det = (U + V) + W;
+    const float det = (U + V) + W;
     if (det == 0.0f) return false;
-    // distance: the hit point's coordinate along the dominant axis (barycentric mix of the three vertices),
-    // then t = (p_kz - o_kz) / d_kz.  Only lanes that pass the edge test get here.
-    const bool k0 = (r.rbits & 0x18u) == 0u, k1 = (r.rbits & 0x08u) != 0u;
+    *pU = U; *pV = V; *pW = W; *pdet = det;
+    return true;
+}
+
+// distance: the hit point's coordinate along the dominant axis kz (barycentric mix of the three vertices),
+// then t = (p_kz - o_kz) / d_kz.  kzbits: bit 0 = (kz == 1), bit 1 = (kz == 2).
+__device__ __forceinline__ void tri_finish(float U, float V, float W, float det, float4 q0, float4 q1, float4 q2, uint32_t kzbits,
+                                           float okz, float ikz, float* t, float* u, float* v) {
+    const bool k0 = kzbits == 0u, k1 = (kzbits & 1u) != 0u;
     const float Az = k0 ? q0.x : (k1 ? q0.y : q0.z), Bz = k0 ? q1.x : (k1 ? q1.y : q1.z), Cz = k0 ? q2.x : (k1 ? q2.y : q2.z);
-    const float okz = k0 ? r.ox : (k1 ? r.oy : r.oz), ikz = k0 ? r.idx : (k1 ? r.idy : r.idz);
-    float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
-    float inv = 1.0f / det;
+    const float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
+    const float inv = 1.0f / det;
     *t = (T * inv - okz) * ikz;
     *u = V * inv;
     *v = W * inv;
+}
+
+// Watertight intersection; returns false when the ray misses the triangle's plane projection.
+__device__ __forceinline__ bool tri_isect(const TravRay& r, float4 q0, float4 q1, float4 q2, float* t, float* u,
+                                          float* v) {
+    float U, V, W, det;
+    if (!tri_edges(r.sh, q0, q1, q2, &U, &V, &W, &det)) return false;
+    const uint32_t kzbits = (r.rbits >> 3) & 3u;
+    const bool k0 = kzbits == 0u, k1 = (kzbits & 1u) != 0u;
+    tri_finish(U, V, W, det, q0, q1, q2, kzbits, k0 ? r.ox : (k1 ? r.oy : r.oz), k0 ? r.idx : (k1 ? r.idy : r.idz), t, u, v);
     return true;
 }
 
