@@ -4,8 +4,8 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 Workload (config.workload): BASELINE.json configs[2] — Sponza 1920x1080, depth 8 (roulette from depth 3),
-one step = `--spp-per-step` accumulated frames (default 16, so the default 16 steps are the config's
-256 spp).  The Sponza geometry blob is absent from the reference mount, so the scene is the
+one step = `--spp-per-step` accumulated frames (default 256 = the config's whole 256-spp image, traced as
+batches of up to 64 frames in flight; the path-state arrays cap the batch at what fits 16 GiB).  The Sponza geometry blob is absent from the reference mount, so the scene is the
 deterministic "sponza-proxy" (raytracer_b200/proxy_scenes.py: same object/triangle/material counts).
 N > 1: screen tiles (8-row strips, rank r owns strip s when s % N == r), scene replicated, no
 collective on the data path; the strips are gathered over NCCL only for the end-to-end number.
@@ -14,7 +14,8 @@ collective on the data path; the strips are gathered over NCCL only for the end-
                pass) over K steps timed with CUDA events on the library's stream, inputs resident in HBM
   e2e          the same through the C ABI with HOST buffers: camera UBO from host memory each step and the
                RGBA32F image read back to (pinned) host memory each step
-  roofline     dominant kernel (wf_extend_kernel): algorithmic bytes / its CUDA-event time
+  roofline     dominant kernel (wf_extend_kernel: per-ray traversal of bounces >= 1): algorithmic bytes / its
+               CUDA-event time; roofline_packet: the same for the first-bounce packet kernel
   cpu_baseline the CPU oracle (a port: the reference has no CPU path) on a bounded sample, rank 0, N = 1
   --impl reference   times that CPU port with all host threads (the reference's Vulkan path cannot run here)
 """
@@ -42,7 +43,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=16)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=256)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--max-depth", type=int, default=8)
@@ -198,21 +199,30 @@ def run_ours(args):
     scene, cam = make_scene(args.scene, W, H)
     pipe = librt.RT_PIPELINE_WAVEFRONT if args.pipeline == "wavefront" else librt.RT_PIPELINE_MEGAKERNEL
     kw = dict(device=local_rank, max_depth=args.max_depth, rr_start_depth=3, pipeline=pipe, strip_rows=8, strip_index=rank,
-              strip_count=world, frames_in_flight=min(max(B, 1), 32))
+              strip_count=world, frames_in_flight=min(max(B, 1), 64))
     ctx = librt.Context(counters=False, **kw)
     info = ctx.build_scene(scene)
     ctx.resize(W, H)
     ubo = cam.ubo()
     f0 = Wm * B
 
-    # ---- ray counts of the timed frames: identical untimed pass on a counting context --------------------
-    # per-ray primary traversal here: node / triangle counts then follow the per-ray work definition
-    cctx = librt.Context(counters=True, per_ray_primary=True, **kw)
-    cctx.build_scene(scene)
-    cctx.resize(W, H)
-    cctx.trace_frames(ubo, CLEAR, f0, K * B)
-    cnt = cctx.counters()
-    cctx.close()
+    # ---- ray counts of the timed frames: identical untimed passes on counting contexts -------------------
+    # (a) per-ray primary traversal, full depth: the ray counts of `value` and the per-ray work definition of
+    #     SURVEY §8d; (b) the same at depth 1: (a) - (b) = nodes / triangles of the bounces >= 1, which is what
+    #     wf_extend_kernel traces; (c) depth 1 with packets: what the packet kernel really fetches.
+    def count(per_ray, depth):
+        k2 = dict(kw, max_depth=depth)
+        c = librt.Context(counters=True, per_ray_primary=per_ray, **k2)
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(ubo, CLEAR, f0, K * B)
+        out = c.counters()
+        c.close()
+        return out
+
+    cnt = count(True, args.max_depth)
+    cnt1 = count(True, 1)
+    cntp = count(False, 1)
     rays_local = cnt["extend_rays"] + cnt["shadow_rays"]
     rays_total = reduce_scalar(float(rays_local), "SUM")
 
@@ -238,6 +248,7 @@ def run_ours(args):
 
     # ---- per-kernel times (CUDA events around every launch, separate pass over the same frames) -----------
     roof = None
+    roof_pkt = None
     kprof = None
     if pipe == librt.RT_PIPELINE_WAVEFRONT:
         ctx.set_profiling(True)
@@ -245,31 +256,48 @@ def run_ours(args):
             ctx.trace_frames(ubo, CLEAR, f0 + s * B, B)
         kprof = ctx.kernel_profile()
         ctx.set_profiling(False)
-        ext = kprof["extend"]
-        ext_nodes, ext_tris = cnt["nodes"] - cnt["shadow_nodes"], cnt["tris"] - cnt["shadow_tris"]
-        # algorithmic bytes of the extend kernel: BVH8 nodes 128 B + triangles 48 B fetched, ray in 32 B, hit out 16 B
-        alg_bytes = ext_nodes * 128 + ext_tris * 48 + cnt["extend_rays"] * 48
+        ext, pkt = kprof["extend"], kprof["extend_packet"]
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        achieved = alg_bytes / (ext["ms"] * 1e-3) / 1e9 if ext["ms"] > 0 else 0.0
         total_k = sum(v["ms"] for v in kprof.values())
+
+        def alg(c):  # BVH8 nodes 128 B + triangles 48 B fetched by closest-hit rays, ray in 32 B, hit out 16 B
+            return (c["nodes"] - c["shadow_nodes"]) * 128 + (c["tris"] - c["shadow_tris"]) * 48 + c["extend_rays"] * 48
+
+        sec_rays = cnt["extend_rays"] - cnt1["extend_rays"]
+        alg_sec = alg(cnt) - alg(cnt1)
+        achieved = alg_sec / (ext["ms"] * 1e-3) / 1e9 if ext["ms"] > 0 else 0.0
         traffic = None
         try:  # dram__bytes_read+write per ray of the last committed `ncu --set full` capture of this kernel
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_kernel"]
-            traffic = tj["dram_bytes_per_ray"] * cnt["extend_rays"] / max(ext["launches"], 1)
+            traffic = tj["dram_bytes_per_ray"] * sec_rays / max(ext["launches"], 1)
         except Exception:
             pass
-        roof = {"bound": "hbm", "kernel": "wf_extend_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        roof = {"bound": "hbm", "kernel": "wf_extend_kernel (per-ray closest hit, bounces 1..%d)" % (args.max_depth - 1),
+                "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": "measured" if "hbm_gbs" in peaks else "fallback",
                 "launches": ext["launches"], "avg_launch_ms": ext["ms"] / max(ext["launches"], 1),
-                "alg_bytes_per_launch": alg_bytes / max(ext["launches"], 1),
-                "bytes_per_extend_ray": alg_bytes / max(cnt["extend_rays"], 1),
+                "alg_bytes_per_launch": alg_sec / max(ext["launches"], 1),
+                "bytes_per_ray": alg_sec / max(sec_rays, 1), "rays_per_launch": sec_rays / max(ext["launches"], 1),
                 "share_of_step": ext["ms"] / total_k if total_k > 0 else None,
+                "note": "the BVH (< 20 MB) is L2/L1-resident, so algorithmic bytes / time is a bookkeeping ratio against the "
+                        "HBM copy peak, not a DRAM utilisation; `traffic` is the DRAM figure",
                 "kernel_ms": {k: round(v["ms"], 3) for k, v in kprof.items()}}
+        if pkt["launches"]:
+            a_ray, a_pkt = alg(cnt1), alg(cntp)
+            roof_pkt = {"kernel": "wf_extend_packet_kernel (first bounce, 128 rays per warp)", "launches": pkt["launches"],
+                        "avg_launch_ms": pkt["ms"] / pkt["launches"], "share_of_step": pkt["ms"] / total_k if total_k > 0 else None,
+                        "per_ray_alg_bytes_per_launch": a_ray / pkt["launches"],
+                        "achieved_per_ray_definition": a_ray / (pkt["ms"] * 1e-3) / 1e9,
+                        "fetched_bytes_per_launch": a_pkt / pkt["launches"],
+                        "achieved_fetched": a_pkt / (pkt["ms"] * 1e-3) / 1e9, "unit": "GB/s", "peak": peak,
+                        "rays_per_launch": cnt1["extend_rays"] / pkt["launches"]}
+        else:
+            roof_pkt = None
 
     # ---- end to end through the C ABI with host buffers ------------------------------------------------
     host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
@@ -338,6 +366,8 @@ def run_ours(args):
                 "gpu_launches": int(launches), "clocks": sampler.summary()}
         if roof:
             line["roofline"] = roof
+            if roof_pkt:
+                line["roofline_packet"] = roof_pkt
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)

@@ -239,7 +239,9 @@ RT_API int rt_event_record(rt_ctx* ctx, int which);
 RT_API int rt_event_elapsed_ms(rt_ctx* ctx, float* ms);
 /* per-kernel device times of the wavefront pipeline: when enabled, every launch is bracketed by CUDA
  * events on the launching stream; rt_get_kernel_profile sums them since the last enable/reset. */
-enum { RT_K_RAYGEN = 0, RT_K_EXTEND = 1, RT_K_SHADE = 2, RT_K_SHADOW = 3, RT_K_ACCUMULATE = 4, RT_K_COUNT = 5 };
+/* RT_K_EXTEND: per-ray closest-hit traversal (all bounces but the first, and first-bounce tiles the packet kernel
+ * hands back); RT_K_EXTEND_PACKET: first bounce traced as packets */
+enum { RT_K_RAYGEN = 0, RT_K_EXTEND = 1, RT_K_SHADE = 2, RT_K_SHADOW = 3, RT_K_ACCUMULATE = 4, RT_K_EXTEND_PACKET = 5, RT_K_COUNT = 6 };
 typedef struct rt_kernel_profile {
     float ms[RT_K_COUNT];
     uint32_t launches[RT_K_COUNT];

@@ -752,15 +752,18 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     for (int depth = 0; depth < fp.max_depth; depth++) {
         wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, q_in, depth == 0 ? n_slots : 0xFFFFFFFFu);
         const uint32_t* qi = depth == 0 ? nullptr : w->queue[q_in].p;
-        pf.begin(RT_K_EXTEND, stream);
         if (depth == 0 && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
             // packets first; what they hand back (tiles across an axis plane) goes through the per-ray kernel
+            pf.begin(RT_K_EXTEND_PACKET, stream);
             wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, v, w->queue[0].p, fp.width, n_px,
                                                                                      res.counters);
+            pf.end(stream);
+            pf.begin(RT_K_EXTEND, stream);
             wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, w->queue[0].p, CT_FB, fp.width, n_px,
                                                                                res.counters);
             n_launch++;
         } else {
+            pf.begin(RT_K_EXTEND, stream);
             wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, fp.width, n_px, res.counters);
         }
         pf.end(stream);

@@ -61,11 +61,11 @@ class RtCounters(C.Structure):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
 
 
-KERNEL_NAMES = ("raygen", "extend", "shade", "shadow", "accumulate")
+KERNEL_NAMES = ("raygen", "extend", "shade", "shadow", "accumulate", "extend_packet")
 
 
 class RtKernelProfile(C.Structure):
-    _fields_ = [("ms", C.c_float * 5), ("launches", C.c_uint32 * 5)]
+    _fields_ = [("ms", C.c_float * 6), ("launches", C.c_uint32 * 6)]
 
 
 class RtSceneInfo(C.Structure):
