@@ -352,6 +352,85 @@ __global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_extend_kernel(Scen
     }
 }
 
+// extend, cooperative triangle tests (rt_trav.cuh: coop_*): the kernel for incoherent rays (bounces >= 1 and what the
+// packet kernel hands back).  The loop is warp-uniform: lanes without a ray skip the node step but take their share
+// of the pooled triangle tests.
+#ifndef RT_COOP_MIN_BLOCKS
+#define RT_COOP_MIN_BLOCKS 8
+#endif
+template <bool COUNT>
+__global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel(SceneView sc, WfView wf, const uint32_t* queue,
+                                                                                 uint32_t q_idx, uint32_t width, uint32_t n_px,
+                                                                                 DevCounters* counters) {
+    __shared__ CoopWarp s_cw[4];
+    const uint32_t n = wf.ctrl[q_idx];
+    const uint32_t lane = threadIdx.x & 31u;
+    CoopWarp& cw = s_cw[threadIdx.x >> 5];
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    WarpFetch wfetch;
+    wfetch.next = wfetch.end = 0u;
+    wfetch.drained = false;
+    NodeRay nr;
+    nr.ox = nr.oy = nr.oz = nr.idx = nr.idy = nr.idz = 0.0f; nr.oct = 0u;
+    TravStack stk;
+    uint2 ng = make_uint2(0u, 0u);
+    int sp = 0;
+    float best_t = 0.0f;
+    bool has_ray = false;
+    uint32_t slot = 0;
+    for (;;) {
+        const uint32_t i = warp_fetch(wfetch, &wf.ctrl[CT_CUR_EXT], n, !has_ray);
+        if (i != 0xFFFFFFFFu) {
+            slot = queue ? queue[i] : primary_slot(i, width, n_px);
+            const float4 o = wf.ray_o[slot], d = wf.ray_d[slot];
+            const TravRay r = trav_setup(mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z));
+            coop_init_ray(cw, lane, r, 10000.0f);
+            nr.ox = r.ox; nr.oy = r.oy; nr.oz = r.oz; nr.idx = r.idx; nr.idy = r.idy; nr.idz = r.idz; nr.oct = r.rbits & 7u;
+            ng = make_uint2(0u, 0x80000000u);
+            sp = 0;
+            best_t = 10000.0f;
+            has_ray = true;
+            c_rays++;
+        }
+        __syncwarp();
+        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) break;
+        // while the queue still has entries, return to the fetch once enough lanes are idle
+        const uint32_t max_idle = wfetch.drained ? 31u : (RT_REFILL_IDLE - 1u);
+        for (;;) {
+            uint32_t tmask = 0u, tbase = 0u;
+            if (has_ray) tmask = coop_node<COUNT>(sc, nr, ng, sp, stk, 0.001f, best_t, &tbase, c_nodes);
+            coop_triangles<COUNT>(sc, cw, lane, tmask, tbase, 0.001f, c_tris);
+            if (has_ray) {
+                best_t = __uint_as_float((uint32_t)(cw.key[lane] >> 32));
+                if (!(ng.y & 0xFF000000u)) {
+                    if (sp == 0) {  // traversal complete
+                        const uint32_t ti = cw.tri[lane];
+                        uint32_t inst = 0xFFFFFFFFu, prim = 0u;
+                        float2 uv = make_float2(0.0f, 0.0f);
+                        if (ti != 0xFFFFFFFFu) {
+                            const float* tq = reinterpret_cast<const float*>(sc.tris + (size_t)ti * 3u);
+                            inst = __float_as_uint(__ldg(tq + 7));
+                            prim = __float_as_uint(__ldg(tq + 11));
+                            uv = cw.uv[lane];
+                        }
+                        wf.hit[slot] = make_uint4(__float_as_uint(uv.x), __float_as_uint(uv.y), inst, prim);
+                        has_ray = false;
+                    } else {
+                        ng = stk.e[--sp];
+                    }
+                }
+            }
+            const uint32_t live = __ballot_sync(0xFFFFFFFFu, has_ray);
+            if (32u - (uint32_t)__popc(live) > max_idle) break;
+        }
+    }
+    if (COUNT) {
+        warp_add(&counters->extend_rays, c_rays);
+        warp_add(&counters->nodes, c_nodes);
+        warp_add(&counters->tris, c_tris);
+    }
+}
+
 // ---- primary rays as packets ------------------------------------------------------------------------
 // The primary rays of a screen tile leave the same point and differ by a fraction of a degree, so a warp walks
 // the BVH ONCE for RT_PKT_RPL x 32 of them (RT_PKT_RPL horizontally adjacent 4 x 8 tiles of one frame, see
@@ -730,8 +809,12 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     v.ray_o = w->ray_o.p; v.ray_d = w->ray_d.p; v.thr = w->thr.p; v.col = w->col.p; v.prev = w->prev.p;
     v.seeds = w->seeds.p; v.hit = w->hit.p; v.sh_o = w->sh_o.p; v.sh_d = w->sh_d.p; v.sh_c = w->sh_c.p; v.sh_e = w->sh_e.p;
     v.ctrl = w->ctrl.p;
-    static int g_ext = 0, g_shw = 0, g_shd = 0, g_pkt = 0;
+#ifndef RT_EXTEND_COOP
+#define RT_EXTEND_COOP 1
+#endif
+    static int g_ext = 0, g_shw = 0, g_shd = 0, g_pkt = 0, g_coop = 0;
     if (!g_ext) {
+        g_coop = persistent_grid(wf_extend_coop_kernel<COUNT>, 128);
         g_pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128);
         g_ext = persistent_grid(wf_extend_kernel<COUNT>, 128);
         g_shw = persistent_grid(wf_shadow_kernel<COUNT>, 128);
@@ -759,12 +842,19 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
                                                                                      res.counters);
             pf.end(stream);
             pf.begin(RT_K_EXTEND, stream);
-            wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, w->queue[0].p, CT_FB, fp.width, n_px,
-                                                                               res.counters);
+            if (RT_EXTEND_COOP)
+                wf_extend_coop_kernel<COUNT><<<std::min(g_coop, need), 128, 0, stream>>>(sc, v, w->queue[0].p, CT_FB, fp.width, n_px,
+                                                                                        res.counters);
+            else
+                wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, w->queue[0].p, CT_FB, fp.width, n_px,
+                                                                                   res.counters);
             n_launch++;
         } else {
             pf.begin(RT_K_EXTEND, stream);
-            wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, fp.width, n_px, res.counters);
+            if (RT_EXTEND_COOP)
+                wf_extend_coop_kernel<COUNT><<<std::min(g_coop, need), 128, 0, stream>>>(sc, v, qi, q_in, fp.width, n_px, res.counters);
+            else
+                wf_extend_kernel<COUNT><<<std::min(g_ext, need), 128, 0, stream>>>(sc, v, qi, q_in, fp.width, n_px, res.counters);
         }
         pf.end(stream);
         pf.begin(RT_K_SHADE, stream);

@@ -161,6 +161,18 @@ __device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, co
     return mask;
 }
 
+#ifndef RT_NODE_LDG256
+#define RT_NODE_LDG256 0
+#endif
+__device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ uint4 sel4(bool c, uint4 a, uint4 b) {
+    return make_uint4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
+}
+
 // One ray per lane with a (base, mask) group stack.  The traversal is a resumable state machine so that the
 // persistent kernels can swap a finished ray for a new one without waiting for the rest of the warp; one
 // step = one node (its eight child boxes), all triangles that node references directly, and a stack pop.
@@ -201,10 +213,23 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
     const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
     // near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one
     const uint32_t sx = r.rbits & 1u, sy = (r.rbits >> 1) & 1u, sz = (r.rbits >> 2) & 1u;
+#if RT_NODE_LDG256
+    // four 256-bit loads per node (sm_100 LDG.256): half the L1 tag lookups of eight 128-bit loads when the lanes
+    // of a warp sit in different nodes; the near / far planes are then picked by register selects
+    uint4 w0, w1, lx, hx, ly, hy, lz, hz;
+    ldg256(np, w0, w1);
+    ldg256(np + 2, lx, hx);
+    ldg256(np + 4, ly, hy);
+    ldg256(np + 6, lz, hz);
+    const uint4 nx = sel4(sx != 0u, hx, lx), fx = sel4(sx != 0u, lx, hx);
+    const uint4 ny = sel4(sy != 0u, hy, ly), fy = sel4(sy != 0u, ly, hy);
+    const uint4 nz = sel4(sz != 0u, hz, lz), fz = sel4(sz != 0u, lz, hz);
+#else
     const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
     const uint4 nx = __ldg(np + 2 + sx), fx = __ldg(np + 3 - sx);
     const uint4 ny = __ldg(np + 4 + sy), fy = __ldg(np + 5 - sy);
     const uint4 nz = __ldg(np + 6 + sz), fz = __ldg(np + 7 - sz);
+#endif
     if (COUNT) n_nodes++;
     const uint32_t hm = node_hits(w0, w1, nx, fx, ny, fy, nz, fz, r, st.tmin, st.best.t);
     ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
@@ -239,6 +264,139 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
     }
     st.ng = ng;
     return false;
+}
+
+// ---- warp-cooperative triangle tests (closest hit) --------------------------------------------------
+// With incoherent rays only a few lanes of a warp reach triangles in the same node step, and each runs its own
+// loop over them: ncu showed half of the kernel's warp instructions issued in that loop with 2 of 32 lanes
+// active, every iteration exposing one more load latency.  Here the (ray, triangle) pairs of all lanes are
+// pooled in shared memory after each node step and dealt out evenly: lane w tests pair w for whichever lane
+// owns it.  The owner's closest hit lives in shared memory as one 64-bit key (t bits << 32 | flat id): an
+// unsigned atomicMin on it IS the (t, id)-lexicographic rule of the per-lane loop (t > 0, so the bit patterns
+// order like the floats), hence the same hit record bit for bit.
+#ifndef RT_COOP_ITEMS
+#define RT_COOP_ITEMS 256  /* pairs pooled per node step and warp; more than that (never seen) falls back to per-lane tests */
+#endif
+struct CoopWarp {
+    unsigned long long key[32];  // t bits << 32 | flat triangle id of the closest accepted hit; (tmax bits << 32) = none yet
+    float4 ra[32];               // shear px.x px.y py.x py.y
+    float4 rb[32];               // shear pz.x pz.y cxy.x cxy.y
+    float4 rc[32];               // o_kz, 1/d_kz, kz bits, -
+    float2 uv[32];               // barycentrics of the hit in `key`
+    uint32_t tri[32];            // its index in the BVH triangle array, 0xFFFFFFFF = miss
+    uint32_t items[RT_COOP_ITEMS];  // triangle index | owner lane << 27
+};
+
+// slim per-lane state of the cooperative kernel: everything the node test needs, nothing of the triangle test
+struct NodeRay {
+    float ox, oy, oz, idx, idy, idz;
+    uint32_t oct;
+};
+
+__device__ __forceinline__ void coop_init_ray(CoopWarp& cw, uint32_t lane, const TravRay& r, float tmax) {
+    cw.key[lane] = (unsigned long long)__float_as_uint(tmax) << 32;
+    cw.ra[lane] = make_float4(r.sh.px.x, r.sh.px.y, r.sh.py.x, r.sh.py.y);
+    cw.rb[lane] = make_float4(r.sh.pz.x, r.sh.pz.y, r.sh.cxy.x, r.sh.cxy.y);
+    const uint32_t kzbits = (r.rbits >> 3) & 3u;
+    const bool k0 = kzbits == 0u, k1 = (kzbits & 1u) != 0u;
+    cw.rc[lane] = make_float4(k0 ? r.ox : (k1 ? r.oy : r.oz), k0 ? r.idx : (k1 ? r.idy : r.idz), __uint_as_float(kzbits), 0.0f);
+    cw.tri[lane] = 0xFFFFFFFFu;
+}
+
+// one (ray of lane `owner`, triangle ti) pair; returns the key offered (0 = nothing offered)
+__device__ __forceinline__ unsigned long long coop_test(const SceneView& sc, CoopWarp& cw, uint32_t owner, uint32_t ti, float tmin,
+                                                        float* uu, float* vv) {
+    const float4* tp = sc.tris + (size_t)ti * 3u;
+    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+    const float4 a = cw.ra[owner], b = cw.rb[owner], c = cw.rc[owner];
+    Shear sh;
+    sh.px = make_float2(a.x, a.y); sh.py = make_float2(a.z, a.w); sh.pz = make_float2(b.x, b.y); sh.cxy = make_float2(b.z, b.w);
+    float U, V, W, det;
+    if (!tri_edges(sh, q0, q1, q2, &U, &V, &W, &det)) return 0ull;
+    float tt;
+    tri_finish(U, V, W, det, q0, q1, q2, __float_as_uint(c.z), c.x, c.y, &tt, uu, vv);
+    if (!(tt > tmin)) return 0ull;
+    const unsigned long long key = ((unsigned long long)__float_as_uint(tt) << 32) | __float_as_uint(q0.w);
+    const unsigned long long old = atomicMin(&cw.key[owner], key);
+    return key < old ? key : 0ull;
+}
+
+// All 32 lanes call this after a node step; tmask / tbase: the lane's triangle bits and triangle base (0 when the
+// lane has no ray).  On return every owner's closest hit (key, tri, uv) includes the pooled triangles.
+template <bool COUNT>
+__device__ __forceinline__ void coop_triangles(const SceneView& sc, CoopWarp& cw, uint32_t lane, uint32_t tmask, uint32_t tbase,
+                                               float tmin, uint32_t& n_tris) {
+    const uint32_t cnt = __popc(tmask);
+    uint32_t pre = cnt;  // inclusive scan of the counts
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, pre, o);
+        if (lane >= (uint32_t)o) pre += v;
+    }
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, pre, 31);
+    if (total == 0u) return;
+    if (total <= RT_COOP_ITEMS) {
+        uint32_t pos = pre - cnt;
+        while (tmask) {
+            const uint32_t tb = __ffs(tmask) - 1;
+            tmask &= tmask - 1u;
+            cw.items[pos++] = (tbase + tb) | (lane << 27);
+        }
+        __syncwarp();
+        for (uint32_t base = 0; base < total; base += 32u) {
+            const uint32_t w = base + lane;
+            unsigned long long key = 0ull;
+            uint32_t owner = 0, ti = 0;
+            float uu = 0.0f, vv = 0.0f;
+            if (w < total) {
+                const uint32_t item = cw.items[w];
+                owner = item >> 27;
+                ti = item & 0x07FFFFFFu;
+                if (COUNT) n_tris++;
+                key = coop_test(sc, cw, owner, ti, tmin, &uu, &vv);
+            }
+            __syncwarp();
+            // of the lanes that lowered an owner's key this round, the one whose key stayed publishes the rest
+            if (key != 0ull && cw.key[owner] == key) { cw.tri[owner] = ti; cw.uv[owner] = make_float2(uu, vv); }
+            __syncwarp();
+        }
+    } else {  // more pairs than the pool holds: every lane tests its own triangles
+        while (tmask) {
+            const uint32_t tb = __ffs(tmask) - 1;
+            tmask &= tmask - 1u;
+            float uu, vv;
+            if (COUNT) n_tris++;
+            const unsigned long long key = coop_test(sc, cw, lane, tbase + tb, tmin, &uu, &vv);
+            if (key != 0ull) { cw.tri[lane] = tbase + tb; cw.uv[lane] = make_float2(uu, vv); }
+        }
+        __syncwarp();
+    }
+}
+
+// node part of a traversal step for the cooperative kernel: pop the next child, slab-test its eight boxes.
+// ng / sp / stk as in TravState; returns the triangle bits, *tbase the node's triangle base.
+template <bool COUNT>
+__device__ __forceinline__ uint32_t coop_node(const SceneView& sc, const NodeRay& nr, uint2& ng_io, int& sp, TravStack& stk,
+                                              float tmin, float tmax, uint32_t* tbase, uint32_t& n_nodes) {
+    TravRay r;  // node_hits reads only the members set here
+    r.ox = nr.ox; r.oy = nr.oy; r.oz = nr.oz; r.idx = nr.idx; r.idy = nr.idy; r.idz = nr.idz; r.rbits = nr.oct;
+    uint2 ng = ng_io;
+    const int bit = 31 - __clz(ng.y);
+    ng.y &= ~(1u << bit);
+    const uint32_t slot = ((uint32_t)bit - 24u) ^ nr.oct;
+    const uint32_t node = ng.x + __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
+    if (ng.y & 0xFF000000u) stk.e[sp++] = ng;
+    const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
+    const uint32_t sx = nr.oct & 1u, sy = (nr.oct >> 1) & 1u, sz = (nr.oct >> 2) & 1u;
+    const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
+    const uint4 nx = __ldg(np + 2 + sx), fx = __ldg(np + 3 - sx);
+    const uint4 ny = __ldg(np + 4 + sy), fy = __ldg(np + 5 - sy);
+    const uint4 nz = __ldg(np + 6 + sz), fz = __ldg(np + 7 - sz);
+    if (COUNT) n_nodes++;
+    const uint32_t hm = node_hits(w0, w1, nx, fx, ny, fy, nz, fz, r, tmin, tmax);
+    ng_io = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
+    *tbase = w1.y;
+    return hm & 0x00FFFFFFu;
 }
 
 template <bool ANY, bool COUNT>
