@@ -162,7 +162,7 @@ __device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, co
 }
 
 #ifndef RT_NODE_LDG256
-#define RT_NODE_LDG256 0
+#define RT_NODE_LDG256 1
 #endif
 __device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
     asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -171,6 +171,29 @@ __device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
 }
 __device__ __forceinline__ uint4 sel4(bool c, uint4 a, uint4 b) {
     return make_uint4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
+}
+
+// One node = one 128-byte line: header words w0, w1 and, per axis, the near and far plane vectors for this ray's
+// direction signs (near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one).
+__device__ __forceinline__ void load_node(const uint4* np, uint32_t sx, uint32_t sy, uint32_t sz, uint4& w0, uint4& w1, uint4& nx,
+                                          uint4& fx, uint4& ny, uint4& fy, uint4& nz, uint4& fz) {
+#if RT_NODE_LDG256
+    // four 256-bit loads per node (sm_100 LDG.256) instead of eight 128-bit ones: fewer L1 requests when the lanes
+    // of a warp sit in different nodes; the near / far planes are then picked by register selects
+    uint4 lx, hx, ly, hy, lz, hz;
+    ldg256(np, w0, w1);
+    ldg256(np + 2, lx, hx);
+    ldg256(np + 4, ly, hy);
+    ldg256(np + 6, lz, hz);
+    nx = sel4(sx != 0u, hx, lx); fx = sel4(sx != 0u, lx, hx);
+    ny = sel4(sy != 0u, hy, ly); fy = sel4(sy != 0u, ly, hy);
+    nz = sel4(sz != 0u, hz, lz); fz = sel4(sz != 0u, lz, hz);
+#else
+    w0 = __ldg(np); w1 = __ldg(np + 1);
+    nx = __ldg(np + 2 + sx); fx = __ldg(np + 3 - sx);
+    ny = __ldg(np + 4 + sy); fy = __ldg(np + 5 - sy);
+    nz = __ldg(np + 6 + sz); fz = __ldg(np + 7 - sz);
+#endif
 }
 
 // One ray per lane with a (base, mask) group stack.  The traversal is a resumable state machine so that the
@@ -213,23 +236,8 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
     const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
     // near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one
     const uint32_t sx = r.rbits & 1u, sy = (r.rbits >> 1) & 1u, sz = (r.rbits >> 2) & 1u;
-#if RT_NODE_LDG256
-    // four 256-bit loads per node (sm_100 LDG.256): half the L1 tag lookups of eight 128-bit loads when the lanes
-    // of a warp sit in different nodes; the near / far planes are then picked by register selects
-    uint4 w0, w1, lx, hx, ly, hy, lz, hz;
-    ldg256(np, w0, w1);
-    ldg256(np + 2, lx, hx);
-    ldg256(np + 4, ly, hy);
-    ldg256(np + 6, lz, hz);
-    const uint4 nx = sel4(sx != 0u, hx, lx), fx = sel4(sx != 0u, lx, hx);
-    const uint4 ny = sel4(sy != 0u, hy, ly), fy = sel4(sy != 0u, ly, hy);
-    const uint4 nz = sel4(sz != 0u, hz, lz), fz = sel4(sz != 0u, lz, hz);
-#else
-    const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
-    const uint4 nx = __ldg(np + 2 + sx), fx = __ldg(np + 3 - sx);
-    const uint4 ny = __ldg(np + 4 + sy), fy = __ldg(np + 5 - sy);
-    const uint4 nz = __ldg(np + 6 + sz), fz = __ldg(np + 7 - sz);
-#endif
+    uint4 w0, w1, nx, fx, ny, fy, nz, fz;
+    load_node(np, sx, sy, sz, w0, w1, nx, fx, ny, fy, nz, fz);
     if (COUNT) n_nodes++;
     const uint32_t hm = node_hits(w0, w1, nx, fx, ny, fy, nz, fz, r, st.tmin, st.best.t);
     ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
@@ -388,10 +396,8 @@ __device__ __forceinline__ uint32_t coop_node(const SceneView& sc, const NodeRay
     if (ng.y & 0xFF000000u) stk.e[sp++] = ng;
     const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
     const uint32_t sx = nr.oct & 1u, sy = (nr.oct >> 1) & 1u, sz = (nr.oct >> 2) & 1u;
-    const uint4 w0 = __ldg(np), w1 = __ldg(np + 1);
-    const uint4 nx = __ldg(np + 2 + sx), fx = __ldg(np + 3 - sx);
-    const uint4 ny = __ldg(np + 4 + sy), fy = __ldg(np + 5 - sy);
-    const uint4 nz = __ldg(np + 6 + sz), fz = __ldg(np + 7 - sz);
+    uint4 w0, w1, nx, fx, ny, fy, nz, fz;
+    load_node(np, sx, sy, sz, w0, w1, nx, fx, ny, fy, nz, fz);
     if (COUNT) n_nodes++;
     const uint32_t hm = node_hits(w0, w1, nx, fx, ny, fy, nz, fz, r, tmin, tmax);
     ng_io = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
