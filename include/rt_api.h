@@ -201,6 +201,12 @@ RT_API int rt_trace_frame(rt_ctx* ctx, const float camera_ubo[64], const float c
  * (application loop, application.odin:109-115); lets terminated paths regenerate across frames. */
 RT_API int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
                     uint32_t n_frames);
+/* spp slices (the alternative to screen strips): traces the frames first_frame + k * frame_stride,
+ * k < n_frames, and folds them into the image as samples first_sample + k (0 restarts the mean).  Rank r of N
+ * calls it with first_frame = r, frame_stride = N; the ranks' means are then combined as sum(n_r / n * mean_r)
+ * (raytracer_b200.multi_gpu.SppSliceReduce: one NCCL reduce).  Same estimator, float sums in another order. */
+RT_API int rt_trace_frames_sliced(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
+                                  uint32_t n_frames, uint32_t frame_stride, uint32_t first_sample);
 RT_API int rt_synchronize(rt_ctx* ctx);
 
 /* ---- consume ----------------------------------------------------------------------------

@@ -367,6 +367,8 @@ void rt_fill_frame_params(const rt_ctx* ctx, const float* cam, const float* clea
     if (clear) memcpy(fp->clear, clear, 12); else fp->clear[0] = fp->clear[1] = fp->clear[2] = 0.0f;
     fp->frame = frame;
     fp->n_lanes = 1;
+    fp->frame_stride = 1;
+    fp->sample = frame;
     fp->width = ctx->width;
     fp->height = ctx->height;
     fp->strip_rows = ctx->cfg.strip_rows;
@@ -425,10 +427,12 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     return RT_OK;
 }
 
-int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
-                    uint32_t n_frames) {
+// Frames first_frame + k * frame_stride (k < n_frames) folded into the image as samples first_sample + k.
+static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
+                             uint32_t n_frames, uint32_t frame_stride, uint32_t first_sample) {
     CTX_CHECK(ctx);
     if (!camera_ubo || !clear_color) { set_error("rt_trace_frame: null argument"); return RT_ERR_INVALID_ARGUMENT; }
+    if (frame_stride == 0) { set_error("rt_trace_frames_sliced: frame_stride must be >= 1"); return RT_ERR_INVALID_ARGUMENT; }
     int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     rc = rt_require_target(ctx);
@@ -445,7 +449,9 @@ int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     const bool mega = ctx->cfg.pipeline == RT_PIPELINE_MEGAKERNEL;
     for (uint32_t f = 0; f < n_frames;) {
         FrameParams fp;
-        rt_fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f, &fp);
+        rt_fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f * frame_stride, &fp);
+        fp.frame_stride = frame_stride;
+        fp.sample = first_sample + f;
         fp.n_lanes = mega ? 1u : std::min(ctx->lanes, n_frames - f);
         rc = mega ? launch_frame_megakernel(sc, fp, res, ctx->stream, err) : launch_frame_wavefront(sc, fp, res, ctx->stream, err);
         if (rc != RT_OK) { set_error(err); return rc; }
@@ -454,6 +460,16 @@ int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     ctx->frames_traced += n_frames;
     rt_end_timing(ctx);
     return RT_OK;
+}
+
+int rt_trace_frames(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
+                    uint32_t n_frames) {
+    return trace_frames_impl(ctx, camera_ubo, clear_color, first_frame, n_frames, 1u, first_frame);
+}
+
+int rt_trace_frames_sliced(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
+                           uint32_t n_frames, uint32_t frame_stride, uint32_t first_sample) {
+    return trace_frames_impl(ctx, camera_ubo, clear_color, first_frame, n_frames, frame_stride, first_sample);
 }
 
 int rt_trace_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t frame_number) {

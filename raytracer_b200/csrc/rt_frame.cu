@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(128) megakernel_frame(SceneView sc, FrameParam
             }
             if (throughput_dead(ps.throughput)) break;
         }
-        image[slot] = accumulate_pixel(fp.frame ? image[slot] : make_float4(0.f, 0.f, 0.f, 0.f), ps.color, fp.clamp, fp.frame);
+        image[slot] = accumulate_pixel(fp.sample ? image[slot] : make_float4(0.f, 0.f, 0.f, 0.f), ps.color, fp.clamp, fp.sample);
     }
     if (COUNT) {
         warp_add(&counters->extend_rays, c_ext); warp_add(&counters->shadow_rays, c_sh);
@@ -229,7 +229,7 @@ __global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_cou
 }
 
 // raygen: simple.rgen:70-85.  All slots enter bounce 0 (unless roulette is enabled from depth 0).
-// A launch covers fp.n_lanes consecutive frames ("lanes"): slot = lane * pixels + pixel, frame = fp.frame + lane.
+// A launch covers fp.n_lanes consecutive frames ("lanes"): slot = lane * pixels + pixel, frame = fp.frame + lane * fp.frame_stride.
 __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView wf) {
     const uint32_t n_px = fp.local_rows * fp.width;
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView w
     const uint32_t lane_f = slot / n_px, px = slot - lane_f * n_px;
     const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
     const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
-    fp.frame += lane_f;
+    fp.frame += lane_f * fp.frame_stride;
     PathState ps;
     vec3 o, d;
     raygen_init(fp, x, y, ps, &o, &d);
@@ -782,10 +782,10 @@ __global__ void __launch_bounds__(256) wf_accumulate_kernel(FrameParams fp, WfVi
     const uint32_t n_px = fp.local_rows * fp.width;
     const uint32_t px = blockIdx.x * blockDim.x + threadIdx.x;
     if (px >= n_px) return;
-    float4 acc = fp.frame ? image[px] : make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 acc = fp.sample ? image[px] : make_float4(0.f, 0.f, 0.f, 0.f);
     for (uint32_t l = 0; l < fp.n_lanes; l++) {
         const float4 c = wf.col[(size_t)l * n_px + px];
-        acc = accumulate_pixel(acc, mk3(c.x, c.y, c.z), fp.clamp, fp.frame + l);
+        acc = accumulate_pixel(acc, mk3(c.x, c.y, c.z), fp.clamp, fp.sample + l);
     }
     image[px] = acc;
 }

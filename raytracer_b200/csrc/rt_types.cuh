@@ -103,7 +103,9 @@ struct FrameParams {
     float inv_proj[16];
     float clear[3];
     uint32_t frame;                                 // first frame of the launch
-    uint32_t n_lanes;                               // consecutive frames traced together (wavefront pipeline)
+    uint32_t n_lanes;                               // frames traced together (wavefront pipeline): frame + l * frame_stride
+    uint32_t frame_stride;                          // 1, or the world size when ranks take spp slices
+    uint32_t sample;                                // running-mean index of lane 0 (simple.rgen:127-136); == frame unless sliced
     uint32_t width, height;
     uint32_t strip_rows, strip_index, strip_count;  // rows owned: (y / strip_rows) % strip_count == strip_index
     uint32_t local_rows;                            // rows in this context's compact image

@@ -29,7 +29,7 @@ NODE_BYTES, TRI_BYTES = 128, 48  # Node8 / BvhTri records of rt_get_bvh
 EXPORTS = (
     "rt_create", "rt_destroy", "rt_default_config", "rt_last_error", "rt_version", "rt_build_scene",
     "rt_scene_info_get", "rt_update_material", "rt_update_object_transform", "rt_update_object_material",
-    "rt_update_object_mesh", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_synchronize", "rt_readback",
+    "rt_update_object_mesh", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_trace_frames_sliced", "rt_synchronize", "rt_readback",
     "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_trace_gbuffer", "rt_readback_gbuffer",
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
     "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_set_profiling", "rt_get_kernel_profile",
@@ -121,6 +121,7 @@ def load() -> C.CDLL:
     L.rt_resize.argtypes = [vp, u32, u32]
     L.rt_trace_frame.argtypes = [vp, f32p, f32p, u32]
     L.rt_trace_frames.argtypes = [vp, f32p, f32p, u32, u32]
+    L.rt_trace_frames_sliced.argtypes = [vp, f32p, f32p, u32, u32, u32, u32]
     L.rt_synchronize.argtypes = [vp]
     L.rt_readback.argtypes = [vp, vp, C.c_size_t]
     L.rt_readback_srgb8.argtypes = [vp, vp, C.c_size_t]
@@ -243,6 +244,12 @@ class Context:
         cam = np.ascontiguousarray(camera_ubo, np.float32).reshape(64)
         clr = np.ascontiguousarray(clear_color, np.float32).reshape(3)
         self._check(self.L.rt_trace_frames(self.h, _p(cam), _p(clr), first_frame, n_frames))
+
+    def trace_frames_sliced(self, camera_ubo, clear_color, first_frame, n_frames, frame_stride, first_sample):
+        """Frames first_frame + k * frame_stride folded in as samples first_sample + k (spp slices)."""
+        cam = np.ascontiguousarray(camera_ubo, np.float32).reshape(64)
+        clr = np.ascontiguousarray(clear_color, np.float32).reshape(3)
+        self._check(self.L.rt_trace_frames_sliced(self.h, _p(cam), _p(clr), first_frame, n_frames, frame_stride, first_sample))
 
     def synchronize(self):
         self._check(self.L.rt_synchronize(self.h))

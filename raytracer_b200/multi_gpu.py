@@ -78,3 +78,38 @@ class StripGather:
 
     def assemble_host(self, parts) -> np.ndarray:
         return assemble([p[: self.rows[r]].cpu().numpy() for r, p in enumerate(parts)], self.height, self.strip_rows)
+
+
+def slice_frames(rank: int, world: int, n_frames: int) -> int:
+    """How many of the frames 0 .. n_frames-1 rank `rank` traces when frame f goes to rank f % world."""
+    return (n_frames - rank + world - 1) // world if n_frames > rank else 0
+
+
+class SppSliceReduce:
+    """spp slices (the alternative to screen strips for low-resolution / high-spp runs): every rank
+    traces whole frames f with f % world == rank (`rt_trace_frames_sliced(first_frame=rank, frame_stride=world)`)
+    into its own running mean; the estimate over all n frames is sum_r (n_r / n) * mean_r — ONE reduce(SUM) of the
+    pre-scaled images to rank 0 (NCCL over NVLink on the GPU box, gloo in the CPU tests).  Same estimator as the
+    sequential mix of simple.rgen:127-136, float sums in another order (not bit-identical; ~1e-6 relative)."""
+
+    def __init__(self, dist, height: int, width: int, channels: int = 4, device="cpu"):
+        import torch
+
+        self.dist, self.torch = dist, torch
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.buf = torch.zeros((height, width, channels), dtype=torch.float32, device=device)
+
+    def reduce(self, local_mean, n_frames: int):
+        """local_mean: (H, W, C) mean over this rank's slice_frames(rank, world, n_frames) frames.  Returns the
+        combined image on rank 0 (alpha forced to 1), None elsewhere."""
+        torch = self.torch
+        n_r = slice_frames(self.rank, self.world, n_frames)
+        if n_r:
+            torch.mul(local_mean, float(n_r) / float(n_frames), out=self.buf)
+        else:
+            self.buf.zero_()
+        self.dist.reduce(self.buf, dst=0, op=self.dist.ReduceOp.SUM)
+        if self.rank != 0:
+            return None
+        self.buf[..., 3] = 1.0
+        return self.buf

@@ -271,6 +271,35 @@ def test_strips_union_is_bit_identical():
 
 
 @pytest.mark.parametrize("name", ["cornell_pbr", "conference", "conference_room_large_pbr"])
+def test_spp_slices_match_sequential_accumulation():
+    """SURVEY §8e spp slices: rank r traces frames r, r + N, ...; sum(n_r / n * mean_r) is the sequential running mean
+    up to float summation order (tolerance 2e-6 relative + 1e-7), and stride 1 / sample == frame is bit-identical."""
+    from raytracer_b200 import multi_gpu
+
+    scene = fixture_scene("cornell_pbr")
+    W, H, n = 96, 64, 7
+    cam = _camera_for("cornell_pbr", W / H)
+    c = librt.Context(device=0)
+    try:
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(cam.ubo(), CLEAR, 0, n)
+        want = c.readback().copy()
+        c.trace_frames_sliced(cam.ubo(), CLEAR, 0, n, 1, 0)
+        assert np.array_equal(c.readback().view(np.uint32), want.view(np.uint32))
+        world = 3
+        acc = np.zeros_like(want, dtype=np.float64)
+        for r in range(world):
+            n_r = multi_gpu.slice_frames(r, world, n)
+            assert n_r == len(range(r, n, world))
+            c.trace_frames_sliced(cam.ubo(), CLEAR, r, n_r, world, 0)
+            acc += c.readback().astype(np.float64) * (n_r / n)
+        got = acc.astype(np.float32)
+        assert np.allclose(got[..., :3], want[..., :3], rtol=2e-6, atol=1e-7)
+    finally:
+        c.close()
+
+
 def test_gbuffer_bit_exact(ctx, name):
     scene = fixture_scene(name)
     W, H = 128, 72

@@ -63,3 +63,56 @@ def test_two_rank_strips_assemble_to_the_single_rank_frame(tmp_path, oracle_lib,
     for f in range(2):
         ref = orc.render(cam.ubo(), CLEAR, f, W, H, image=ref)
     assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+
+
+def _slice_worker(rank, world, port, W, H, n_frames, out_path):
+    import torch
+    import torch.distributed as dist
+
+    from oracle.binding import OracleScene
+    from raytracer_b200 import multi_gpu
+    import raytracer_b200 as rb
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        orc = OracleScene(fixture_scene("cornell_pbr")).build_bvh()
+        cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+        # this rank's slice: frames rank, rank + world, ...; each frame rendered on its own (the oracle's frame
+        # number is seed and blend index at once), then folded into the rank's running mean
+        mean = np.zeros((H, W, 4), np.float32)
+        for k, f in enumerate(range(rank, n_frames, world)):
+            img = orc.render(cam.ubo(), CLEAR, f, W, H, image=None) if f == 0 else _single_frame(orc, cam, f, W, H)
+            mean = img if k == 0 else (mean + (img - mean) * np.float32(1.0 / (k + 1))).astype(np.float32)
+        red = multi_gpu.SppSliceReduce(dist, H, W, 4)
+        out = red.reduce(torch.from_numpy(mean), n_frames)
+        if rank == 0:
+            np.save(out_path, out.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def _single_frame(orc, cam, f, W, H):
+    """The clamped single-sample image of frame f: x with mix(0, x, 1/(f+1)) == what the oracle stores, undone."""
+    img = orc.render(cam.ubo(), CLEAR, f, W, H, image=np.zeros((H, W, 4), np.float32))
+    out = img * np.float32(f + 1)
+    out[..., 3] = 1.0
+    return out
+
+
+def test_two_rank_spp_slices_reduce_to_the_sequential_mean(tmp_path, oracle_lib):
+    import torch.multiprocessing as mp
+
+    import raytracer_b200 as rb
+
+    W, H, n = 24, 16, 5
+    out = str(tmp_path / "img.npy")
+    mp.spawn(_slice_worker, args=(2, _free_port(), W, H, n, out), nprocs=2, join=True)
+    got = np.load(out)
+    orc = oracle_lib.OracleScene(fixture_scene("cornell_pbr")).build_bvh()
+    cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+    ref = None
+    for f in range(n):
+        ref = orc.render(cam.ubo(), CLEAR, f, W, H, image=ref)
+    assert np.allclose(got[..., :3], ref[..., :3], rtol=1e-5, atol=1e-6)
+    assert np.all(got[..., 3] == 1.0)
