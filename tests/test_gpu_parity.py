@@ -270,7 +270,6 @@ def test_strips_union_is_bit_identical():
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
 
 
-@pytest.mark.parametrize("name", ["cornell_pbr", "conference", "conference_room_large_pbr"])
 def test_spp_slices_match_sequential_accumulation():
     """SURVEY §8e spp slices: rank r traces frames r, r + N, ...; sum(n_r / n * mean_r) is the sequential running mean
     up to float summation order (tolerance 2e-6 relative + 1e-7), and stride 1 / sample == frame is bit-identical."""
@@ -300,6 +299,7 @@ def test_spp_slices_match_sequential_accumulation():
         c.close()
 
 
+@pytest.mark.parametrize("name", ["cornell_pbr", "conference", "conference_room_large_pbr"])
 def test_gbuffer_bit_exact(ctx, name):
     scene = fixture_scene(name)
     W, H = 128, 72
