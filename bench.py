@@ -5,7 +5,7 @@
 
 Workload (config.workload): BASELINE.json configs[2] — Sponza 1920x1080, depth 8 (roulette from depth 3),
 one step = `--spp-per-step` accumulated frames (default 256 = the config's whole 256-spp image, traced as
-batches of up to 64 frames in flight; the path-state arrays cap the batch at what fits 16 GiB).  The Sponza geometry blob is absent from the reference mount, so the scene is the
+batches of as many frames in flight as the path-state arrays hold in 16 GiB: 41 at N = 1, all 256 at N = 8).  The Sponza geometry blob is absent from the reference mount, so the scene is the
 deterministic "sponza-proxy" (raytracer_b200/proxy_scenes.py: same object/triangle/material counts).
 N > 1: screen tiles (8-row strips, rank r owns strip s when s % N == r), scene replicated, no
 collective on the data path; the strips are gathered over NCCL only for the end-to-end number.
@@ -181,7 +181,18 @@ def run_ours(args):
     if world > 1:
         import torch.distributed as dist
 
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # NCCL announces its version on stdout when the first communicator comes up; keep stdout for the JSON line
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     def barrier():
         if dist is not None:
@@ -199,7 +210,7 @@ def run_ours(args):
     scene, cam = make_scene(args.scene, W, H)
     pipe = librt.RT_PIPELINE_WAVEFRONT if args.pipeline == "wavefront" else librt.RT_PIPELINE_MEGAKERNEL
     kw = dict(device=local_rank, max_depth=args.max_depth, rr_start_depth=3, pipeline=pipe, strip_rows=8, strip_index=rank,
-              strip_count=world, frames_in_flight=min(max(B, 1), 64))
+              strip_count=world, frames_in_flight=max(B, 1))
     ctx = librt.Context(counters=False, **kw)
     info = ctx.build_scene(scene)
     ctx.resize(W, H)

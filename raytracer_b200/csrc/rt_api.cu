@@ -49,7 +49,7 @@ int rt_create(const rt_config* cfg_in, rt_ctx** out) {
     if (cfg.strip_rows == 0) cfg.strip_rows = 8;
     if (cfg.strip_count == 0) cfg.strip_count = 1;
     if (cfg.frames_in_flight == 0) cfg.frames_in_flight = 8;
-    if (cfg.frames_in_flight > 64) cfg.frames_in_flight = 64;
+    if (cfg.frames_in_flight > 1024) cfg.frames_in_flight = 1024;
     if (cfg.max_depth < 1 || cfg.rr_start_depth < 1 || cfg.strip_index >= cfg.strip_count ||
         cfg.pipeline > RT_PIPELINE_MEGAKERNEL || !(cfg.radiance_clamp == cfg.radiance_clamp)) {
         g_create_error = "rt_create: invalid configuration";
