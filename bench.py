@@ -245,12 +245,14 @@ def run_ours(args):
     barrier()
     sampler.start()
     ctx.reset_counters()
+    torch.cuda.profiler.start()  # `ncu --profile-from-start off` then lists exactly the launches of the timed region
     ctx.event_record(0)
     for s in range(K):
         ctx.trace_frames(ubo, CLEAR, f0 + s * B, B)
     ctx.event_record(1)
     ms = ctx.event_elapsed_ms()
     ctx.synchronize()
+    torch.cuda.profiler.stop()
     barrier()
     sampler.stop_flag = True
     launches = ctx.counters()["launches"]
