@@ -637,7 +637,7 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 6  /* 80 registers: measured 0.219 -> 0.195 ms/frame against 4 blocks of 128 registers */
 #endif
-template <bool COUNT, bool FIRST>
+template <bool COUNT, bool FIRST, bool LIGHTS>
 __global__ void __launch_bounds__(128, RT_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
                                                        uint32_t q_idx, uint32_t* q_out, int depth, DevCounters* counters) {
     const uint32_t n = wf.ctrl[q_idx];
@@ -680,7 +680,7 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_BLOCKS) wf_shade_kernel(Scen
                 Hit h;
                 h.t = 0.0f; h.u = __uint_as_float(hrec.x); h.v = __uint_as_float(hrec.y); h.id = 0u; h.inst = hrec.z; h.prim = hrec.w;
                 c_hits++;
-                res = shade_hit(sc, ps, h, mk3(dv.x, dv.y, dv.z), sr, c_nee);
+                res = shade_hit<LIGHTS>(sc, ps, h, mk3(dv.x, dv.y, dv.z), sr, c_nee);
                 if (!res.alive) {
                     sky = true;  // payload.hit = false -> the ray-gen shader adds the sky term
                 } else {
@@ -813,13 +813,14 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
 #ifndef RT_EXTEND_COOP
 #define RT_EXTEND_COOP 1
 #endif
-    static int g_ext = 0, g_shw = 0, g_shd = 0, g_pkt = 0, g_coop = 0;
+    static int g_ext = 0, g_shw = 0, g_shd = 0, g_shd0 = 0, g_pkt = 0, g_coop = 0;
     if (!g_ext) {
         g_coop = persistent_grid(wf_extend_coop_kernel<COUNT>, 128);
         g_pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128);
         g_ext = persistent_grid(wf_extend_kernel<COUNT>, 128);
         g_shw = persistent_grid(wf_shadow_kernel<COUNT>, 128);
-        g_shd = persistent_grid(wf_shade_kernel<COUNT, false>, 128);
+        g_shd = persistent_grid(wf_shade_kernel<COUNT, false, true>, 128);
+        g_shd0 = persistent_grid(wf_shade_kernel<COUNT, false, false>, 128);
     }
     const uint32_t gb = (n_slots + 255) / 256;
     const uint32_t gb_px = (n_px + 255) / 256;
@@ -859,17 +860,23 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         }
         pf.end(stream);
         pf.begin(RT_K_SHADE, stream);
-        if (depth == 0)
-            wf_shade_kernel<COUNT, true><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
-                                                                                    res.counters);
-        else
-            wf_shade_kernel<COUNT, false><<<std::min(g_shd, need), 128, 0, stream>>>(sc, fp, v, qi, q_in, w->queue[q_in ^ 1u].p, depth,
-                                                                                     res.counters);
+        {
+            const bool lit = sc.n_lights != 0u;
+            const int g = std::min(lit ? g_shd : g_shd0, need);
+            uint32_t* qo = w->queue[q_in ^ 1u].p;
+            if (depth == 0 && lit) wf_shade_kernel<COUNT, true, true><<<g, 128, 0, stream>>>(sc, fp, v, qi, q_in, qo, depth, res.counters);
+            else if (depth == 0) wf_shade_kernel<COUNT, true, false><<<g, 128, 0, stream>>>(sc, fp, v, qi, q_in, qo, depth, res.counters);
+            else if (lit) wf_shade_kernel<COUNT, false, true><<<g, 128, 0, stream>>>(sc, fp, v, qi, q_in, qo, depth, res.counters);
+            else wf_shade_kernel<COUNT, false, false><<<g, 128, 0, stream>>>(sc, fp, v, qi, q_in, qo, depth, res.counters);
+        }
         pf.end(stream);
-        pf.begin(RT_K_SHADOW, stream);
-        wf_shadow_kernel<COUNT><<<std::min(g_shw, need), 128, 0, stream>>>(sc, fp, v, res.counters);
-        pf.end(stream);
-        n_launch += 4;
+        if (sc.n_lights != 0u) {  // no light, no visibility ray
+            pf.begin(RT_K_SHADOW, stream);
+            wf_shadow_kernel<COUNT><<<std::min(g_shw, need), 128, 0, stream>>>(sc, fp, v, res.counters);
+            pf.end(stream);
+            n_launch++;
+        }
+        n_launch += 3;
         q_in ^= 1u;
     }
     pf.begin(RT_K_ACCUMULATE, stream);

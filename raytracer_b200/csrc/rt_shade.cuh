@@ -333,6 +333,10 @@ __device__ __forceinline__ float light_selection_pdf(const SceneView& sc, vec3 x
 }
 
 // simple.rchit:590-706.  `flags`: RT_FLAG_DIRECT_LIGHTING / RT_FLAG_MIS (both set = the shipped shader).
+// LIGHTS = false: the variant for scenes without lights (sc.n_lights == 0, hence no emissive material either: a light IS
+// an object whose material has emission_power > 0, gpu_scene.odin:366-379).  The NEE and emissive-MIS code drops out at
+// compile time — the same draws are taken and the same values produced, in a kernel half the size.
+template <bool LIGHTS = true>
 __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState& ps, const Hit& hit, vec3 ray_dir,
                                                  ShadowRequest& sr, uint32_t& n_nee) {
     ShadeResult out;
@@ -364,13 +368,15 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
     const float psl = glsl_clamp(mat.roughness, 0.1f, 0.9f);
     const float p = rnd01(ps.seed);
     if (p < psl) {
-        vec3 direct;
-        bool sampled;
-        if (nee_sample(sc, world_pos, N, mat, ray_dir, hit.inst, ps.seed, &direct, &sr, &sampled)) {
-            sr.pending = true;
-            sr.contrib = div3(mul3(ps.throughput, direct), psl);
+        if (LIGHTS) {
+            vec3 direct;
+            bool sampled;
+            if (nee_sample(sc, world_pos, N, mat, ray_dir, hit.inst, ps.seed, &direct, &sr, &sampled)) {
+                sr.pending = true;
+                sr.contrib = div3(mul3(ps.throughput, direct), psl);
+            }
+            if (sampled) n_nee++;
         }
-        if (sampled) n_nee++;
         did_direct = true;
     }
 
@@ -380,7 +386,7 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
     float ry = rnd01(ps.seed);
     BsdfSample bs = sample_brdf(wo, mat, rx, ry, ps.seed);
 
-    if (is_emissive) {
+    if (LIGHTS && is_emissive) {
         if (ps.first_bounce || ps.is_specular) {
             out.emissive_add = true;
             out.emissive = scale3(mul3(ps.throughput, mat.emission_color), mat.emission_power);
