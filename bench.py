@@ -14,7 +14,7 @@ collective on the data path; the strips are gathered over NCCL only for the end-
                pass) over K steps timed with CUDA events on the library's stream, inputs resident in HBM
   e2e          the same through the C ABI with HOST buffers: camera UBO from host memory each step and the
                RGBA32F image read back to (pinned) host memory each step
-  roofline     dominant kernel (wf_extend_kernel: per-ray traversal of bounces >= 1): algorithmic bytes / its
+  roofline     dominant kernel (wf_extend_coop_kernel: per-ray traversal of bounces >= 1): algorithmic bytes / its
                CUDA-event time; roofline_packet: the same for the first-bounce packet kernel
   cpu_baseline the CPU oracle (a port: the reference has no CPU path) on a bounded sample, rank 0, N = 1
   --impl reference   times that CPU port with all host threads (the reference's Vulkan path cannot run here)
@@ -290,7 +290,7 @@ def run_ours(args):
             traffic = tj["dram_bytes_per_ray"] * sec_rays / max(ext["launches"], 1)
         except Exception:
             pass
-        roof = {"bound": "hbm", "kernel": "wf_extend_kernel (per-ray closest hit, bounces 1..%d)" % (args.max_depth - 1),
+        roof = {"bound": "hbm", "kernel": "wf_extend_coop_kernel (one ray per lane, pooled triangle tests; bounces 1..%d)" % (args.max_depth - 1),
                 "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": "measured" if "hbm_gbs" in peaks else "fallback",
                 "launches": ext["launches"], "avg_launch_ms": ext["ms"] / max(ext["launches"], 1),
