@@ -77,6 +77,13 @@ int rt_create(const rt_config* cfg_in, rt_ctx** out) {
     rt_ctx* ctx = new rt_ctx();
     ctx->cfg = cfg;
     ctx->device = dev;
+    {   // keep freed scratch in the device's default pool (PoolBuf): rebuilds then reuse it without a driver round trip
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            uint64_t keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+    }
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
         ctx->counters.alloc(1) != cudaSuccess) {

@@ -70,13 +70,13 @@ __global__ void scan_add_kernel(uint32_t* data, uint32_t n, const uint32_t* bloc
 }
 
 struct Scanner {
-    DevBuf<uint32_t> lvl1, lvl2;
-    cudaError_t reserve(size_t n) {
+    PoolBuf<uint32_t> lvl1, lvl2;
+    cudaError_t reserve(size_t n, cudaStream_t s) {
         size_t b1 = (n + SCAN_TILE - 1) / SCAN_TILE;
         size_t b2 = (b1 + SCAN_TILE - 1) / SCAN_TILE;
-        cudaError_t e = lvl1.ensure(b1 + 1);
+        cudaError_t e = lvl1.alloc(b1 + 1, s);
         if (e != cudaSuccess) return e;
-        return lvl2.ensure(b2 + 1);
+        return lvl2.alloc(b2 + 1, s);
     }
     // exclusive scan in place; n <= SCAN_TILE^3
     void run(uint32_t* data, uint32_t n, cudaStream_t s) {
@@ -535,10 +535,10 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
     BUILD_TRY(cudaEventCreate(&ev1));
     BUILD_TRY(cudaEventRecord(ev0, stream));
     const uint32_t max_nodes = n / 3 + 2;  // every wide node below the root covers > 3 triangles: W(n) <= (n-1)/3
-    BUILD_TRY(out.nodes.alloc((size_t)max_nodes * RT_NODE_WORDS));
-    BUILD_TRY(out.tris.alloc((size_t)n * 3));
-    BUILD_TRY(out.morton.alloc(n));
-    BUILD_TRY(out.sorted_ids.alloc(n));
+    BUILD_TRY(out.nodes.ensure((size_t)max_nodes * RT_NODE_WORDS));
+    BUILD_TRY(out.tris.ensure((size_t)n * 3));
+    BUILD_TRY(out.morton.ensure(n));
+    BUILD_TRY(out.sorted_ids.ensure(n));
     out.n_nodes = 1;
     out.depth = 1;
     if (n == 0) {
@@ -548,30 +548,30 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
         cudaEventDestroy(ev0); cudaEventDestroy(ev1);
         return RT_OK;
     }
-    DevBuf<BuildScratch> scratch;
-    DevBuf<float4> flat, tlo, thi, nlo, nhi;
-    DevBuf<unsigned long long> keys_b;
-    DevBuf<uint32_t> ids_b, hist, left, right, first, count, parent, arrive;
-    DevBuf<uint32_t> level_a, level_b, child_slots, n_int, n_tri;
+    PoolBuf<BuildScratch> scratch;
+    PoolBuf<float4> flat, tlo, thi, nlo, nhi;
+    PoolBuf<unsigned long long> keys_b;
+    PoolBuf<uint32_t> ids_b, hist, left, right, first, count, parent, arrive;
+    PoolBuf<uint32_t> level_a, level_b, child_slots, n_int, n_tri;
     Scanner scanner;
     const uint32_t n_tiles = (n + SORT_TILE - 1) / SORT_TILE;
-    BUILD_TRY(scratch.alloc(1));
-    BUILD_TRY(flat.alloc((size_t)n * 3));
-    BUILD_TRY(tlo.alloc(n));
-    BUILD_TRY(thi.alloc(n));
-    BUILD_TRY(keys_b.alloc(n));
-    BUILD_TRY(ids_b.alloc(n));
-    BUILD_TRY(hist.alloc((size_t)n_tiles * 256));
-    BUILD_TRY(scanner.reserve(std::max<size_t>((size_t)n_tiles * 256, n)));
+    BUILD_TRY(scratch.alloc(1, stream));
+    BUILD_TRY(flat.alloc((size_t)n * 3, stream));
+    BUILD_TRY(tlo.alloc(n, stream));
+    BUILD_TRY(thi.alloc(n, stream));
+    BUILD_TRY(keys_b.alloc(n, stream));
+    BUILD_TRY(ids_b.alloc(n, stream));
+    BUILD_TRY(hist.alloc((size_t)n_tiles * 256, stream));
+    BUILD_TRY(scanner.reserve(std::max<size_t>((size_t)n_tiles * 256, n), stream));
     const uint32_t n_bin = (n == 1) ? 1 : 2 * n - 1;
-    BUILD_TRY(nlo.alloc(n_bin));
-    BUILD_TRY(nhi.alloc(n_bin));
-    BUILD_TRY(left.alloc(n));
-    BUILD_TRY(right.alloc(n));
-    BUILD_TRY(first.alloc(n));
-    BUILD_TRY(count.alloc(n));
-    BUILD_TRY(parent.alloc(n_bin));
-    BUILD_TRY(arrive.alloc(n));
+    BUILD_TRY(nlo.alloc(n_bin, stream));
+    BUILD_TRY(nhi.alloc(n_bin, stream));
+    BUILD_TRY(left.alloc(n, stream));
+    BUILD_TRY(right.alloc(n, stream));
+    BUILD_TRY(first.alloc(n, stream));
+    BUILD_TRY(count.alloc(n, stream));
+    BUILD_TRY(parent.alloc(n_bin, stream));
+    BUILD_TRY(arrive.alloc(n, stream));
 
     const uint32_t T = 256;
     init_scratch_kernel<<<1, 1, 0, stream>>>(scratch.p);
@@ -603,11 +603,11 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
     TreeView bt;
     bt.left = left.p; bt.right = right.p; bt.first = first.p; bt.count = count.p;
     bt.lo = nlo.p; bt.hi = nhi.p; bt.n = n;
-    BUILD_TRY(level_a.alloc(max_nodes));
-    BUILD_TRY(level_b.alloc(max_nodes));
-    BUILD_TRY(child_slots.alloc((size_t)max_nodes * 8));
-    BUILD_TRY(n_int.alloc(max_nodes));
-    BUILD_TRY(n_tri.alloc(max_nodes));
+    BUILD_TRY(level_a.alloc(max_nodes, stream));
+    BUILD_TRY(level_b.alloc(max_nodes, stream));
+    BUILD_TRY(child_slots.alloc((size_t)max_nodes * 8, stream));
+    BUILD_TRY(n_int.alloc(max_nodes, stream));
+    BUILD_TRY(n_tri.alloc(max_nodes, stream));
     const uint32_t zero = 0;
     BUILD_TRY(cudaMemcpyAsync(level_a.p, &zero, 4, cudaMemcpyHostToDevice, stream));
     uint32_t n_level = 1, level_first = 0, nodes_total = 1, tris_total = 0, depth = 0;

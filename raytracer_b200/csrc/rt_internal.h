@@ -41,6 +41,32 @@ struct DevBuf {
     DevBuf& operator=(const DevBuf&) = delete;
 };
 
+// Scratch that lives for one call: stream-ordered allocation from the device's default memory pool
+// (cudaMallocAsync).  rt_create raises the pool's release threshold, so after the first build the
+// ~25 temporaries of a rebuild cost microseconds instead of a cudaMalloc + a device-synchronising cudaFree each.
+template <typename T>
+struct PoolBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaStream_t s = nullptr;
+    cudaError_t alloc(size_t count, cudaStream_t stream) {
+        release();
+        s = stream;
+        if (count == 0) count = 1;
+        cudaError_t e = cudaMallocAsync((void**)&p, count * sizeof(T), stream);
+        if (e == cudaSuccess) n = count; else p = nullptr;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeAsync(p, s);
+        p = nullptr; n = 0;
+    }
+    ~PoolBuf() { release(); }
+    PoolBuf() = default;
+    PoolBuf(const PoolBuf&) = delete;
+    PoolBuf& operator=(const PoolBuf&) = delete;
+};
+
 // ---- BVH build (rt_build.cu) --------------------------------------------------------------
 struct BuildInput {
     const DevObject* d_objects;  // device
