@@ -225,6 +225,25 @@ def test_trace_frames_batch_equals_loop(ctx):
     assert np.array_equal(a.view(np.uint32), ctx.readback().view(np.uint32))
 
 
+def test_many_frames_in_flight_equals_loop():
+    """130 frames traced as ONE wavefront (frames_in_flight 200) == 130 single-frame dispatches, bit for bit."""
+    scene = fixture_scene("cornell_pbr")
+    cam = _camera_for("cornell_pbr", 1.0)
+    a = librt.Context(device=0, frames_in_flight=1)
+    b = librt.Context(device=0, frames_in_flight=200)
+    try:
+        for c in (a, b):
+            c.build_scene(scene)
+            c.resize(48, 40)
+        for f in range(130):
+            a.trace_frame(cam.ubo(), CLEAR, f)
+        b.trace_frames(cam.ubo(), CLEAR, 0, 130)
+        assert np.array_equal(a.readback().view(np.uint32), b.readback().view(np.uint32))
+    finally:
+        a.close()
+        b.close()
+
+
 def test_deeper_paths_and_roulette():
     """max_depth 8 with roulette from depth 3 (north_star's Sponza setting) — still the oracle's numbers."""
     scene = fixture_scene("cornell_pbr")
