@@ -52,9 +52,11 @@ enum {
     RT_FLAG_DIRECT_LIGHTING = 1u << 0, /* USE_DIRECT_LIGHTING 1 */
     RT_FLAG_MIS = 1u << 1,             /* USE_MIS 1 */
     RT_FLAG_COUNTERS = 1u << 2,        /* maintain device ray/node/triangle counters */
-    /* Primary rays are normally traced as 32-ray packets with one shared traversal per 4x8 screen tile (same hit
-     * records, fewer node/triangle fetches: `nodes`/`tris` then count one fetch per packet).  With this flag every
-     * primary ray walks the BVH on its own, which is the per-ray work definition of SURVEY.md §8(d). */
+    /* Primary rays are normally traced as 128-ray packets with one shared traversal per 16x8 screen tile (same hit
+     * records, fewer node/triangle fetches: `nodes`/`tris` then count one fetch per packet), and visibility rays pool
+     * their triangle tests per warp (same result; a ray may test the rest of a node's triangles after its first
+     * occluder).  With this flag every primary ray walks the BVH on its own and visibility rays stop at their first
+     * occluder, which is the per-ray work definition of SURVEY.md §8(d): counters then equal the CPU oracle's. */
     RT_FLAG_PER_RAY_PRIMARY = 1u << 3,
     RT_FLAG_DEFAULT = (1u << 0) | (1u << 1) | (1u << 2)
 };

@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel
         for (;;) {
             uint32_t tmask = 0u, tbase = 0u;
             if (has_ray) tmask = coop_node<COUNT>(sc, nr, ng, sp, stk, 0.001f, best_t, &tbase, c_nodes);
-            coop_triangles<COUNT>(sc, cw, lane, tmask, tbase, 0.001f, c_tris);
+            coop_triangles<false, COUNT>(sc, cw, lane, tmask, tbase, 0.001f, c_tris);
             if (has_ray) {
                 best_t = __uint_as_float((uint32_t)(cw.key[lane] >> 32));
                 if (!(ng.y & 0xFF000000u)) {
@@ -776,6 +776,82 @@ __global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_shadow_kernel(Scen
     }
 }
 
+// shadow, cooperative triangle tests: isVisibleRQ for every queued NEE sample with the (ray, triangle) pairs of a warp
+// pooled as in wf_extend_coop_kernel; "occluded" is a flag, so pooling cannot change it.
+template <bool COUNT>
+__global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_shadow_coop_kernel(SceneView sc, FrameParams fp, WfView wf,
+                                                                                 DevCounters* counters) {
+    __shared__ CoopWarp s_cw[4];
+    const uint32_t n = wf.ctrl[CT_SH];
+    const uint32_t lane = threadIdx.x & 31u;
+    CoopWarp& cw = s_cw[threadIdx.x >> 5];
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    WarpFetch wfetch;
+    wfetch.next = wfetch.end = 0u;
+    wfetch.drained = false;
+    NodeRay nr;
+    nr.ox = nr.oy = nr.oz = nr.idx = nr.idy = nr.idz = 0.0f; nr.oct = 0u;
+    TravStack stk;
+    uint2 ng = make_uint2(0u, 0u);
+    int sp = 0;
+    float tmax = 0.0f;
+    bool has_ray = false;
+    uint32_t entry = 0;
+    for (;;) {
+        const uint32_t i = warp_fetch(wfetch, &wf.ctrl[CT_CUR_SHW], n, !has_ray);
+        if (i != 0xFFFFFFFFu) {
+            entry = i;
+            const float4 o = wf.sh_o[i], d = wf.sh_d[i];
+            const TravRay r = trav_setup(mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z));
+            tmax = o.w;
+            coop_init_ray(cw, lane, r, tmax, __float_as_uint(d.w));
+            nr.ox = r.ox; nr.oy = r.oy; nr.oz = r.oz; nr.idx = r.idx; nr.idy = r.idy; nr.idz = r.idz; nr.oct = r.rbits & 7u;
+            ng = make_uint2(0u, 0x80000000u);
+            sp = 0;
+            has_ray = true;
+            c_rays++;
+        }
+        __syncwarp();
+        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) break;
+        const uint32_t max_idle = wfetch.drained ? 31u : (RT_REFILL_IDLE - 1u);
+        for (;;) {
+            uint32_t tmask = 0u, tbase = 0u;
+            if (has_ray) tmask = coop_node<COUNT>(sc, nr, ng, sp, stk, 0.001f, tmax, &tbase, c_nodes);
+            coop_triangles<true, COUNT>(sc, cw, lane, tmask, tbase, 0.001f, c_tris);
+            if (has_ray) {
+                const bool occluded = cw.tri[lane] == 0u;
+                bool done = occluded;
+                if (!done && !(ng.y & 0xFF000000u)) {
+                    if (sp == 0) done = true; else ng = stk.e[--sp];
+                }
+                if (done) {  // the ordered colour adds of wf_shadow_kernel
+                    const float4 c = wf.sh_c[entry], e = wf.sh_e[entry];
+                    const uint32_t slot = __float_as_uint(c.w), fl = __float_as_uint(e.w);
+                    float4 cv = wf.col[slot];
+                    vec3 col = mk3(cv.x, cv.y, cv.z);
+                    if (!occluded) col = add3(col, mk3(c.x, c.y, c.z));
+                    if (fl & 1u) col = add3(col, mk3(e.x, e.y, e.z));
+                    if (fl & 2u) {
+                        const float4 tv = wf.thr[slot];
+                        col = add3(col, mul3(mk3(tv.x, tv.y, tv.z), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
+                    }
+                    wf.col[slot] = make_float4(col.x, col.y, col.z, cv.w);
+                    has_ray = false;
+                }
+            }
+            const uint32_t live = __ballot_sync(0xFFFFFFFFu, has_ray);
+            if (32u - (uint32_t)__popc(live) > max_idle) break;
+        }
+    }
+    if (COUNT) {
+        warp_add(&counters->shadow_rays, c_rays);
+        warp_add(&counters->nodes, c_nodes);
+        warp_add(&counters->tris, c_tris);
+        warp_add(&counters->shadow_nodes, c_nodes);
+        warp_add(&counters->shadow_tris, c_tris);
+    }
+}
+
 // accumulate: simple.rgen:121-136
 // the lanes of a pixel are folded into the running mean in frame order, so the float result is the one of
 // n_lanes successive single-frame dispatches
@@ -872,7 +948,13 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         pf.end(stream);
         if (sc.n_lights != 0u) {  // no light, no visibility ray
             pf.begin(RT_K_SHADOW, stream);
-            wf_shadow_kernel<COUNT><<<std::min(g_shw, need), 128, 0, stream>>>(sc, fp, v, res.counters);
+#ifndef RT_SHADOW_COOP
+#define RT_SHADOW_COOP 1
+#endif
+            if (RT_SHADOW_COOP && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY))
+                wf_shadow_coop_kernel<COUNT><<<std::min(g_coop, need), 128, 0, stream>>>(sc, fp, v, res.counters);
+            else
+                wf_shadow_kernel<COUNT><<<std::min(g_shw, need), 128, 0, stream>>>(sc, fp, v, res.counters);
             pf.end(stream);
             n_launch++;
         }

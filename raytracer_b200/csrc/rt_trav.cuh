@@ -289,9 +289,10 @@ struct CoopWarp {
     unsigned long long key[32];  // t bits << 32 | flat triangle id of the closest accepted hit; (tmax bits << 32) = none yet
     float4 ra[32];               // shear px.x px.y py.x py.y
     float4 rb[32];               // shear pz.x pz.y cxy.x cxy.y
-    float4 rc[32];               // o_kz, 1/d_kz, kz bits, -
+    float4 rc[32];               // o_kz, 1/d_kz, kz bits, tmax (any-hit)
     float2 uv[32];               // barycentrics of the hit in `key`
-    uint32_t tri[32];            // its index in the BVH triangle array, 0xFFFFFFFF = miss
+    uint32_t tri[32];            // its index in the BVH triangle array, 0xFFFFFFFF = miss; any-hit: 0 = occluded
+    uint32_t ignore[32];         // any-hit: triangles of this instance do not occlude (simple.rchit:378-382)
     uint32_t items[RT_COOP_ITEMS];  // triangle index | owner lane << 27
 };
 
@@ -301,21 +302,27 @@ struct NodeRay {
     uint32_t oct;
 };
 
-__device__ __forceinline__ void coop_init_ray(CoopWarp& cw, uint32_t lane, const TravRay& r, float tmax) {
+__device__ __forceinline__ void coop_init_ray(CoopWarp& cw, uint32_t lane, const TravRay& r, float tmax,
+                                              uint32_t ignore_inst = 0xFFFFFFFFu) {
     cw.key[lane] = (unsigned long long)__float_as_uint(tmax) << 32;
     cw.ra[lane] = make_float4(r.sh.px.x, r.sh.px.y, r.sh.py.x, r.sh.py.y);
     cw.rb[lane] = make_float4(r.sh.pz.x, r.sh.pz.y, r.sh.cxy.x, r.sh.cxy.y);
     const uint32_t kzbits = (r.rbits >> 3) & 3u;
     const bool k0 = kzbits == 0u, k1 = (kzbits & 1u) != 0u;
-    cw.rc[lane] = make_float4(k0 ? r.ox : (k1 ? r.oy : r.oz), k0 ? r.idx : (k1 ? r.idy : r.idz), __uint_as_float(kzbits), 0.0f);
+    cw.rc[lane] = make_float4(k0 ? r.ox : (k1 ? r.oy : r.oz), k0 ? r.idx : (k1 ? r.idy : r.idz), __uint_as_float(kzbits), tmax);
     cw.tri[lane] = 0xFFFFFFFFu;
+    cw.ignore[lane] = ignore_inst;
 }
 
-// one (ray of lane `owner`, triangle ti) pair; returns the key offered (0 = nothing offered)
+// one (ray of lane `owner`, triangle ti) pair; returns the key offered (0 = nothing offered).
+// ANY (visibility rays): a hit in (tmin, tmax) on another instance than `ignore` marks the owner occluded — a flag,
+// so the order of the tests cannot matter; nothing is offered.
+template <bool ANY>
 __device__ __forceinline__ unsigned long long coop_test(const SceneView& sc, CoopWarp& cw, uint32_t owner, uint32_t ti, float tmin,
                                                         float* uu, float* vv) {
     const float4* tp = sc.tris + (size_t)ti * 3u;
     const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+    if (ANY && __float_as_uint(q1.w) == cw.ignore[owner]) return 0ull;
     const float4 a = cw.ra[owner], b = cw.rb[owner], c = cw.rc[owner];
     Shear sh;
     sh.px = make_float2(a.x, a.y); sh.py = make_float2(a.z, a.w); sh.pz = make_float2(b.x, b.y); sh.cxy = make_float2(b.z, b.w);
@@ -324,6 +331,10 @@ __device__ __forceinline__ unsigned long long coop_test(const SceneView& sc, Coo
     float tt;
     tri_finish(U, V, W, det, q0, q1, q2, __float_as_uint(c.z), c.x, c.y, &tt, uu, vv);
     if (!(tt > tmin)) return 0ull;
+    if (ANY) {
+        if (tt < c.w) cw.tri[owner] = 0u;
+        return 0ull;
+    }
     const unsigned long long key = ((unsigned long long)__float_as_uint(tt) << 32) | __float_as_uint(q0.w);
     const unsigned long long old = atomicMin(&cw.key[owner], key);
     return key < old ? key : 0ull;
@@ -331,7 +342,7 @@ __device__ __forceinline__ unsigned long long coop_test(const SceneView& sc, Coo
 
 // All 32 lanes call this after a node step; tmask / tbase: the lane's triangle bits and triangle base (0 when the
 // lane has no ray).  On return every owner's closest hit (key, tri, uv) includes the pooled triangles.
-template <bool COUNT>
+template <bool ANY, bool COUNT>
 __device__ __forceinline__ void coop_triangles(const SceneView& sc, CoopWarp& cw, uint32_t lane, uint32_t tmask, uint32_t tbase,
                                                float tmin, uint32_t& n_tris) {
     const uint32_t cnt = __popc(tmask);
@@ -361,12 +372,14 @@ __device__ __forceinline__ void coop_triangles(const SceneView& sc, CoopWarp& cw
                 owner = item >> 27;
                 ti = item & 0x07FFFFFFu;
                 if (COUNT) n_tris++;
-                key = coop_test(sc, cw, owner, ti, tmin, &uu, &vv);
+                key = coop_test<ANY>(sc, cw, owner, ti, tmin, &uu, &vv);
             }
             __syncwarp();
-            // of the lanes that lowered an owner's key this round, the one whose key stayed publishes the rest
-            if (key != 0ull && cw.key[owner] == key) { cw.tri[owner] = ti; cw.uv[owner] = make_float2(uu, vv); }
-            __syncwarp();
+            if (!ANY) {
+                // of the lanes that lowered an owner's key this round, the one whose key stayed publishes the rest
+                if (key != 0ull && cw.key[owner] == key) { cw.tri[owner] = ti; cw.uv[owner] = make_float2(uu, vv); }
+                __syncwarp();
+            }
         }
     } else {  // more pairs than the pool holds: every lane tests its own triangles
         while (tmask) {
@@ -374,8 +387,8 @@ __device__ __forceinline__ void coop_triangles(const SceneView& sc, CoopWarp& cw
             tmask &= tmask - 1u;
             float uu, vv;
             if (COUNT) n_tris++;
-            const unsigned long long key = coop_test(sc, cw, lane, tbase + tb, tmin, &uu, &vv);
-            if (key != 0ull) { cw.tri[lane] = tbase + tb; cw.uv[lane] = make_float2(uu, vv); }
+            const unsigned long long key = coop_test<ANY>(sc, cw, lane, tbase + tb, tmin, &uu, &vv);
+            if (!ANY && key != 0ull) { cw.tri[lane] = tbase + tb; cw.uv[lane] = make_float2(uu, vv); }
         }
         __syncwarp();
     }
