@@ -483,6 +483,7 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
         uint32_t slot[R];
         Shear sh[R];
         float ikz[R], bt[R], bu[R], bv[R];
+        vec3 idl[R];  // 1/d of the lane's rays, until the hulls are built
         uint32_t bid[R], btri[R];
         uint32_t kzs = 0u, valid = 0u;
         float ox, oy, oz;
@@ -511,10 +512,7 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                 const uint32_t kz = (r.rbits >> 3) & 3u;
                 kzs |= kz << (2 * k);
                 ikz[k] = kz == 0u ? r.idx : (kz == 1u ? r.idy : r.idz);
-                // per-lane part of the hull
-                ilx = k == 0 ? r.idx : fminf(ilx, r.idx); ihx = k == 0 ? r.idx : fmaxf(ihx, r.idx);
-                ily = k == 0 ? r.idy : fminf(ily, r.idy); ihy = k == 0 ? r.idy : fmaxf(ihy, r.idy);
-                ilz = k == 0 ? r.idz : fminf(ilz, r.idz); ihz = k == 0 ? r.idz : fmaxf(ihz, r.idz);
+                idl[k] = mk3(r.idx, r.idy, r.idz);
                 bt[k] = 10000.0f; bu[k] = 0.0f; bv[k] = 0.0f; bid[k] = 0xFFFFFFFFu; btri[k] = 0u;
             }
             ox = __uint_as_float(ox0); oy = __uint_as_float(oy0); oz = __uint_as_float(oz0);
@@ -534,14 +532,27 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
         }
         if (COUNT) c_rays += __popc(valid);
         const bool s0 = (oct & 1u) != 0u, s1 = (oct & 2u) != 0u, s2 = (oct & 4u) != 0u;
-        // hull of the reciprocal directions, widened so that the products below err on the safe side
-        ilx = warp_fmin_signed(ilx, s0); ihx = warp_fmax_signed(ihx, s0);
-        ily = warp_fmin_signed(ily, s1); ihy = warp_fmax_signed(ihy, s1);
-        ilz = warp_fmin_signed(ilz, s2); ihz = warp_fmax_signed(ihz, s2);
+        // Hulls of the reciprocal directions, one per sub-packet (sub-packet k = ray k of every lane = one 4 x 8 tile),
+        // widened so that the products below err on the safe side.  Lane l tests child (l & 7) against the hull of
+        // sub-packet (l >> 3): a child is entered when any sub-packet reaches it, and a triangle is tested only by the rays
+        // of the sub-packets that reach its leaf box (on the Sponza proxy 2.2 of 4: tools/packet_proto.py).
+        const uint32_t sub = lane >> 3;
+        {
+            float lx = 0.f, hx = 0.f, ly = 0.f, hy = 0.f, lz = 0.f, hz = 0.f;
+#pragma unroll
+            for (int k = 0; k < R; k++) {
+                const float a = warp_fmin_signed(idl[k].x, s0), b = warp_fmax_signed(idl[k].x, s0);
+                const float c2 = warp_fmin_signed(idl[k].y, s1), d2 = warp_fmax_signed(idl[k].y, s1);
+                const float e2 = warp_fmin_signed(idl[k].z, s2), f2 = warp_fmax_signed(idl[k].z, s2);
+                if (R == 4 ? (sub == (uint32_t)k) : (k == 0)) { lx = a; hx = b; ly = c2; hy = d2; lz = e2; hz = f2; }
+                else if (R != 4) { lx = fminf(lx, a); hx = fmaxf(hx, b); ly = fminf(ly, c2); hy = fmaxf(hy, d2); lz = fminf(lz, e2); hz = fmaxf(hz, f2); }
+            }
+            ilx = lx; ihx = hx; ily = ly; ihy = hy; ilz = lz; ihz = hz;
+        }
         ilx -= fabsf(ilx) * RT_PKT_MARGIN; ihx += fabsf(ihx) * RT_PKT_MARGIN;
         ily -= fabsf(ily) * RT_PKT_MARGIN; ihy += fabsf(ihy) * RT_PKT_MARGIN;
         ilz -= fabsf(ilz) * RT_PKT_MARGIN; ihz += fabsf(ihz) * RT_PKT_MARGIN;
-        float tmaxp = 10000.0f;  // max over the packet of the rays' current closest distances
+        float tmaxp = 10000.0f;  // max over the lane's sub-packet of the rays' current closest distances
         uint2 ng = make_uint2(0u, 0x80000000u);
         int sp = 0;
         for (;;) {
@@ -577,9 +588,18 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                                    fmaxf(fmaxf(lz * ilz, lz * ihz), fmaxf(hz * ilz, hz * ihz)));
             const uint32_t idx = (meta & 31u) ^ (((meta & 0x18u) == 0x18u) ? oct : 0u);
             const bool hit = fmaxf(tn, 0.001f) <= fminf(tf, tmaxp);
-            const uint32_t hm = __reduce_or_sync(0xFFFFFFFFu, hit ? ((meta >> 5) << idx) : 0u);
+            const uint32_t mybits = hit ? ((meta >> 5) << idx) : 0u;
+            const uint32_t hm = __reduce_or_sync(0xFFFFFFFFu, mybits);
             ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
             uint32_t tmask = hm & 0x00FFFFFFu;
+            uint32_t sm[R];  // triangle bits reached by each sub-packet
+            if (R == 4 && tmask) {
+#pragma unroll
+                for (int k = 0; k < R; k++) sm[k] = __reduce_or_sync(0xFFFFFFFFu, sub == (uint32_t)k ? mybits : 0u);
+            } else {
+#pragma unroll
+                for (int k = 0; k < R; k++) sm[k] = tmask;
+            }
             if (tmask) {
                 do {  // warp-uniform
                     const int tb = __ffs(tmask) - 1;
@@ -591,6 +611,7 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                     const uint32_t id = __float_as_uint(q0.w);
 #pragma unroll
                     for (int k = 0; k < R; k++) {
+                        if (!((sm[k] >> tb) & 1u)) continue;  // warp-uniform: this sub-packet's hull misses the leaf box
                         float U, V, W, det;
                         if (tri_edges(sh[k], q0, q1, q2, &U, &V, &W, &det)) {
                             const uint32_t kz = (kzs >> (2 * k)) & 3u;
@@ -601,10 +622,18 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                         }
                     }
                 } while (tmask);
-                float m = bt[0];
+                if (R == 4) {  // farthest current hit of the lane's sub-packet (distances are positive)
 #pragma unroll
-                for (int k = 1; k < R; k++) m = fmaxf(m, bt[k]);
-                tmaxp = __uint_as_float(__reduce_max_sync(0xFFFFFFFFu, __float_as_uint(m)));  // distances are positive
+                    for (int k = 0; k < R; k++) {
+                        const float m = __uint_as_float(__reduce_max_sync(0xFFFFFFFFu, __float_as_uint(bt[k])));
+                        if (sub == (uint32_t)k) tmaxp = m;
+                    }
+                } else {
+                    float m = bt[0];
+#pragma unroll
+                    for (int k = 1; k < R; k++) m = fmaxf(m, bt[k]);
+                    tmaxp = __uint_as_float(__reduce_max_sync(0xFFFFFFFFu, __float_as_uint(m)));
+                }
             }
             if (!(ng.y & 0xFF000000u)) {
                 if (sp == 0) break;
