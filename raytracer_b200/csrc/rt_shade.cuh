@@ -87,12 +87,11 @@ __device__ __forceinline__ vec3 f_schlick(vec3 F0, float VoH) {
     return add3(F0, scale3(sub3(splat3(1.0f), F0), pow5f(1.0f - VoH)));
 }
 // simple.rchit:100-110
-__device__ __forceinline__ vec3 cosine_direction(float rx, float ry) {
-    float phi = RT_TWO_PI * rx;
+// (s, c) = sincos_rt(2 pi rx): both lobes turn the same random number into the same azimuth, so the caller evaluates it
+// once ahead of the lobe branch instead of once per divergent side
+__device__ __forceinline__ vec3 cosine_direction(float s, float c, float ry) {
     float ct = sqrtf(ry);
     float st = sqrtf(1.0f - ry);
-    float s, c;
-    sincos_rt(phi, &s, &c);
     return mk3(c * st, s * st, ct);
 }
 // Lambert lobe with the Fresnel complement, as sampleBRDF evaluates it (simple.rchit:416-422, :434-440)
@@ -135,13 +134,10 @@ __device__ __forceinline__ float microfacet_pdf(vec3 wo, vec3 h, float roughness
     return glsl_max((D * nh) / (4.0f * voh), RT_EPS_PDF);
 }
 // simple.rchit:202-217
-__device__ __forceinline__ vec3 sample_ggx(float rx, float ry, float roughness) {
+__device__ __forceinline__ vec3 sample_ggx(float s, float c, float ry, float roughness) {
     float a = roughness * roughness;
-    float phi = RT_TWO_PI * rx;
     float ct = sqrtf((1.0f - ry) / (1.0f + (a * a - 1.0f) * ry));
     float st = sqrtf(1.0f - ct * ct);
-    float s, c;
-    sincos_rt(phi, &s, &c);
     return mk3(st * c, st * s, ct);
 }
 // simple.rchit:234-237
@@ -175,11 +171,13 @@ struct BsdfSample {
 __device__ __forceinline__ BsdfSample sample_brdf(vec3 wo, const Mat& m, float rx, float ry, uint32_t& seed) {
     BsdfSample r;
     float sw = specular_probability(m);
+    float sn, cs;
+    sincos_rt(RT_TWO_PI * rx, &sn, &cs);
     if (rnd01(seed) < sw) {
-        vec3 h = sample_ggx(rx, ry, m.roughness);
+        vec3 h = sample_ggx(sn, cs, ry, m.roughness);
         vec3 wi = reflect3(neg3(wo), h);
         if (wi.z <= 0.0f) {
-            wi = cosine_direction(rx, ry);
+            wi = cosine_direction(sn, cs, ry);
             r.is_specular = false;
             r.value = diffuse_value(wo, wi, m);
             r.direction = wi;
@@ -189,7 +187,7 @@ __device__ __forceinline__ BsdfSample sample_brdf(vec3 wo, const Mat& m, float r
             r.direction = wi;
         }
     } else {
-        r.direction = cosine_direction(rx, ry);
+        r.direction = cosine_direction(sn, cs, ry);
         r.is_specular = false;
         r.value = diffuse_value(wo, r.direction, m);
     }
