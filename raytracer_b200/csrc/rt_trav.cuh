@@ -323,11 +323,12 @@ __device__ __forceinline__ unsigned long long coop_test(const SceneView& sc, Coo
     const float4* tp = sc.tris + (size_t)ti * 3u;
     const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
     if (ANY && __float_as_uint(q1.w) == cw.ignore[owner]) return 0ull;
-    const float4 a = cw.ra[owner], b = cw.rb[owner], c = cw.rc[owner];
+    const float4 a = cw.ra[owner], b = cw.rb[owner];
     Shear sh;
     sh.px = make_float2(a.x, a.y); sh.py = make_float2(a.z, a.w); sh.pz = make_float2(b.x, b.y); sh.cxy = make_float2(b.z, b.w);
     float U, V, W, det;
     if (!tri_edges(sh, q0, q1, q2, &U, &V, &W, &det)) return 0ull;
+    const float4 c = cw.rc[owner];  // only the few pairs that pass the edge test need the distance terms
     float tt;
     tri_finish(U, V, W, det, q0, q1, q2, __float_as_uint(c.z), c.x, c.y, &tt, uu, vv);
     if (!(tt > tmin)) return 0ull;
