@@ -52,6 +52,17 @@ RT_HD float glsl_min(float x, float y) { return (y < x) ? y : x; }
 RT_HD float glsl_max(float x, float y) { return (x < y) ? y : x; }
 RT_HD float glsl_clamp(float x, float lo, float hi) { return glsl_min(glsl_max(x, lo), hi); }
 
+// a / b, same bits as the plain quotient.  A zero numerator sends the compiler's division sequence down its out-of-line
+// slow path (~35 instructions), and a metal's Lambert lobe is exactly zero, so hit shading took that path nine times per
+// hit on Sponza's all-metal materials.  0 / b is a zero signed sign(a) ^ sign(b) for every finite non-zero b: that case
+// is answered directly and the division runs on a harmless numerator.
+RT_HD float div_zn(float a, float b) {
+    const bool z = (a == 0.0f) && (fabsf(b) > 0.0f) && (fabsf(b) < INFINITY);
+    const float q = (z ? 1.0f : a) / b;
+    return z ? bits_float((float_bits(a) ^ float_bits(b)) & 0x80000000u) : q;
+}
+RT_HD vec3 div3z(vec3 a, float s) { return mk3(div_zn(a.x, s), div_zn(a.y, s), div_zn(a.z, s)); }
+
 // dot = (x x' + y y') + z z'
 RT_HD float dot3(vec3 a, vec3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 RT_HD vec3 cross3(vec3 a, vec3 b) {

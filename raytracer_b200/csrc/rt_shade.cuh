@@ -100,7 +100,7 @@ __device__ __forceinline__ vec3 diffuse_value(vec3 wo, vec3 wi, const Mat& m) {
     float VoH = glsl_clamp(dot3(wo, h), 0.0f, 1.0f);
     vec3 F = f_schlick(f0_of(m), VoH);
     vec3 da = scale3(m.albedo, 1.0f - m.metallic);
-    return div3(mul3(da, sub3(splat3(1.0f), F)), RT_PI);
+    return div3z(mul3(da, sub3(splat3(1.0f), F)), RT_PI);
 }
 // simple.rchit:118-166
 __device__ __forceinline__ vec3 eval_full_brdf(vec3 wo, vec3 wi, const Mat& m) {
@@ -111,7 +111,7 @@ __device__ __forceinline__ vec3 eval_full_brdf(vec3 wo, vec3 wi, const Mat& m) {
     float VoH = dot3(wo, h);
     vec3 F = f_schlick(f0_of(m), VoH);
     vec3 da = scale3(m.albedo, 1.0f - m.metallic);
-    vec3 diffuse = div3(mul3(da, sub3(splat3(1.0f), F)), RT_PI);
+    vec3 diffuse = div3z(mul3(da, sub3(splat3(1.0f), F)), RT_PI);
     float D = d_ggx(NoH, m.roughness);
     float G = g_smith(NoV, NoL, m.roughness);
     vec3 specular = div3(scale3(F, D * G), (4.0f * NoV) * NoL);
@@ -311,7 +311,7 @@ __device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, 
     float diff_pdf = wi.z / RT_PI;
     float brdf_pdf = sp * spec_pdf + (1.0f - sp) * diff_pdf;
     float w = mis_weight_power(light_pdf, brdf_pdf);
-    *direct = div3(scale3(scale3(mul3(brdf, Le), wi.z), w), glsl_max(light_pdf, 1e-6f));
+    *direct = div3z(scale3(scale3(mul3(brdf, Le), wi.z), w), glsl_max(light_pdf, 1e-6f));
     sr->origin = from;
     sr->dir = sdir;
     sr->tmax = sdist * 0.999f;
@@ -371,7 +371,7 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
             bool sampled;
             if (nee_sample(sc, world_pos, N, mat, ray_dir, hit.inst, ps.seed, &direct, &sr, &sampled)) {
                 sr.pending = true;
-                sr.contrib = div3(mul3(ps.throughput, direct), psl);
+                sr.contrib = div3z(mul3(ps.throughput, direct), psl);
             }
             if (sampled) n_nee++;
         }
@@ -414,7 +414,7 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
     ps.p_sample_light = psl;
 
     if (bs.pdf > 0.0f && bs.direction.z > 0.0f) {
-        ps.throughput = mul3(ps.throughput, div3(scale3(bs.value, bs.direction.z), bs.pdf));
+        ps.throughput = mul3(ps.throughput, div3z(scale3(bs.value, bs.direction.z), bs.pdf));
         out.next_dir = local_to_world(bs.direction, basis);
         out.next_origin = world_pos;
         out.alive = true;
