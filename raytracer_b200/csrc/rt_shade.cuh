@@ -94,14 +94,6 @@ __device__ __forceinline__ vec3 cosine_direction(float s, float c, float ry) {
     float st = sqrtf(1.0f - ry);
     return mk3(c * st, s * st, ct);
 }
-// Lambert lobe with the Fresnel complement, as sampleBRDF evaluates it (simple.rchit:416-422, :434-440)
-__device__ __forceinline__ vec3 diffuse_value(vec3 wo, vec3 wi, const Mat& m) {
-    vec3 h = normalize3(add3(wo, wi));
-    float VoH = glsl_clamp(dot3(wo, h), 0.0f, 1.0f);
-    vec3 F = f_schlick(f0_of(m), VoH);
-    vec3 da = scale3(m.albedo, 1.0f - m.metallic);
-    return div3z(mul3(da, sub3(splat3(1.0f), F)), RT_PI);
-}
 // simple.rchit:118-166
 __device__ __forceinline__ vec3 eval_full_brdf(vec3 wo, vec3 wi, const Mat& m) {
     float NoL = wi.z, NoV = wo.z;
@@ -116,15 +108,6 @@ __device__ __forceinline__ vec3 eval_full_brdf(vec3 wo, vec3 wi, const Mat& m) {
     float G = g_smith(NoV, NoL, m.roughness);
     vec3 specular = div3(scale3(F, D * G), (4.0f * NoV) * NoL);
     return add3(diffuse, specular);
-}
-// simple.rchit:168-193
-__device__ __forceinline__ vec3 microfacet_f(vec3 wo, vec3 wi, vec3 h, const Mat& m) {
-    float NoL = wi.z, NoV = wo.z;
-    if (NoL <= 0.0f || NoV <= 0.0f) return splat3(0.0f);
-    float D = d_ggx(h.z, m.roughness);
-    float G = g_smith(NoV, NoL, m.roughness);
-    vec3 F = f_schlick(f0_of(m), dot3(wo, h));
-    return div3(scale3(F, D * G), (4.0f * NoV) * NoL);
 }
 // simple.rchit:195-200
 __device__ __forceinline__ float microfacet_pdf(vec3 wo, vec3 h, float roughness) {
@@ -167,32 +150,45 @@ struct BsdfSample {
     bool is_specular;
 };
 
-// simple.rchit:403-449
+// simple.rchit:403-449.  The reference evaluates each lobe inside its own branch; a warp holds both kinds of lane, so the
+// parts the lobes share are hoisted out of the branch here — the cosine direction (diffuse lanes and the specular lanes
+// that fall back to it), the half vector of the chosen direction (the Lambert lobe's and the pdf's are the same value),
+// and the Schlick term (same F0, each lane's own cosine).  Every lane still performs exactly the reference's operations.
 __device__ __forceinline__ BsdfSample sample_brdf(vec3 wo, const Mat& m, float rx, float ry, uint32_t& seed) {
     BsdfSample r;
     float sw = specular_probability(m);
     float sn, cs;
     sincos_rt(RT_TWO_PI * rx, &sn, &cs);
+    r.direction = cosine_direction(sn, cs, ry);
+    r.is_specular = false;
+    vec3 hs = mk3(0.0f, 0.0f, 0.0f);
     if (rnd01(seed) < sw) {
-        vec3 h = sample_ggx(sn, cs, ry, m.roughness);
-        vec3 wi = reflect3(neg3(wo), h);
-        if (wi.z <= 0.0f) {
-            wi = cosine_direction(sn, cs, ry);
-            r.is_specular = false;
-            r.value = diffuse_value(wo, wi, m);
-            r.direction = wi;
-        } else {
+        hs = sample_ggx(sn, cs, ry, m.roughness);
+        vec3 wi = reflect3(neg3(wo), hs);
+        if (!(wi.z <= 0.0f)) {
             r.is_specular = true;
-            r.value = microfacet_f(wo, wi, h, m);
             r.direction = wi;
         }
-    } else {
-        r.direction = cosine_direction(sn, cs, ry);
-        r.is_specular = false;
-        r.value = diffuse_value(wo, r.direction, m);
     }
     vec3 h = normalize3(add3(wo, r.direction));
-    float sp = microfacet_pdf(wo, h, m.roughness);
+    float woh = dot3(wo, h);
+    vec3 F = f_schlick(f0_of(m), r.is_specular ? dot3(wo, hs) : glsl_clamp(woh, 0.0f, 1.0f));
+    if (r.is_specular) {  // microfacetF, simple.rchit:168-193
+        float NoL = r.direction.z, NoV = wo.z;
+        if (NoL <= 0.0f || NoV <= 0.0f) {
+            r.value = splat3(0.0f);
+        } else {
+            float D = d_ggx(hs.z, m.roughness);
+            float G = g_smith(NoV, NoL, m.roughness);
+            r.value = div3(scale3(F, D * G), (4.0f * NoV) * NoL);
+        }
+    } else {  // the Lambert lobe with the Fresnel complement, simple.rchit:416-422 and :434-440
+        vec3 da = scale3(m.albedo, 1.0f - m.metallic);
+        r.value = div3z(mul3(da, sub3(splat3(1.0f), F)), RT_PI);
+    }
+    float nh = glsl_max(h.z, RT_EPS_COS);  // microfacet_pdf(wo, h, roughness)
+    float voh = glsl_max(woh, RT_EPS_VOH);
+    float sp = glsl_max((d_ggx(nh, m.roughness) * nh) / (4.0f * voh), RT_EPS_PDF);
     float dp = glsl_max(r.direction.z, 0.0f) / RT_PI;
     r.pdf = sw * sp + (1.0f - sw) * dp;
     r.pdf = glsl_max(r.pdf, RT_EPS_PDF);
