@@ -660,6 +660,10 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
     }
 }
 
+// The shade kernel wants all of a path's state in flight at once; ptxas sinks plain loads below the miss test, so the
+// lines behind it are requested with a prefetch it leaves in place.
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 // shade: simple.rmiss / simple.rchit for every queued path + the ray-gen loop tail (simple.rgen:106-118).
 // Colour terms are added in the reference's order: NEE, emissive, sky.  When the NEE term waits for
 // its visibility ray, the later terms travel with the shadow-queue entry and wf_shadow_kernel adds them.
@@ -685,6 +689,10 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_BLOCKS) wf_shade_kernel(Scen
         PathState ps;
         if (i < n) {
             slot = q_in ? q_in[i] : i;
+            // the state behind the miss test is requested together with the hit record (one memory latency, not two)
+            prefetch_l1(&wf.ray_d[slot]);
+            prefetch_l1(&wf.seeds[slot]);
+            if (!FIRST) prefetch_l1(&wf.prev[slot]);
             const uint4 hrec = wf.hit[slot];
             // first bounce: the payload initialisation of simple.rgen:76-85
             const float4 tv = FIRST ? make_float4(1.0f, 1.0f, 1.0f, 1.0f) : wf.thr[slot];
@@ -736,8 +744,8 @@ __global__ void __launch_bounds__(128, RT_SHADE_MIN_BLOCKS) wf_shade_kernel(Scen
         }
         const uint32_t qi = queue_push(&wf.ctrl[q_idx ^ 1u], push_next);
         if (push_next) q_out[qi] = slot;
-        const uint32_t si = queue_push(&wf.ctrl[CT_SH], push_shadow);
-        if (push_shadow) {
+        const uint32_t si = LIGHTS ? queue_push(&wf.ctrl[CT_SH], push_shadow) : 0u;
+        if (LIGHTS && push_shadow) {
             // a sky term is only pending when the hit shader ended the path, in which case the throughput
             // in the state array is still the one the term needs (on the first bounce it has not been stored yet)
             if (FIRST && sky) wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_brdf_pdf);
