@@ -141,7 +141,7 @@ __device__ __forceinline__ vec3 unshadowed(const SceneView& sc, const RSurf& s, 
     const float cos_y = fabsf(dot3(lp.n, wi_w));  // lights emit from both faces (sampleLight flips the normal)
     const vec3 wi = world_to_local(wi_w, basis);
     if (!(wi.z > 1e-4f) || !(cos_y > 1e-6f)) return splat3(0.0f);
-    const vec3 f = eval_full_brdf(wo_l, wi, mat);
+    const vec3 f = eval_full_brdf(wo_l, wi, normalize3(add3(wo_l, wi)), mat);
     return scale3(mul3(f, lp.Le), (wi.z * cos_y) / d2);
 }
 

@@ -95,10 +95,10 @@ __device__ __forceinline__ vec3 cosine_direction(float s, float c, float ry) {
     return mk3(c * st, s * st, ct);
 }
 // simple.rchit:118-166
-__device__ __forceinline__ vec3 eval_full_brdf(vec3 wo, vec3 wi, const Mat& m) {
+// h = normalize(wo + wi), which the caller needs for the pdf as well
+__device__ __forceinline__ vec3 eval_full_brdf(vec3 wo, vec3 wi, vec3 h, const Mat& m) {
     float NoL = wi.z, NoV = wo.z;
     if (NoL <= 0.0f || NoV <= 0.0f) return splat3(0.0f);
-    vec3 h = normalize3(add3(wo, wi));
     float NoH = h.z;
     float VoH = dot3(wo, h);
     vec3 F = f_schlick(f0_of(m), VoH);
@@ -223,7 +223,7 @@ struct ShadeResult {
 // NEE: simple.rchit:543-583 (light selection) + :472-505 (evaluateLightMIS) + :239-322 (sampleLight)
 // + the ray of :350-371.  Returns false when nothing can be added (no draw is skipped that the
 // reference takes).
-__device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, const Mat& mat, vec3 view_dir,
+__device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, const Basis& basis, vec3 wo, const Mat& mat,
                                            uint32_t current_object, uint32_t& seed, vec3* direct, ShadowRequest* sr,
                                            bool* sampled) {
     *sampled = false;
@@ -249,8 +249,6 @@ __device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, 
     const float sel_pdf = wsel / total;
     *sampled = true;
 
-    Basis basis = create_basis(N);
-    vec3 wo = world_to_local(neg3(view_dir), basis);
     // ---- sampleLight ----
     const DevLight* light = sc.lights + sel;
     const uint32_t lobj = __ldg(&light->object_index);
@@ -273,8 +271,9 @@ __device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, 
     vec3 wp = xf_point(tr, local_pos);
     vec3 cr = cross3(sub3(w1, w0), sub3(w2, w0));
     vec3 ln = normalize3(cr);
-    vec3 to_surface = sub3(x, wp);
-    float cosL = dot3(ln, normalize3(to_surface));
+    // normalize(x - wp) of simple.rchit:283 is -normalize(wp - x) bit for bit (negation commutes with every rounding)
+    vec3 tl = normalize3(sub3(wp, x));
+    float cosL = dot3(ln, neg3(tl));
     if (cosL < 0.0f) { cosL = fabsf(cosL); ln = neg3(ln); }
     if (!(cosL > 0.0f)) return false;
     vec3 to_light = sub3(wp, x);
@@ -293,16 +292,15 @@ __device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, 
     vec3 wi = world_to_local(ldir, basis);
     if (!(wi.z > 1e-4f)) return false;
     // isVisibleRQ ray (simple.rchit:350-371)
-    vec3 tl = normalize3(sub3(wp, x));
     vec3 from = add3(x, scale3(scale3(N, 0.001f), sign1(dot3(N, tl))));
     vec3 sdir = sub3(wp, from);
     float sdist = length3(sdir);
     if (sdist <= 0.0f) return false;
     sdir = div3(sdir, sdist);
-    vec3 brdf = eval_full_brdf(wo, wi, mat);
+    vec3 h = normalize3(add3(wo, wi));
+    vec3 brdf = eval_full_brdf(wo, wi, h, mat);
     float light_pdf = lpdf_geo * sel_pdf;
     float sp = specular_probability(mat);
-    vec3 h = normalize3(add3(wo, wi));
     float spec_pdf = microfacet_pdf(wo, h, mat.roughness);
     float diff_pdf = wi.z / RT_PI;
     float brdf_pdf = sp * spec_pdf + (1.0f - sp) * diff_pdf;
@@ -361,11 +359,13 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
     bool did_direct = false;
     const float psl = glsl_clamp(mat.roughness, 0.1f, 0.9f);
     const float p = rnd01(ps.seed);
+    const Basis basis = create_basis(N);
+    const vec3 wo = world_to_local(neg3(ray_dir), basis);
     if (p < psl) {
         if (LIGHTS) {
             vec3 direct;
             bool sampled;
-            if (nee_sample(sc, world_pos, N, mat, ray_dir, hit.inst, ps.seed, &direct, &sr, &sampled)) {
+            if (nee_sample(sc, world_pos, N, basis, wo, mat, hit.inst, ps.seed, &direct, &sr, &sampled)) {
                 sr.pending = true;
                 sr.contrib = div3z(mul3(ps.throughput, direct), psl);
             }
@@ -374,8 +374,6 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
         did_direct = true;
     }
 
-    Basis basis = create_basis(N);
-    vec3 wo = world_to_local(neg3(ray_dir), basis);
     float rx = rnd01(ps.seed);
     float ry = rnd01(ps.seed);
     BsdfSample bs = sample_brdf(wo, mat, rx, ry, ps.seed);
