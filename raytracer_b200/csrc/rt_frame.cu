@@ -670,8 +670,11 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 6  /* 80 registers: measured 0.219 -> 0.195 ms/frame against 4 blocks of 128 registers */
 #endif
+#ifndef RT_SHADE_LIT_MIN_BLOCKS
+#define RT_SHADE_LIT_MIN_BLOCKS 7  /* the variant with the NEE code: 72 registers + 176 B of spills still beat 6 blocks (1.279 -> 1.262 ms/frame, config 4b) */
+#endif
 template <bool COUNT, bool FIRST, bool LIGHTS>
-__global__ void __launch_bounds__(128, RT_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
+__global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
                                                        uint32_t q_idx, uint32_t* q_out, int depth, DevCounters* counters) {
     const uint32_t n = wf.ctrl[q_idx];
     uint32_t c_hits = 0, c_nee = 0;

@@ -33,7 +33,13 @@ def main():
     import bench
     from raytracer_b200 import librt
 
-    scene, cam = bench.make_scene(a.scene, a.width, a.height)
+    if a.scene in ("sponza-proxy", "soup1m"):
+        scene, cam = bench.make_scene(a.scene, a.width, a.height)
+    else:  # a fixture scene of the configs table (cornell_box, cornell_pbr, conference_mirror_chairs, multi_dispersion ...)
+        sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+        import run_configs
+
+        scene, cam = run_configs.load(a.scene), run_configs.camera_for(a.scene, a.width / a.height)
     pipe = librt.RT_PIPELINE_WAVEFRONT if a.pipeline == "wavefront" else librt.RT_PIPELINE_MEGAKERNEL
     ctx = librt.Context(counters=a.counters, device=0, max_depth=a.depth, rr_start_depth=3, pipeline=pipe, frames_in_flight=a.lanes,
                         per_ray_primary=a.per_ray)
