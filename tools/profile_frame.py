@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--kprof", action="store_true", help="per-kernel CUDA-event times (serialises launches)")
     ap.add_argument("--lanes", type=int, default=0, help="frames_in_flight (0 = library default)")
     ap.add_argument("--per-ray", action="store_true", help="RT_FLAG_PER_RAY_PRIMARY: no primary-ray packets")
+    ap.add_argument("--restir", action="store_true", help="rt_restir_frame (ReSTIR DI) instead of rt_trace_frames")
     a = ap.parse_args()
     import bench
     from raytracer_b200 import librt
@@ -53,8 +54,11 @@ def main():
         ctx.event_record(0)
         f = a.first_frame
         while f < a.first_frame + a.frames:
-            n = min(a.batch, a.first_frame + a.frames - f)
-            ctx.trace_frames(ubo, bench.CLEAR, f, n)
+            n = 1 if a.restir else min(a.batch, a.first_frame + a.frames - f)
+            if a.restir:
+                ctx.restir_frame(ubo, bench.CLEAR, f)
+            else:
+                ctx.trace_frames(ubo, bench.CLEAR, f, n)
             f += n
         ctx.event_record(1)
         ms = ctx.event_elapsed_ms()
