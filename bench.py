@@ -284,10 +284,11 @@ def run_ours(args):
         sec_rays = cnt["extend_rays"] - cnt1["extend_rays"]
         alg_sec = alg(cnt) - alg(cnt1)
         achieved = alg_sec / (ext["ms"] * 1e-3) / 1e9 if ext["ms"] > 0 else 0.0
-        traffic = None
+        traffic, l1_stage = None, None
         try:  # dram__bytes_read+write per ray of the last committed `ncu --set full` capture of this kernel
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_kernel"]
             traffic = tj["dram_bytes_per_ray"] * sec_rays / max(ext["launches"], 1)
+            l1_stage = tj.get("l1_data_stage")
         except Exception:
             pass
         roof = {"bound": "hbm", "kernel": "wf_extend_coop_kernel (one ray per lane, pooled triangle tests; bounces 1..%d)" % (args.max_depth - 1),
@@ -299,6 +300,7 @@ def run_ours(args):
                 "share_of_step": ext["ms"] / total_k if total_k > 0 else None,
                 "note": "the BVH (< 20 MB) is L2/L1-resident, so algorithmic bytes / time is a bookkeeping ratio against the "
                         "HBM copy peak, not a DRAM utilisation; `traffic` is the DRAM figure",
+                "l1_data_stage": l1_stage,  # what bounds the kernel in practice (ncu, committed capture): L1 wavefronts, not DRAM
                 "kernel_ms": {k: round(v["ms"], 3) for k, v in kprof.items()}}
         if pkt["launches"]:
             a_ray, a_pkt = alg(cnt1), alg(cntp)
