@@ -177,6 +177,7 @@ struct WavefrontBuffers {
     DevBuf<float4> sh_d;    // shadow dir.xyz, light object bits
     DevBuf<float4> sh_c;    // contribution.xyz, slot bits
     DevBuf<float4> sh_e;    // emissive term.xyz, flags (1 = emissive add, 2 = sky add)
+    DevBuf<float4> sh_n;    // light sample waiting for wf_nee_kernel: its three draws, selection pdf
     DevBuf<uint32_t> ctrl;  // [0..1] queue counts, [2] shadow count, [3..5] work cursors (extend, shade, shadow)
 };
 
@@ -188,7 +189,7 @@ int wavefront_alloc(WavefrontBuffers** out, uint32_t n_slots, std::string& err) 
     A(w->ray_o.alloc(n_slots)); A(w->ray_d.alloc(n_slots)); A(w->thr.alloc(n_slots)); A(w->col.alloc(n_slots));
     A(w->prev.alloc(n_slots)); A(w->seeds.alloc(n_slots)); A(w->hit.alloc(n_slots));
     A(w->queue[0].alloc(n_slots)); A(w->queue[1].alloc(n_slots));
-    A(w->sh_o.alloc(n_slots)); A(w->sh_d.alloc(n_slots)); A(w->sh_c.alloc(n_slots)); A(w->sh_e.alloc(n_slots));
+    A(w->sh_o.alloc(n_slots)); A(w->sh_d.alloc(n_slots)); A(w->sh_c.alloc(n_slots)); A(w->sh_e.alloc(n_slots)); A(w->sh_n.alloc(n_slots));
     A(w->ctrl.alloc(8));
     if (e != cudaSuccess) {
         err = std::string("wavefront_alloc: ") + cudaGetErrorString(e);
@@ -204,7 +205,7 @@ struct WfView {
     float4 *ray_o, *ray_d, *thr, *col, *prev;
     uint2* seeds;
     uint4* hit;
-    float4 *sh_o, *sh_d, *sh_c, *sh_e;
+    float4 *sh_o, *sh_d, *sh_c, *sh_e, *sh_n;
     uint32_t* ctrl;
 };
 
@@ -686,6 +687,8 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
         uint32_t slot = 0;
         ShadowRequest sr;
         sr.pending = false;
+        NeeRequest nq;
+        nq.pending = false;
         ShadeResult res;
         res.emissive_add = false;
         res.alive = false;
@@ -720,7 +723,7 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
                 Hit h;
                 h.t = 0.0f; h.u = __uint_as_float(hrec.x); h.v = __uint_as_float(hrec.y); h.id = 0u; h.inst = hrec.z; h.prim = hrec.w;
                 c_hits++;
-                res = shade_hit<LIGHTS>(sc, ps, h, mk3(dv.x, dv.y, dv.z), sr, c_nee);
+                res = shade_hit<LIGHTS, true>(sc, ps, h, mk3(dv.x, dv.y, dv.z), sr, c_nee, &nq);
                 if (!res.alive) {
                     sky = true;  // payload.hit = false -> the ray-gen shader adds the sky term
                 } else {
@@ -730,7 +733,7 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
                     push_next = go;
                 }
             }
-            push_shadow = sr.pending;
+            push_shadow = LIGHTS && nq.pending;
             if (!push_shadow) {
                 if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
                 if (sky) ps.color = add3(ps.color, mul3(ps.throughput, clearc));
@@ -752,9 +755,13 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
             // a sky term is only pending when the hit shader ended the path, in which case the throughput
             // in the state array is still the one the term needs (on the first bounce it has not been stored yet)
             if (FIRST && sky) wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_brdf_pdf);
-            wf.sh_o[si] = make_float4(sr.origin.x, sr.origin.y, sr.origin.z, sr.tmax);
-            wf.sh_d[si] = make_float4(sr.dir.x, sr.dir.y, sr.dir.z, __uint_as_float(sr.light_object));
-            wf.sh_c[si] = make_float4(sr.contrib.x, sr.contrib.y, sr.contrib.z, __uint_as_float(slot));
+            // the light sample as drawn (NeeRequest); wf_nee_kernel replaces it by the visibility ray and the contribution.
+            // It reads the hit point from the ray-origin array, which continuing paths have just written.
+            if (!push_next) wf.ray_o[slot] = make_float4(nq.x.x, nq.x.y, nq.x.z, 0.0f);
+            wf.sh_o[si] = make_float4(nq.N.x, nq.N.y, nq.N.z, __uint_as_float(nq.material));
+            wf.sh_d[si] = make_float4(nq.wo.x, nq.wo.y, nq.wo.z, __uint_as_float(nq.light));
+            wf.sh_c[si] = make_float4(nq.throughput.x, nq.throughput.y, nq.throughput.z, __uint_as_float(slot));
+            wf.sh_n[si] = make_float4(nq.r_tri, nq.q1, nq.q2, nq.sel_pdf);
             const uint32_t fl = (res.emissive_add ? 1u : 0u) | (sky ? 2u : 0u);
             wf.sh_e[si] = make_float4(res.emissive_add ? res.emissive.x : 0.0f, res.emissive_add ? res.emissive.y : 0.0f,
                                       res.emissive_add ? res.emissive.z : 0.0f, __uint_as_float(fl));
@@ -764,6 +771,50 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
         warp_add(&counters->hits, c_hits);
         warp_add(&counters->nee, c_nee);
     }
+}
+
+// nee: the second half of the light sample (sampleLight geometry, evaluateLightMIS, the isVisibleRQ ray) for every entry
+// of the shadow queue, one thread per sample.  Inside the hit shader this code ran with 6 of 32 lanes active (ncu r1p,
+// config 4b) and made the kernel 3 700 instructions long; here every lane has a sample.  An entry whose sample
+// contributes nothing (light facing away, below the horizon ...) gets tmax < 0: no ray, only the later colour terms.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_nee_kernel(SceneView sc, WfView wf) {
+    const uint32_t n = wf.ctrl[CT_SH];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = wf.sh_o[i], b = wf.sh_d[i], c = wf.sh_c[i], r = wf.sh_n[i];
+        const uint32_t slot = __float_as_uint(c.w);
+        const float4 xo = wf.ray_o[slot];
+        const Mat mat = load_material(sc.materials + __float_as_uint(a.w));
+        const vec3 N = mk3(a.x, a.y, a.z);
+        const Basis basis = create_basis(N);
+        const float psl = glsl_clamp(mat.roughness, 0.1f, 0.9f);
+        vec3 direct;
+        ShadowRequest sr;
+        if (nee_evaluate(sc, mk3(xo.x, xo.y, xo.z), N, basis, mk3(b.x, b.y, b.z), mat, __float_as_uint(b.w), r.w, r.x, r.y, r.z, &direct,
+                         &sr)) {
+            const vec3 contrib = div3z(mul3(mk3(c.x, c.y, c.z), direct), psl);
+            wf.sh_o[i] = make_float4(sr.origin.x, sr.origin.y, sr.origin.z, sr.tmax);
+            wf.sh_d[i] = make_float4(sr.dir.x, sr.dir.y, sr.dir.z, __uint_as_float(sr.light_object));
+            wf.sh_c[i] = make_float4(contrib.x, contrib.y, contrib.z, c.w);
+        } else {
+            wf.sh_o[i] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+        }
+    }
+}
+
+// the colour terms that follow the NEE term of a shadow-queue entry, in the reference's order (emissive, sky)
+__device__ __forceinline__ void shadow_entry_finish(const FrameParams& fp, const WfView& wf, uint32_t entry, bool visible) {
+    const float4 c = wf.sh_c[entry], e = wf.sh_e[entry];
+    const uint32_t slot = __float_as_uint(c.w), fl = __float_as_uint(e.w);
+    float4 cv = wf.col[slot];
+    vec3 col = mk3(cv.x, cv.y, cv.z);
+    if (visible) col = add3(col, mk3(c.x, c.y, c.z));
+    if (fl & 1u) col = add3(col, mk3(e.x, e.y, e.z));
+    if (fl & 2u) {
+        const float4 tv = wf.thr[slot];
+        col = add3(col, mul3(mk3(tv.x, tv.y, tv.z), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
+    }
+    wf.col[slot] = make_float4(col.x, col.y, col.z, cv.w);
 }
 
 // shadow: isVisibleRQ (simple.rchit:350-385) for every queued NEE sample, then the ordered colour adds
@@ -783,25 +834,22 @@ __global__ void __launch_bounds__(128, RT_TRAV_MIN_BLOCKS) wf_shadow_kernel(Scen
         if (i != 0xFFFFFFFFu) {
             entry = i;
             const float4 o = wf.sh_o[i], d = wf.sh_d[i];
-            trav_init(st, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, o.w, __float_as_uint(d.w));
-            has_ray = true;
-            c_rays++;
+            if (o.w < 0.0f) {  // the sample contributes nothing: no ray
+                shadow_entry_finish(fp, wf, i, false);
+            } else {
+                trav_init(st, mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z), 0.001f, o.w, __float_as_uint(d.w));
+                has_ray = true;
+                c_rays++;
+            }
         }
-        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) break;
+        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) {
+            if (__ballot_sync(0xFFFFFFFFu, i != 0xFFFFFFFFu) == 0u) break;  // nothing fetched: the queue is empty
+            continue;                                                         // only ray-less entries this time
+        }
         const uint32_t min_active = wfetch.drained ? 1u : (32u - RT_REFILL_IDLE + 1u);
         while (has_ray) {
             if (trav_step<true, COUNT>(sc, st, stk, c_nodes, c_tris)) {
-                const float4 c = wf.sh_c[entry], e = wf.sh_e[entry];
-                const uint32_t slot = __float_as_uint(c.w), fl = __float_as_uint(e.w);
-                float4 cv = wf.col[slot];
-                vec3 col = mk3(cv.x, cv.y, cv.z);
-                if (st.best.id == 0xFFFFFFFFu) col = add3(col, mk3(c.x, c.y, c.z));
-                if (fl & 1u) col = add3(col, mk3(e.x, e.y, e.z));
-                if (fl & 2u) {
-                    const float4 tv = wf.thr[slot];
-                    col = add3(col, mul3(mk3(tv.x, tv.y, tv.z), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
-                }
-                wf.col[slot] = make_float4(col.x, col.y, col.z, cv.w);
+                shadow_entry_finish(fp, wf, entry, st.best.id == 0xFFFFFFFFu);
                 has_ray = false;
             }
             if (__popc(__activemask()) < min_active) break;
@@ -842,17 +890,24 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_shadow_coop_kernel
         if (i != 0xFFFFFFFFu) {
             entry = i;
             const float4 o = wf.sh_o[i], d = wf.sh_d[i];
-            const TravRay r = trav_setup(mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z));
-            tmax = o.w;
-            coop_init_ray(cw, lane, r, tmax, __float_as_uint(d.w));
-            nr.ox = r.ox; nr.oy = r.oy; nr.oz = r.oz; nr.idx = r.idx; nr.idy = r.idy; nr.idz = r.idz; nr.oct = r.rbits & 7u;
-            ng = make_uint2(0u, 0x80000000u);
-            sp = 0;
-            has_ray = true;
-            c_rays++;
+            if (o.w < 0.0f) {  // the sample contributes nothing: no ray
+                shadow_entry_finish(fp, wf, i, false);
+            } else {
+                const TravRay r = trav_setup(mk3(o.x, o.y, o.z), mk3(d.x, d.y, d.z));
+                tmax = o.w;
+                coop_init_ray(cw, lane, r, tmax, __float_as_uint(d.w));
+                nr.ox = r.ox; nr.oy = r.oy; nr.oz = r.oz; nr.idx = r.idx; nr.idy = r.idy; nr.idz = r.idz; nr.oct = r.rbits & 7u;
+                ng = make_uint2(0u, 0x80000000u);
+                sp = 0;
+                has_ray = true;
+                c_rays++;
+            }
         }
         __syncwarp();
-        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) break;
+        if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) {
+            if (__ballot_sync(0xFFFFFFFFu, i != 0xFFFFFFFFu) == 0u) break;  // nothing fetched: the queue is empty
+            continue;                                                         // only ray-less entries this time
+        }
         const uint32_t max_idle = wfetch.drained ? 31u : (RT_REFILL_IDLE - 1u);
         for (;;) {
             uint32_t tmask = 0u, tbase = 0u;
@@ -864,18 +919,8 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_shadow_coop_kernel
                 if (!done && !(ng.y & 0xFF000000u)) {
                     if (sp == 0) done = true; else ng = stk.e[--sp];
                 }
-                if (done) {  // the ordered colour adds of wf_shadow_kernel
-                    const float4 c = wf.sh_c[entry], e = wf.sh_e[entry];
-                    const uint32_t slot = __float_as_uint(c.w), fl = __float_as_uint(e.w);
-                    float4 cv = wf.col[slot];
-                    vec3 col = mk3(cv.x, cv.y, cv.z);
-                    if (!occluded) col = add3(col, mk3(c.x, c.y, c.z));
-                    if (fl & 1u) col = add3(col, mk3(e.x, e.y, e.z));
-                    if (fl & 2u) {
-                        const float4 tv = wf.thr[slot];
-                        col = add3(col, mul3(mk3(tv.x, tv.y, tv.z), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
-                    }
-                    wf.col[slot] = make_float4(col.x, col.y, col.z, cv.w);
+                if (done) {
+                    shadow_entry_finish(fp, wf, entry, !occluded);
                     has_ray = false;
                 }
             }
@@ -924,12 +969,12 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     if (!w || w->n_slots < n_slots) { err = "wavefront buffers not allocated"; return RT_ERR_NO_TARGET; }
     WfView v;
     v.ray_o = w->ray_o.p; v.ray_d = w->ray_d.p; v.thr = w->thr.p; v.col = w->col.p; v.prev = w->prev.p;
-    v.seeds = w->seeds.p; v.hit = w->hit.p; v.sh_o = w->sh_o.p; v.sh_d = w->sh_d.p; v.sh_c = w->sh_c.p; v.sh_e = w->sh_e.p;
+    v.seeds = w->seeds.p; v.hit = w->hit.p; v.sh_o = w->sh_o.p; v.sh_d = w->sh_d.p; v.sh_c = w->sh_c.p; v.sh_e = w->sh_e.p; v.sh_n = w->sh_n.p;
     v.ctrl = w->ctrl.p;
 #ifndef RT_EXTEND_COOP
 #define RT_EXTEND_COOP 1
 #endif
-    static int g_ext = 0, g_shw = 0, g_shd = 0, g_shd0 = 0, g_pkt = 0, g_coop = 0;
+    static int g_ext = 0, g_shw = 0, g_shd = 0, g_shd0 = 0, g_pkt = 0, g_coop = 0, g_nee = 0;
     if (!g_ext) {
         g_coop = persistent_grid(wf_extend_coop_kernel<COUNT>, 128);
         g_pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128);
@@ -937,6 +982,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         g_shw = persistent_grid(wf_shadow_kernel<COUNT>, 128);
         g_shd = persistent_grid(wf_shade_kernel<COUNT, false, true>, 128);
         g_shd0 = persistent_grid(wf_shade_kernel<COUNT, false, false>, 128);
+        g_nee = persistent_grid(wf_nee_kernel<COUNT>, 128);
     }
     const uint32_t gb = (n_slots + 255) / 256;
     const uint32_t gb_px = (n_px + 255) / 256;
@@ -987,6 +1033,10 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         }
         pf.end(stream);
         if (sc.n_lights != 0u) {  // no light, no visibility ray
+            pf.begin(RT_K_SHADE, stream);  // the deferred half of the hit shader's light sample
+            wf_nee_kernel<COUNT><<<std::min(g_nee, need), 128, 0, stream>>>(sc, v);
+            pf.end(stream);
+            n_launch++;
             pf.begin(RT_K_SHADOW, stream);
 #ifndef RT_SHADOW_COOP
 #define RT_SHADOW_COOP 1

@@ -213,6 +213,17 @@ struct ShadowRequest {
     vec3 contrib;          // throughput * direct / p_sample_light, to add when visible
 };
 
+// A light sample that has been drawn but not evaluated yet (wavefront pipeline, see nee_select / nee_evaluate): everything
+// after the draws of sampleLight is a pure function of these values and of the hit, so it can run in a later kernel.
+struct NeeRequest {
+    bool pending;
+    uint32_t light;         // index of the selected light
+    float sel_pdf;          // its selection probability
+    float r_tri, q1, q2;    // the three draws of sampleLight (triangle, point)
+    vec3 x, N, wo, throughput;  // hit point, shading normal, local view direction, throughput at the time of the sample
+    uint32_t material;      // material index of the hit
+};
+
 struct ShadeResult {
     bool alive;           // payload.hit after the hit shader
     vec3 next_origin, next_dir;
@@ -221,12 +232,12 @@ struct ShadeResult {
 };
 
 // NEE: simple.rchit:543-583 (light selection) + :472-505 (evaluateLightMIS) + :239-322 (sampleLight)
-// + the ray of :350-371.  Returns false when nothing can be added (no draw is skipped that the
-// reference takes).
-__device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, const Basis& basis, vec3 wo, const Mat& mat,
-                                           uint32_t current_object, uint32_t& seed, vec3* direct, ShadowRequest* sr,
-                                           bool* sampled) {
-    *sampled = false;
+// + the ray of :350-371, in two halves.  nee_select takes every random draw the reference takes (selection, triangle,
+// point: no draw is skipped that the reference takes) and nee_evaluate turns them into the unshadowed contribution and the
+// visibility ray; nothing in the second half feeds back into the path, so the wavefront pipeline runs it one thread per
+// sample in its own kernel (wf_nee_kernel) instead of inside the divergent hit shader.
+__device__ __forceinline__ bool nee_select(const SceneView& sc, vec3 x, uint32_t current_object, uint32_t& seed, uint32_t* light,
+                                           float* sel_pdf, float* r_tri, float* q1, float* q2) {
     const uint32_t L = sc.n_lights;
     if (L == 0u) return false;
     const uint32_t maxL = L < RT_MAXLIGHTS ? L : RT_MAXLIGHTS;
@@ -246,21 +257,27 @@ __device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, 
         if (r1 <= 0.0f) { sel = i; wsel = w; break; }
     }
     if (sel == 0xFFFFFFFFu) return false;
-    const float sel_pdf = wsel / total;
-    *sampled = true;
+    *light = sel;
+    *sel_pdf = wsel / total;
+    *r_tri = rnd01(seed);
+    *q1 = rnd01(seed);
+    *q2 = rnd01(seed);
+    return true;
+}
 
+__device__ __forceinline__ bool nee_evaluate(const SceneView& sc, vec3 x, vec3 N, const Basis& basis, vec3 wo, const Mat& mat,
+                                             uint32_t sel, float sel_pdf, float r_tri, float q1, float q2, vec3* direct,
+                                             ShadowRequest* sr) {
     // ---- sampleLight ----
     const DevLight* light = sc.lights + sel;
     const uint32_t lobj = __ldg(&light->object_index);
     const DevObject* lo = sc.objects + lobj;
     const uint32_t ntri = __ldg(&light->num_triangles);
-    uint32_t tri = (uint32_t)(rnd01(seed) * (float)ntri);
+    uint32_t tri = (uint32_t)(r_tri * (float)ntri);
     if (tri > ntri - 1u) tri = ntri - 1u;
     const uint32_t* ip = sc.indices + __ldg(&lo->index_base) + 3u * tri;
     const rt_vertex* vb = sc.vertices + __ldg(&lo->vertex_base);
     vec3 p0 = vertex_pos(vb + __ldg(ip)), p1 = vertex_pos(vb + __ldg(ip + 1)), p2 = vertex_pos(vb + __ldg(ip + 2));
-    float q1 = rnd01(seed);
-    float q2 = rnd01(seed);
     float sq = sqrtf(q1);
     float bu = 1.0f - sq, bv = sq * (1.0f - q2), bw = sq * q2;
     vec3 local_pos = add3(add3(scale3(p0, bu), scale3(p1, bv)), scale3(p2, bw));
@@ -313,6 +330,16 @@ __device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, 
     return true;
 }
 
+__device__ __forceinline__ bool nee_sample(const SceneView& sc, vec3 x, vec3 N, const Basis& basis, vec3 wo, const Mat& mat,
+                                           uint32_t current_object, uint32_t& seed, vec3* direct, ShadowRequest* sr,
+                                           bool* sampled) {
+    uint32_t sel;
+    float sel_pdf, r_tri, q1, q2;
+    *sampled = nee_select(sc, x, current_object, seed, &sel, &sel_pdf, &r_tri, &q1, &q2);
+    if (!*sampled) return false;
+    return nee_evaluate(sc, x, N, basis, wo, mat, sel, sel_pdf, r_tri, q1, q2, direct, sr);
+}
+
 // simple.rchit:536-541 with :522-534 (no light is skipped here)
 __device__ __forceinline__ float light_selection_pdf(const SceneView& sc, vec3 x, uint32_t light_idx) {
     float w = light_weight(sc, x, light_idx);
@@ -328,11 +355,13 @@ __device__ __forceinline__ float light_selection_pdf(const SceneView& sc, vec3 x
 // LIGHTS = false: the variant for scenes without lights (sc.n_lights == 0, hence no emissive material either: a light IS
 // an object whose material has emission_power > 0, gpu_scene.odin:366-379).  The NEE and emissive-MIS code drops out at
 // compile time — the same draws are taken and the same values produced, in a kernel half the size.
-template <bool LIGHTS = true>
+// DEFER = true (wavefront pipeline): the light sample is drawn here and handed back in `nq` for wf_nee_kernel to evaluate.
+template <bool LIGHTS = true, bool DEFER = false>
 __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState& ps, const Hit& hit, vec3 ray_dir,
-                                                 ShadowRequest& sr, uint32_t& n_nee) {
+                                                 ShadowRequest& sr, uint32_t& n_nee, NeeRequest* nq = nullptr) {
     ShadeResult out;
     sr.pending = false;
+    if (DEFER) nq->pending = false;
     out.emissive_add = false;
     const DevObject* obj = sc.objects + hit.inst;
     const Mat mat = load_material(sc.materials + __ldg(&obj->material_index));
@@ -362,7 +391,14 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
     const Basis basis = create_basis(N);
     const vec3 wo = world_to_local(neg3(ray_dir), basis);
     if (p < psl) {
-        if (LIGHTS) {
+        if (LIGHTS && DEFER) {
+            if (nee_select(sc, world_pos, hit.inst, ps.seed, &nq->light, &nq->sel_pdf, &nq->r_tri, &nq->q1, &nq->q2)) {
+                nq->pending = true;
+                nq->x = world_pos; nq->N = N; nq->wo = wo; nq->throughput = ps.throughput;
+                nq->material = __ldg(&obj->material_index);
+                n_nee++;
+            }
+        } else if (LIGHTS) {
             vec3 direct;
             bool sampled;
             if (nee_sample(sc, world_pos, N, basis, wo, mat, hit.inst, ps.seed, &direct, &sr, &sampled)) {
