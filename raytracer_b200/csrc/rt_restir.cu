@@ -172,12 +172,15 @@ __device__ __forceinline__ bool reservoir_sample_valid(const SceneView& sc, cons
     if (r.light_index >= sc.n_lights) return false;
     return __float_as_uint(r.distance) < __ldg(&sc.lights[r.light_index].num_triangles);
 }
-__device__ __forceinline__ float target_of(const SceneView& sc, const SurfShade& ss, const rt_reservoir& r) {
-    if (!reservoir_sample_valid(sc, r)) return 0.0f;
-    const LightPoint lp = light_point(sc, r.light_index, __float_as_uint(r.distance), r.uv[0], r.uv[1]);
+// target function of a light point that has already been reconstructed (the same sample judged at several surfaces)
+__device__ __forceinline__ float target_of_point(const SceneView& sc, const SurfShade& ss, const LightPoint& lp) {
     if (lp.object == ss.s.inst) return 0.0f;  // a light does not light itself (simple.rchit:548-553 skips it)
     const float p = luminance(unshadowed(sc, ss.s, ss.basis, ss.wo_l, ss.mat, lp));
     return (p > 0.0f && p == p && !is_inf1(p)) ? p : 0.0f;
+}
+__device__ __forceinline__ float target_of(const SceneView& sc, const SurfShade& ss, const rt_reservoir& r) {
+    if (!reservoir_sample_valid(sc, r)) return 0.0f;
+    return target_of_point(sc, ss, light_point(sc, r.light_index, __float_as_uint(r.distance), r.uv[0], r.uv[1]));
 }
 
 // ---- pass 2: initial candidates (RIS) + temporal reuse ---------------------------------------------------
@@ -298,6 +301,8 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
             const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
             const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
             uint32_t seed = tea16((y * fp.width + x) ^ 0x53504154u, fp.frame);  // 'SPAT'
+            LightPoint lpw;  // the surviving sample's light point, once it has been reconstructed
+            bool have_lpw = false;
             if ((prm.flags & RT_RESTIR_SPATIAL) && prm.spatial_samples > 0u) {
                 // the pixel's own reservoir enters as one sample of weight p^ W M
                 float sel_p = res.target_pdf;
@@ -335,10 +340,12 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
                 }
                 // 1/Z: count the sources that could have produced the winner (their own target function is > 0 there)
                 float Z = (sel_p > 0.0f) ? (float)res.M : 0.0f;
-                if (sel_p > 0.0f) {
+                if (sel_p > 0.0f && reservoir_sample_valid(sc, res)) {  // one light point for all sources (an invalid sample has target 0 everywhere)
+                    lpw = light_point(sc, res.light_index, __float_as_uint(res.distance), res.uv[0], res.uv[1]);
+                    have_lpw = true;
                     for (uint32_t k = 0; k < n_nb; k++) {
                         const SurfShade qs = prepare_surface(sc, surf, nb[k]);
-                        if (target_of(sc, qs, res) > 0.0f) Z += (float)in[nb[k]].M;
+                        if (target_of_point(sc, qs, lpw) > 0.0f) Z += (float)in[nb[k]].M;
                     }
                 }
                 res.M = M;
@@ -349,7 +356,7 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
             }
             // shading: f Le G V W for the surviving sample, one visibility ray (isVisibleRQ, simple.rchit:350-385)
             if (res.W > 0.0f && reservoir_sample_valid(sc, res)) {
-                const LightPoint lp = light_point(sc, res.light_index, __float_as_uint(res.distance), res.uv[0], res.uv[1]);
+                const LightPoint lp = have_lpw ? lpw : light_point(sc, res.light_index, __float_as_uint(res.distance), res.uv[0], res.uv[1]);
                 const vec3 c = scale3(unshadowed(sc, ss.s, ss.basis, ss.wo_l, ss.mat, lp), res.W);
                 const vec3 tl = normalize3(sub3(lp.y, ss.s.pos));
                 const vec3 from = add3(ss.s.pos, scale3(scale3(ss.s.N, 0.001f), sign1(dot3(ss.s.N, tl))));
