@@ -5,7 +5,7 @@
 
 Workload (config.workload): BASELINE.json configs[2] — Sponza 1920x1080, depth 8 (roulette from depth 3),
 one step = `--spp-per-step` accumulated frames (default 256 = the config's whole 256-spp image, traced as
-batches of as many frames in flight as the path-state arrays hold in 16 GiB: 41 at N = 1, all 256 at N = 8).  The Sponza geometry blob is absent from the reference mount, so the scene is the
+batches of as many frames in flight as the path-state arrays hold in 56 GiB: two batches of 128 at N = 1, all 256 at N >= 2).  The Sponza geometry blob is absent from the reference mount, so the scene is the
 deterministic "sponza-proxy" (raytracer_b200/proxy_scenes.py: same object/triangle/material counts).
 N > 1: screen tiles (8-row strips, rank r owns strip s when s % N == r), scene replicated, no
 collective on the data path; the strips are gathered over NCCL only for the end-to-end number.

@@ -82,7 +82,7 @@ typedef struct rt_config {
     uint32_t strip_count;  /* world size; 0 -> 1 */
     /* rt_trace_frames traces up to this many consecutive frames as one wavefront (deep, short bounces of
      * one frame overlap the long first bounces of the others); the image is bit-identical to
-     * frame-by-frame dispatch.  0 -> 8; at most 1024, and capped so the path-state arrays stay below 16 GiB. */
+     * frame-by-frame dispatch.  0 -> 8; at most 1024, and capped so the path-state arrays stay below 56 GiB. */
     uint32_t frames_in_flight;
     uint32_t reserved[6];
 } rt_config;

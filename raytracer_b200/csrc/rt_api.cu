@@ -422,10 +422,13 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     if (ctx->wf) { wavefront_free(ctx->wf); ctx->wf = nullptr; }
     if (ctx->cfg.pipeline == RT_PIPELINE_WAVEFRONT) {
         std::string err;
-        // path state is ~200 B per slot; keep all lanes together under 16 GiB and 2^31 slots
+        // path state is ~200 B per slot; keep all lanes together under RT_STATE_CAP_GIB and 2^31 slots
+#ifndef RT_STATE_CAP_GIB
+#define RT_STATE_CAP_GIB 56  /* of the B200's 180 GB: 128 frames in flight at 1080p; 41 -> 128 frames: 0.540 -> 0.525 ms/frame */
+#endif
         uint64_t lanes = ctx->cfg.frames_in_flight;
         const uint64_t per_lane = std::max<uint64_t>(n, 1) * 200ull;
-        lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, (16ull << 30) / per_lane));
+        lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, ((uint64_t)RT_STATE_CAP_GIB << 30) / per_lane));
         lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, 0x7FFFFFFFull / std::max<uint64_t>(n, 1)));
         ctx->lanes = (uint32_t)lanes;
         const int rc = wavefront_alloc(&ctx->wf, (uint32_t)(n * lanes), err);
@@ -454,12 +457,15 @@ static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const floa
     std::string err;
     rt_begin_timing(ctx);
     const bool mega = ctx->cfg.pipeline == RT_PIPELINE_MEGAKERNEL;
+    // equal batches: 256 frames with room for 145 in flight run as 128 + 128, not 145 + 111
+    const uint32_t n_batches = mega ? n_frames : (n_frames + ctx->lanes - 1u) / std::max(ctx->lanes, 1u);
+    const uint32_t per_batch = mega ? 1u : (n_frames + std::max(n_batches, 1u) - 1u) / std::max(n_batches, 1u);
     for (uint32_t f = 0; f < n_frames;) {
         FrameParams fp;
         rt_fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f * frame_stride, &fp);
         fp.frame_stride = frame_stride;
         fp.sample = first_sample + f;
-        fp.n_lanes = mega ? 1u : std::min(ctx->lanes, n_frames - f);
+        fp.n_lanes = mega ? 1u : std::min(per_batch, n_frames - f);
         rc = mega ? launch_frame_megakernel(sc, fp, res, ctx->stream, err) : launch_frame_wavefront(sc, fp, res, ctx->stream, err);
         if (rc != RT_OK) { set_error(err); return rc; }
         f += fp.n_lanes;
