@@ -130,6 +130,13 @@ __device__ __forceinline__ float mis_weight_power(float p1, float p2) {
 }
 
 __device__ __forceinline__ vec3 vertex_pos(const rt_vertex* v) { return mk3(__ldg(&v->pos[0]), __ldg(&v->pos[1]), __ldg(&v->pos[2])); }
+// position and normal of a 24-byte vertex as three 64-bit loads
+__device__ __forceinline__ void load_vertex(const rt_vertex* v, vec3* pos, vec3* nrm) {
+    const float2* q = reinterpret_cast<const float2*>(v);
+    const float2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+    *pos = mk3(a.x, a.y, b.x);
+    *nrm = mk3(b.y, c.x, c.y);
+}
 __device__ __forceinline__ vec3 vertex_nrm(const rt_vertex* v) {
     return mk3(__ldg(&v->normal[0]), __ldg(&v->normal[1]), __ldg(&v->normal[2]));
 }
@@ -364,23 +371,48 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
     if (DEFER) nq->pending = false;
     out.emissive_add = false;
     const DevObject* obj = sc.objects + hit.inst;
-    const Mat mat = load_material(sc.materials + __ldg(&obj->material_index));
-    const uint32_t* ip = sc.indices + __ldg(&obj->index_base) + 3u * hit.prim;
-    const rt_vertex* vb = sc.vertices + __ldg(&obj->vertex_base);
-    const rt_vertex* v0 = vb + __ldg(ip);
-    const rt_vertex* v1 = vb + __ldg(ip + 1);
-    const rt_vertex* v2 = vb + __ldg(ip + 2);
-    const vec3 p0 = vertex_pos(v0), p1 = vertex_pos(v1), p2 = vertex_pos(v2);
-    const float bx = (1.0f - hit.u) - hit.v, by = hit.u, bz = hit.v;
-    float model[12];
+    // The object record and the vertices with wide loads: after the first bounce every lane sits in another object and
+    // triangle, and such a load costs the L1 pipe the same whatever its width (the bounce-1 launch ran at 80 % of that pipe
+    // with 56 scalar loads per hit: ncu r1q).  DevObject: words 0..11 model, 12..20 nrm, 21 material, 22 light, 23 vertex base.
+    // The variant with the light-sampling code has no registers to spare for 24 words in flight (measured: 0.64 -> 0.74 ms
+    // per frame on config 4b) and keeps the scalar loads.
+    float model[12], n9[9];
+    uint32_t material_index, light_index, vertex_base;
+    if (!LIGHTS) {
+        uint4 oa, ob, oc, od, oe, of;
+        ldg256(reinterpret_cast<const uint4*>(obj), oa, ob);
+        ldg256(reinterpret_cast<const uint4*>(obj) + 2, oc, od);
+        ldg256(reinterpret_cast<const uint4*>(obj) + 4, oe, of);
+        const uint32_t w[21] = {oa.x, oa.y, oa.z, oa.w, ob.x, ob.y, ob.z, ob.w, oc.x, oc.y, oc.z, oc.w, od.x, od.y, od.z, od.w, oe.x, oe.y, oe.z, oe.w, of.x};
 #pragma unroll
-    for (int k = 0; k < 12; k++) model[k] = __ldg(&obj->model[k]);
+        for (int k = 0; k < 12; k++) model[k] = __uint_as_float(w[k]);
+#pragma unroll
+        for (int k = 0; k < 9; k++) n9[k] = __uint_as_float(w[12 + k]);
+        material_index = of.y; light_index = of.z; vertex_base = of.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 12; k++) model[k] = __ldg(&obj->model[k]);
+#pragma unroll
+        for (int k = 0; k < 9; k++) n9[k] = __ldg(&obj->nrm[k]);
+        material_index = __ldg(&obj->material_index); light_index = __ldg(&obj->light_index); vertex_base = __ldg(&obj->vertex_base);
+    }
+    const Mat mat = load_material(sc.materials + material_index);
+    const uint32_t* ip = sc.indices + __ldg(&obj->index_base) + 3u * hit.prim;
+    const rt_vertex* vb = sc.vertices + vertex_base;
+    vec3 p0, p1, p2, m0, m1, m2;
+    if (!LIGHTS) {
+        load_vertex(vb + __ldg(ip), &p0, &m0);
+        load_vertex(vb + __ldg(ip + 1), &p1, &m1);
+        load_vertex(vb + __ldg(ip + 2), &p2, &m2);
+    } else {
+        const rt_vertex *v0 = vb + __ldg(ip), *v1 = vb + __ldg(ip + 1), *v2 = vb + __ldg(ip + 2);
+        p0 = vertex_pos(v0); p1 = vertex_pos(v1); p2 = vertex_pos(v2);
+        m0 = vertex_nrm(v0); m1 = vertex_nrm(v1); m2 = vertex_nrm(v2);
+    }
+    const float bx = (1.0f - hit.u) - hit.v, by = hit.u, bz = hit.v;
     vec3 pos = add3(add3(scale3(p0, bx), scale3(p1, by)), scale3(p2, bz));
     vec3 world_pos = xf_point(model, pos);
-    vec3 nrm = normalize3(add3(add3(scale3(vertex_nrm(v0), bx), scale3(vertex_nrm(v1), by)), scale3(vertex_nrm(v2), bz)));
-    float n9[9];
-#pragma unroll
-    for (int k = 0; k < 9; k++) n9[k] = __ldg(&obj->nrm[k]);
+    vec3 nrm = normalize3(add3(add3(scale3(m0, bx), scale3(m1, by)), scale3(m2, bz)));
     vec3 N = normalize3(mat3_mul(n9, nrm));
     if (!(dot3(N, neg3(ray_dir)) > 0.0f)) N = neg3(N);
     const bool is_emissive = mat.emission_power > 0.0f;
@@ -395,7 +427,7 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
             if (nee_select(sc, world_pos, hit.inst, ps.seed, &nq->light, &nq->sel_pdf, &nq->r_tri, &nq->q1, &nq->q2)) {
                 nq->pending = true;
                 nq->x = world_pos; nq->N = N; nq->wo = wo; nq->throughput = ps.throughput;
-                nq->material = __ldg(&obj->material_index);
+                nq->material = material_index;
                 n_nee++;
             }
         } else if (LIGHTS) {
@@ -419,7 +451,7 @@ __device__ __forceinline__ ShadeResult shade_hit(const SceneView& sc, PathState&
             out.emissive_add = true;
             out.emissive = scale3(mul3(ps.throughput, mat.emission_color), mat.emission_power);
         } else if (!ps.did_direct) {
-            const uint32_t li = __ldg(&obj->light_index);
+            const uint32_t li = light_index;
             const DevLight* light = sc.lights + li;
             float tr[12];
 #pragma unroll

@@ -164,11 +164,6 @@ __device__ __forceinline__ uint32_t node_hits(const uint4 w0, const uint4 w1, co
 #ifndef RT_NODE_LDG256
 #define RT_NODE_LDG256 1
 #endif
-__device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
-    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-                 : "l"(p));
-}
 __device__ __forceinline__ uint4 sel4(bool c, uint4 a, uint4 b) {
     return make_uint4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
 }

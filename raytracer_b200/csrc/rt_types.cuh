@@ -6,6 +6,7 @@
 //   LightData   (shaders/ray_common.glsl:42-46, gpu_scene.odin:31-36)  -> DevLight
 //   TLAS/BLAS   (acceleration_structure.odin:65-199, driver-opaque)    -> Node8 + BvhTri
 #pragma once
+#include <stddef.h>
 #include <stdint.h>
 
 #include "../../include/rt_api.h"
@@ -63,6 +64,9 @@ struct __align__(16) DevObject {  // 128 B
     uint32_t pad[4];
 };
 static_assert(sizeof(DevObject) == 128, "DevObject is 128 bytes");
+static_assert(offsetof(DevObject, nrm) == 48 && offsetof(DevObject, material_index) == 84 && offsetof(DevObject, light_index) == 88 &&
+                  offsetof(DevObject, vertex_base) == 92 && offsetof(DevObject, index_base) == 96,
+              "shade_hit reads DevObject as six 16-byte words");
 
 struct __align__(16) DevLight {  // 64 B
     float transform[12];  // as DevObject.model
@@ -120,5 +124,16 @@ RT_HD uint32_t strip_global_row(uint32_t local_row, uint32_t strip_rows, uint32_
     uint32_t band = local_row / strip_rows, r = local_row % strip_rows;
     return (band * strip_count + strip_index) * strip_rows + r;
 }
+
+#if defined(__CUDACC__)
+// 256-bit read-only load (sm_100 LDG.256); p must be 32-byte aligned.  A load whose threads sit in different lines costs
+// the SM's L1 pipe one cycle per thread whatever its width (profiles/r1q_gather_microbench.md), so wide loads are how
+// a divergent gather gets cheaper.
+__device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(p));
+}
+#endif
 
 }  // namespace rt
