@@ -1051,9 +1051,12 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         n_launch += 3;
         q_in ^= 1u;
     }
+    // batches fold into the image in frame order, whichever stream they ran on
+    if (res.wait_accumulate) FRAME_TRY(cudaStreamWaitEvent(stream, res.wait_accumulate, 0));
     pf.begin(RT_K_ACCUMULATE, stream);
     wf_accumulate_kernel<<<gb_px, 256, 0, stream>>>(fp, v, res.image);
     pf.end(stream);
+    if (res.done_accumulate) FRAME_TRY(cudaEventRecord(res.done_accumulate, stream));
     n_launch++;
     if (res.launches) *res.launches += n_launch;
     FRAME_TRY(cudaGetLastError());

@@ -121,6 +121,8 @@ struct FrameResources {
     WavefrontBuffers* wf = nullptr;
     KernelProfiler* prof = nullptr;
     uint64_t* launches = nullptr;  // host-side launch counter
+    cudaEvent_t wait_accumulate = nullptr;  // the accumulation of this batch waits for this event (the previous batch's, other stream)
+    cudaEvent_t done_accumulate = nullptr;  // recorded after the accumulation of this batch
 };
 int wavefront_alloc(WavefrontBuffers** wf, uint32_t n_pixels, std::string& err);
 void wavefront_free(WavefrontBuffers* wf);
@@ -178,6 +180,11 @@ struct rt_ctx {
     rt::DevBuf<uchar4> srgb;
     rt::DevBuf<rt::DevCounters> counters;
     rt::WavefrontBuffers* wf = nullptr;
+    // second half of the frames in flight: consecutive batches alternate between two streams and two sets of path state, so
+    // that the tail of one batch's kernels (few blocks left, SMs idle) is filled by the next batch's
+    rt::WavefrontBuffers* wf2 = nullptr;
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_acc[2] = {nullptr, nullptr};
     // g-buffer images (allocated on first use)
     rt::DevBuf<uchar4> g_albedo, g_output;
     rt::DevBuf<ushort4> g_normal, g_emission;
