@@ -20,6 +20,16 @@ static thread_local std::string g_create_error;
     cudaSetDevice((ctx)->device);
 #define set_error ctx->set_error
 
+static bool create_side_streams(rt_ctx* ctx) {
+    for (int k = 0; k < RT_N_STREAMS; k++)
+        if (cudaEventCreateWithFlags(&ctx->ev_acc[k], cudaEventDisableTiming) != cudaSuccess) return false;
+    for (int k = 0; k < RT_N_STREAMS - 1; k++)
+        if (cudaStreamCreateWithFlags(&ctx->streamx[k], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming) != cudaSuccess)
+            return false;
+    return true;
+}
+
 extern "C" {
 
 const char* rt_version(void) { return "raytracer_b200 librt 0.1 (sm_100a)"; }
@@ -85,11 +95,7 @@ int rt_create(const rt_config* cfg_in, rt_ctx** out) {
         }
     }
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->ev_acc[0], cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->ev_acc[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess || !create_side_streams(ctx) ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
         ctx->counters.alloc(1) != cudaSuccess) {
         g_create_error = std::string("rt_create: ") + cudaGetErrorString(cudaGetLastError());
@@ -105,11 +111,13 @@ void rt_destroy(rt_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    if (ctx->stream2) cudaStreamSynchronize(ctx->stream2);
+    for (cudaStream_t st : ctx->streamx) if (st) cudaStreamSynchronize(st);
     if (ctx->wf) wavefront_free(ctx->wf);
-    if (ctx->wf2) wavefront_free(ctx->wf2);
-    for (cudaEvent_t e : {ctx->ev_fork, ctx->ev_join, ctx->ev_acc[0], ctx->ev_acc[1]}) if (e) cudaEventDestroy(e);
-    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+    for (rt::WavefrontBuffers* w : ctx->wfx) if (w) wavefront_free(w);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    for (cudaEvent_t e : ctx->ev_join) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->ev_acc) if (e) cudaEventDestroy(e);
+    for (cudaStream_t st : ctx->streamx) if (st) cudaStreamDestroy(st);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     for (int k = 0; k < 2; k++) if (ctx->user_ev[k]) cudaEventDestroy(ctx->user_ev[k]);
@@ -429,7 +437,7 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     ctx->rs_history = false;
     ctx->rs_surf.release(); ctx->rs_cur.release(); ctx->rs_hist[0].release(); ctx->rs_hist[1].release();
     if (ctx->wf) { wavefront_free(ctx->wf); ctx->wf = nullptr; }
-    if (ctx->wf2) { wavefront_free(ctx->wf2); ctx->wf2 = nullptr; }
+    for (rt::WavefrontBuffers*& w : ctx->wfx) if (w) { wavefront_free(w); w = nullptr; }
     if (ctx->cfg.pipeline == RT_PIPELINE_WAVEFRONT) {
         std::string err;
 #ifndef RT_TWO_STREAM_MIN_LANES
@@ -443,12 +451,12 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
         const uint64_t per_lane = std::max<uint64_t>(n, 1) * 200ull;
         lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, ((uint64_t)RT_STATE_CAP_GIB << 30) / per_lane));
         lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, 0x7FFFFFFFull / std::max<uint64_t>(n, 1)));
-        // from RT_TWO_STREAM_MIN_LANES frames in flight on, the path state is split into two halves for two streams
-        const bool two = lanes >= RT_TWO_STREAM_MIN_LANES;
-        if (two) lanes = (lanes + 1) / 2;
+        // from RT_TWO_STREAM_MIN_LANES frames in flight on, the path state is split into equal shares for RT_N_STREAMS streams
+        const bool split = lanes >= RT_TWO_STREAM_MIN_LANES;
+        if (split) lanes = (lanes + RT_N_STREAMS - 1) / RT_N_STREAMS;
         ctx->lanes = (uint32_t)lanes;
         int rc = wavefront_alloc(&ctx->wf, (uint32_t)(n * lanes), err);
-        if (rc == RT_OK && two) rc = wavefront_alloc(&ctx->wf2, (uint32_t)(n * lanes), err);
+        for (int k = 0; k < RT_N_STREAMS - 1 && rc == RT_OK && split; k++) rc = wavefront_alloc(&ctx->wfx[k], (uint32_t)(n * lanes), err);
         if (rc != RT_OK) { set_error(err); return rc; }
     }
     return RT_OK;
@@ -477,14 +485,20 @@ static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const floa
     // equal batches: 256 frames with room for 145 in flight run as 128 + 128, not 145 + 111
     const uint32_t n_batches = mega ? n_frames : (n_frames + ctx->lanes - 1u) / std::max(ctx->lanes, 1u);
     const uint32_t per_batch = mega ? 1u : (n_frames + std::max(n_batches, 1u) - 1u) / std::max(n_batches, 1u);
-    // Two streams when there is more than one batch (and no per-kernel profiling, whose event pairs want the launches
-    // serialised): batch b runs on stream b % 2 with its own path state; only the accumulations are ordered across streams.
-    const bool two = !mega && ctx->wf2 && n_batches > 1 && !ctx->prof.enabled;
-    if (two) {
-        if (cudaEventRecord(ctx->ev_fork, ctx->stream) != cudaSuccess || cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0) != cudaSuccess) {
-            set_error(std::string("rt_trace_frames: ") + cudaGetErrorString(cudaGetLastError()));
-            return RT_ERR_CUDA;
-        }
+    // Several streams when there is more than one batch (and no per-kernel profiling, whose event pairs want the launches
+    // serialised): batch b runs on stream b % RT_N_STREAMS with its own path state; only the accumulations are ordered
+    // across streams.
+    const bool multi = !mega && RT_N_STREAMS > 1 && ctx->wfx[0] && n_batches > 1 && !ctx->prof.enabled;
+    const uint32_t n_str = multi ? std::min<uint32_t>(RT_N_STREAMS, n_batches) : 1u;
+    auto cuda_fail = [&](cudaError_t e) {
+        if (e == cudaSuccess) return false;
+        set_error(std::string("rt_trace_frames: ") + cudaGetErrorString(e));
+        return true;
+    };
+    if (multi) {
+        if (cuda_fail(cudaEventRecord(ctx->ev_fork, ctx->stream))) return RT_ERR_CUDA;
+        for (uint32_t k = 1; k < n_str; k++)
+            if (cuda_fail(cudaStreamWaitEvent(ctx->streamx[k - 1], ctx->ev_fork, 0))) return RT_ERR_CUDA;
     }
     uint32_t b = 0;
     for (uint32_t f = 0; f < n_frames; b++) {
@@ -493,20 +507,20 @@ static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const floa
         fp.frame_stride = frame_stride;
         fp.sample = first_sample + f;
         fp.n_lanes = mega ? 1u : std::min(per_batch, n_frames - f);
-        const uint32_t s = two ? (b & 1u) : 0u;
-        res.wf = s ? ctx->wf2 : ctx->wf;
-        res.wait_accumulate = (two && b > 0) ? ctx->ev_acc[(b - 1u) & 1u] : nullptr;
-        res.done_accumulate = two ? ctx->ev_acc[b & 1u] : nullptr;
-        cudaStream_t st = s ? ctx->stream2 : ctx->stream;
+        const uint32_t s = b % n_str;
+        res.wf = s ? ctx->wfx[s - 1] : ctx->wf;
+        res.wait_accumulate = (multi && b > 0) ? ctx->ev_acc[(b - 1u) % n_str] : nullptr;
+        res.done_accumulate = multi ? ctx->ev_acc[s] : nullptr;
+        cudaStream_t st = s ? ctx->streamx[s - 1] : ctx->stream;
         rc = mega ? launch_frame_megakernel(sc, fp, res, st, err) : launch_frame_wavefront(sc, fp, res, st, err);
         if (rc != RT_OK) { set_error(err); return rc; }
         f += fp.n_lanes;
     }
-    if (two) {  // everything on the second stream precedes its last accumulation or is ordered by the join
-        if (cudaEventRecord(ctx->ev_join, ctx->stream2) != cudaSuccess || cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0) != cudaSuccess) {
-            set_error(std::string("rt_trace_frames: ") + cudaGetErrorString(cudaGetLastError()));
-            return RT_ERR_CUDA;
-        }
+    if (multi) {  // the context's stream continues once every side stream has finished its batches
+        for (uint32_t k = 1; k < n_str; k++)
+            if (cuda_fail(cudaEventRecord(ctx->ev_join[k - 1], ctx->streamx[k - 1])) ||
+                cuda_fail(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[k - 1], 0)))
+                return RT_ERR_CUDA;
     }
     ctx->frames_traced += n_frames;
     rt_end_timing(ctx);

@@ -148,6 +148,9 @@ struct HostMesh {
     uint32_t vertex_base = 0, index_base = 0;
 };
 
+#ifndef RT_N_STREAMS
+#define RT_N_STREAMS 2
+#endif
 struct rt_ctx {
     rt_config cfg;
     int device = 0;
@@ -180,11 +183,11 @@ struct rt_ctx {
     rt::DevBuf<uchar4> srgb;
     rt::DevBuf<rt::DevCounters> counters;
     rt::WavefrontBuffers* wf = nullptr;
-    // second half of the frames in flight: consecutive batches alternate between two streams and two sets of path state, so
-    // that the tail of one batch's kernels (few blocks left, SMs idle) is filled by the next batch's
-    rt::WavefrontBuffers* wf2 = nullptr;
-    cudaStream_t stream2 = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_acc[2] = {nullptr, nullptr};
+    // the other shares of the frames in flight: consecutive batches rotate over RT_N_STREAMS streams, each with its own path
+    // state, so that the tail of one batch's kernels (few blocks left, SMs idle) is filled by the next batch's
+    rt::WavefrontBuffers* wfx[RT_N_STREAMS - 1] = {};    // path state of streams 1 .. RT_N_STREAMS - 1 (stream 0 uses wf)
+    cudaStream_t streamx[RT_N_STREAMS - 1] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[RT_N_STREAMS - 1] = {}, ev_acc[RT_N_STREAMS] = {};
     // g-buffer images (allocated on first use)
     rt::DevBuf<uchar4> g_albedo, g_output;
     rt::DevBuf<ushort4> g_normal, g_emission;
