@@ -268,7 +268,7 @@ static V3 evaluateLightMIS(const Ctx& cx, V3 hitPos, V3 normal, const Material& 
     return radiance;
 }
 
-// simple.rchit:543-583
+// simple.rchit:543-583 estimateDirectLightingMIS_PowerImportance (reached through the one-line wrapper estimateDirectLightingMIS, :586-588)
 static V3 estimateDirectLighting(const Ctx& cx, V3 hitPos, V3 normal, const Material& material, V3 viewDir,
                                  uint32_t currentObjectIndex, uint32_t& seed) {
     const Scene& s = *cx.s;
@@ -296,7 +296,7 @@ static V3 estimateDirectLighting(const Ctx& cx, V3 hitPos, V3 normal, const Mate
     return evaluateLightMIS(cx, hitPos, normal, material, viewDir, (uint32_t)selectedLight, lightPdf, seed);
 }
 
-// simple.rchit:536-541 with :522-534 (no skip)
+// simple.rchit:536-541 computeLightSelectionPdf with :522-534 computeTotalLightWeight (no skip)
 static float computeLightSelectionPdf(const Ctx& cx, V3 hitPos, uint32_t lightIdx) {
     float weight = computeLightWeight(cx, hitPos, lightIdx);
     int numLights = (int)cx.s->lights.size();
@@ -452,7 +452,7 @@ static V3 raygenPixel(const Ctx& cx, const float* cam, const float* clear, uint3
                       uint32_t W, uint32_t H) {
     uint32_t seed = tea(y * W + x, frame);
     float jx = 0.5f, jy = 0.5f;
-    if (frame != 0) {  // simple.rgen:25-38
+    if (frame != 0) {  // simple.rgen:25-38 getSampleOffset
         float r1 = rnd(seed);
         float r2 = rnd(seed);
         jx = 0.5f + (r1 - 0.5f) * 0.4f;

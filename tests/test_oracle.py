@@ -122,3 +122,94 @@ def test_soup_oracle_counters_are_sane(oracle_lib):
     orc.render(rb.Camera(position=(0.5, 0.5, -2.0), target=(0.5, 0.5, 0.5)).ubo(), CLEAR, 1, 32, 32, counters=cnt)
     ext, sh, nodes, tris, hits, nee = (int(x) for x in cnt)
     assert 32 * 32 <= ext <= 3 * 32 * 32 and hits <= ext and nee <= hits and sh <= nee and nodes >= ext
+
+
+# ---- pins against the reference's SHIPPED SPIR-V (tests/golden/spirv_constants.json, made by tools/spirv_constants.py) ----
+def _source_literals(paths):
+    """f32 bit patterns and u32 values of every numeric literal in the given C++ sources (comments stripped)."""
+    import re
+    import struct
+    src = "".join(open(p).read() for p in paths)
+    src = re.sub(r"//.*", "", src)
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    f32, u32 = set(), set()
+    for m in re.finditer(r"(?<![\w.])(\d+\.\d*(?:[eE][+-]?\d+)?|\.\d+(?:[eE][+-]?\d+)?|\d+[eE][+-]?\d+)f?\b", src):
+        f32.add(struct.unpack("<I", struct.pack("<f", float(m.group(1))))[0])
+    for m in re.finditer(r"(?<![\w.])(0[xX][0-9a-fA-F]+|\d+)[uU]?\b", src):
+        u32.add(int(m.group(1), 0) & 0xFFFFFFFF)
+        f32.add(struct.unpack("<I", struct.pack("<f", float(int(m.group(1), 0) & 0xFFFFFFFF)))[0])
+    return f32, u32
+
+
+def _spirv():
+    import json
+    return json.load(open(os.path.join(GOLDEN, "spirv_constants.json")))
+
+
+@pytest.mark.parametrize("where", ["oracle", "cuda"])
+def test_constants_are_the_shipped_ones(where):
+    """SURVEY §8(c) pin (2): every 32-bit float / unsigned literal of the shipped rgen.spv, rchit.spv, restir_rgen.spv
+    and restir_rchit.spv (the binaries raytracing_renderer.odin:62-71 loads) appears, bit for bit, as a literal of the
+    CPU oracle — and of the CUDA headers, which restate the same math a second time."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if where == "oracle":
+        files = [os.path.join(root, "oracle", f) for f in ("oracle_render.cpp", "oracle_math.h", "oracle_scene.h", "oracle_api.cpp")]
+    else:
+        files = [os.path.join(root, "raytracer_b200", "csrc", f) for f in
+                 ("rt_math.cuh", "rt_shade.cuh", "rt_frame.cu", "rt_types.cuh", "rt_internal.h", "rt_trav.cuh", "rt_api.cu", "rt_restir.cu")]
+    f32, u32 = _source_literals(files)
+    # the firefly clamp min(color, 5) of simple.rgen:121 is a run-time field on both sides (rt_config.radiance_clamp,
+    # orc_render's `clamp`), default 5.0 in both bindings: checked below instead of as a literal
+    configurable = {0x40A00000}
+    spv = _spirv()
+    for mod in ("rgen.spv", "rchit.spv", "restir_rgen.spv", "restir_rchit.spv"):
+        r = spv[mod]
+        missing = [v for v, b in zip(r["f32"], r["f32_bits"])
+                   if b not in f32 and (b ^ 0x80000000) not in f32 and b not in configurable]
+        assert not missing, f"{mod}: float constants of the shipped shader with no literal in the {where} sources: {missing}"
+        missing = [v for v in r["u32"] if v not in u32]
+        assert not missing, f"{mod}: unsigned constants of the shipped shader with no literal in the {where} sources: {missing}"
+    import inspect
+    from oracle.binding import OracleScene
+    from raytracer_b200.librt import Context
+    assert inspect.signature(OracleScene.render).parameters["clamp"].default == 5.0
+    assert inspect.signature(Context.__init__).parameters["radiance_clamp"].default == 5.0
+    assert inspect.signature(Context.__init__).parameters["max_depth"].default == 3      # MAX_DEPTH, rgen.spv i32 3
+
+
+def test_rng_constants_are_the_shipped_ones(oracle_lib):
+    """The TEA key schedule / LCG multipliers the NumPy restatement above uses are the ones inside rgen.spv, and the
+    24-bit mantissa scale of rnd() (random.glsl:49-53) is there as 16777215 & / 16777216.0."""
+    r = _spirv()["rgen.spv"]
+    for c in (0x9E3779B9, 0xA341316C, 0xC8013EA4, 0xAD90777D, 0x7E95761E, 1664525, 1013904223, 0x00FFFFFF, 16):
+        assert c in r["u32"], hex(c)
+    assert 16777216.0 in r["f32"]
+    vals, state = oracle_lib.rnd_seq(0x12345678, 1)
+    assert state == (1664525 * 0x12345678 + 1013904223) & 0xFFFFFFFF
+
+
+def test_shipped_call_graph_is_the_restated_one():
+    """Which GLSL functions the shipped closest-hit / ray-gen `main` reaches (OpFunctionCall walk of the binaries).
+    SURVEY §8(c): brdfHitsSelectedLightRQ, misWeight, lightPdfFromTriangleHitParams and calculatePDF are source-only,
+    and NEE goes through estimateDirectLightingMIS -> ..._PowerImportance -> evaluateLightMIS -> sampleLight / isVisibleRQ."""
+    spv = _spirv()
+    chit = spv["rchit.spv"]
+    assert chit["entry_points"] == [["ClosestHitKHR", "main"]]
+    for dead in ("brdfHitsSelectedLightRQ", "misWeight", "lightPdfFromTriangleHitParams", "calculatePDF"):
+        assert dead not in chit["calls"], dead
+    assert chit["calls"]["main"] == ["computeLightSelectionPdf", "cosTheta", "createBasis", "estimateDirectLightingMIS",
+                                     "localToWorld", "misWeightPower", "rnd", "sampleBRDF", "worldToLocal"]
+    assert chit["calls"]["estimateDirectLightingMIS"] == ["estimateDirectLightingMIS_PowerImportance"]
+    assert chit["calls"]["estimateDirectLightingMIS_PowerImportance"] == ["computeLightWeight", "evaluateLightMIS", "rnd"]
+    assert {"isVisibleRQ", "sampleLight", "misWeightPower", "evaluateFullBRDF"} <= set(chit["calls"]["evaluateLightMIS"])
+    assert chit["calls"]["sampleBRDF"] == ["F_Schlick", "cosTheta", "generateCosineWeightedDirection", "getSpecularProbability",
+                                           "microfacetF", "microfacetPDF", "rnd", "sampleGGX"]
+    assert sorted(chit["reachable"]) == sorted(chit["calls"])          # nothing else was compiled in
+    gen = spv["rgen.spv"]
+    assert gen["calls"]["main"] == ["calculateCameraRay", "getSampleOffset", "russianRoulette", "tea"]
+    assert gen["calls"]["russianRoulette"] == ["rnd"] and gen["calls"]["getSampleOffset"] == ["rnd"]
+    # every function the binaries reach is cited by name in the oracle's sources
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = "".join(open(os.path.join(root, "oracle", f)).read() for f in ("oracle_render.cpp", "oracle_math.h"))
+    uncited = [f for f in set(chit["reachable"]) | set(gen["reachable"]) if f != "main" and f not in text]
+    assert not uncited, f"functions of the shipped shaders the oracle does not cite: {uncited}"
