@@ -465,8 +465,11 @@ __device__ __forceinline__ float warp_fmax_signed(float v, bool neg) {
     return __uint_as_float(neg ? __reduce_min_sync(0xFFFFFFFFu, b) : __reduce_max_sync(0xFFFFFFFFu, b));
 }
 
+#ifndef RT_FUSED_RAYGEN
+#define RT_FUSED_RAYGEN 0 /* measured r1t: packet kernel 8.21 -> 11.97 ms per 64-frame batch, ray-gen launch saved 1.69: 0.506 -> 0.544 ms/frame; off */
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kernel(SceneView sc, WfView wf, uint32_t* fb_queue,
+__global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kernel(SceneView sc, FrameParams fp, WfView wf, uint32_t* fb_queue,
                                                                                   uint32_t width, uint32_t n_px,
                                                                                   DevCounters* counters) {
     constexpr int R = RT_PKT_RPL;
@@ -498,7 +501,27 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                 const uint32_t i = (g * R + (uint32_t)k) * 32u + lane;
                 if (i < n) valid |= 1u << k;
                 slot[k] = primary_slot(i < n ? i : n - 1u, width, n_px);
+#if RT_FUSED_RAYGEN
+                // the ray-gen shader runs here (simple.rgen:70-85): no ray-gen launch, no primary ray read back.  The hit
+                // shader wants the direction and the seeds, the per-ray kernel (packets handed back) the origin as well.
+                float4 o4, d4;
+                {
+                    const uint32_t lane_f = slot[k] / n_px, px = slot[k] - lane_f * n_px;
+                    const uint32_t lrow = px / width, x = px - lrow * width;
+                    const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+                    uint32_t seed;
+                    vec3 o, d;
+                    raygen_ray(fp, fp.frame + lane_f * fp.frame_stride, x, y, &seed, &o, &d);
+                    o4 = make_float4(o.x, o.y, o.z, 0.0f);
+                    d4 = make_float4(d.x, d.y, d.z, 0.0f);
+                    if (i < n) {
+                        wf.ray_d[slot[k]] = d4;
+                        wf.seeds[slot[k]] = make_uint2(seed, seed);
+                    }
+                }
+#else
                 const float4 o4 = wf.ray_o[slot[k]], d4 = wf.ray_d[slot[k]];
+#endif
                 const uint32_t sb = (__float_as_uint(d4.x) >> 31) | ((__float_as_uint(d4.y) >> 31) << 1) | ((__float_as_uint(d4.z) >> 31) << 2);
                 if (k == 0) {  // every lane executes every shuffle: no short-circuit around a *_sync call
                     sb0 = __shfl_sync(0xFFFFFFFFu, sb, 0);
@@ -529,6 +552,15 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                 base = __shfl_sync(0xFFFFFFFFu, base, 0);
                 if (v) fb_queue[base + __popc(bal & ((1u << lane) - 1u))] = slot[k];
             }
+#if RT_FUSED_RAYGEN
+            // origins are not compared lane by lane here (all equal inv_view's translation): the lane's own value is the ray's
+            if (valid) {
+                const float4 o4 = make_float4(fp.inv_view[12], fp.inv_view[13], fp.inv_view[14], 0.0f);
+#pragma unroll
+                for (int k = 0; k < R; k++)
+                    if ((valid >> k) & 1u) wf.ray_o[slot[k]] = o4;
+            }
+#endif
             continue;
         }
         if (COUNT) c_rays += __popc(valid);
@@ -989,10 +1021,13 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     KernelProfiler none;
     KernelProfiler& pf = res.prof ? *res.prof : none;
     uint64_t n_launch = 0;
-    pf.begin(RT_K_RAYGEN, stream);
-    wf_raygen_kernel<<<gb, 256, 0, stream>>>(fp, v);
-    pf.end(stream);
-    n_launch++;
+    // with packets on the first bounce the ray-gen shader runs inside the packet kernel
+    if (!RT_FUSED_RAYGEN || (fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
+        pf.begin(RT_K_RAYGEN, stream);
+        wf_raygen_kernel<<<gb, 256, 0, stream>>>(fp, v);
+        pf.end(stream);
+        n_launch++;
+    }
     uint32_t q_in = 0;
     // no more blocks than the widest possible queue needs
     const int need = (int)((n_slots + 127) / 128);
@@ -1002,7 +1037,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         if (depth == 0 && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
             // packets first; what they hand back (tiles across an axis plane) goes through the per-ray kernel
             pf.begin(RT_K_EXTEND_PACKET, stream);
-            wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, v, w->queue[0].p, fp.width, n_px,
+            wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, fp, v, w->queue[0].p, fp.width, n_px,
                                                                                      res.counters);
             pf.end(stream);
             pf.begin(RT_K_EXTEND, stream);

@@ -505,16 +505,22 @@ __device__ __forceinline__ void camera_ray(const FrameParams& fp, float px, floa
 }
 
 // simple.rgen:70-85: seed, jitter, primary ray, payload initialisation
-__device__ __forceinline__ void raygen_init(const FrameParams& fp, uint32_t x, uint32_t y, PathState& ps, vec3* o, vec3* d) {
-    uint32_t seed = tea16(y * fp.width + x, fp.frame);
+__device__ __forceinline__ void raygen_ray(const FrameParams& fp, uint32_t frame, uint32_t x, uint32_t y, uint32_t* seed_out, vec3* o, vec3* d) {
+    uint32_t seed = tea16(y * fp.width + x, frame);
     float jx = 0.5f, jy = 0.5f;
-    if (fp.frame != 0u) {
+    if (frame != 0u) {
         float r1 = rnd01(seed);
         float r2 = rnd01(seed);
         jx = 0.5f + (r1 - 0.5f) * 0.4f;
         jy = 0.5f + (r2 - 0.5f) * 0.4f;
     }
     camera_ray(fp, (float)x + jx, (float)y + jy, true, o, d);
+    *seed_out = seed;
+}
+
+__device__ __forceinline__ void raygen_init(const FrameParams& fp, uint32_t x, uint32_t y, PathState& ps, vec3* o, vec3* d) {
+    uint32_t seed;
+    raygen_ray(fp, fp.frame, x, y, &seed, o, d);
     ps.seed = seed;
     ps.rr_seed = seed;
     ps.color = splat3(0.0f);
