@@ -730,11 +730,13 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
             // the state behind the miss test is requested together with the hit record (one memory latency, not two)
             prefetch_l1(&wf.ray_d[slot]);
             prefetch_l1(&wf.seeds[slot]);
-            if (!FIRST) prefetch_l1(&wf.prev[slot]);
+            if (!FIRST && LIGHTS) prefetch_l1(&wf.prev[slot]);
             const uint4 hrec = wf.hit[slot];
             // first bounce: the payload initialisation of simple.rgen:76-85
             const float4 tv = FIRST ? make_float4(1.0f, 1.0f, 1.0f, 1.0f) : wf.thr[slot];
-            const float4 cv = FIRST ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : wf.col[slot];
+            // without lights a path's colour is zero until the sky term that ends it: nothing to read, and only that term
+            // (or the first bounce, which initialises the slot) to write
+            const float4 cv = (FIRST || !LIGHTS) ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : wf.col[slot];
             ps.throughput = mk3(tv.x, tv.y, tv.z);
             ps.prev_brdf_pdf = tv.w;
             ps.color = mk3(cv.x, cv.y, cv.z);
@@ -742,7 +744,9 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
             if (hrec.z == 0xFFFFFFFFu) {  // simple.rmiss:26-29 -> simple.rgen:106-109
                 sky = true;
             } else {
-                const float4 pv = FIRST ? make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(PF_FIRST)) : wf.prev[slot];
+                // previous hit point and bounce flags feed the emissive rules of simple.rchit:641-686 only: a scene without
+                // lights has no emissive surface, so its variant neither reads nor writes that record (32 B per path and bounce)
+                const float4 pv = (FIRST || !LIGHTS) ? make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(PF_FIRST)) : wf.prev[slot];
                 const float4 dv = wf.ray_d[slot];
                 const uint2 sd = wf.seeds[slot];
                 const uint32_t fl = __float_as_uint(pv.w);
@@ -770,13 +774,13 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
                 if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
                 if (sky) ps.color = add3(ps.color, mul3(ps.throughput, clearc));
             }
-            wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, ps.p_sample_light);
+            if (LIGHTS || FIRST || sky) wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, ps.p_sample_light);
             if (push_next) {
                 wf.ray_o[slot] = make_float4(res.next_origin.x, res.next_origin.y, res.next_origin.z, 0.0f);
                 wf.ray_d[slot] = make_float4(res.next_dir.x, res.next_dir.y, res.next_dir.z, 0.0f);
                 wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_brdf_pdf);
                 const uint32_t fl = (ps.is_specular ? PF_SPECULAR : 0u) | (ps.did_direct ? PF_DID_DIRECT : 0u);
-                wf.prev[slot] = make_float4(ps.prev_hit_pos.x, ps.prev_hit_pos.y, ps.prev_hit_pos.z, __uint_as_float(fl));
+                if (LIGHTS) wf.prev[slot] = make_float4(ps.prev_hit_pos.x, ps.prev_hit_pos.y, ps.prev_hit_pos.z, __uint_as_float(fl));
                 wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
             }
         }
