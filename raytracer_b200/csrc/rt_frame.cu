@@ -160,16 +160,15 @@ int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameRes
 // ================================================================================================
 // wavefront pipeline
 // ================================================================================================
-// Path state, SoA over pixel slots.  flag bits in prev.w:
+// Path state, SoA over pixel slots.  flag bits in ray_o.w (scenes with lights):
 enum { PF_FIRST = 1u, PF_SPECULAR = 2u, PF_DID_DIRECT = 4u };
 
 struct WavefrontBuffers {
     uint32_t n_slots = 0;
-    DevBuf<float4> ray_o;   // origin.xyz, -
+    DevBuf<float4> ray_o;   // origin.xyz = previousHitPos of the bounce that reads it, flags
     DevBuf<float4> ray_d;   // direction.xyz, -
     DevBuf<float4> thr;     // throughput.xyz, previousBrdfPdf
     DevBuf<float4> col;     // color.xyz, p_sample_light
-    DevBuf<float4> prev;    // previousHitPos.xyz, flags
     DevBuf<uint2> seeds;    // payload.seed, ray-gen seed
     DevBuf<uint4> hit;      // u bits, v bits, inst (0xFFFFFFFF = miss), prim
     DevBuf<uint32_t> queue[2];
@@ -187,7 +186,7 @@ int wavefront_alloc(WavefrontBuffers** out, uint32_t n_slots, std::string& err) 
     cudaError_t e = cudaSuccess;
     auto A = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
     A(w->ray_o.alloc(n_slots)); A(w->ray_d.alloc(n_slots)); A(w->thr.alloc(n_slots)); A(w->col.alloc(n_slots));
-    A(w->prev.alloc(n_slots)); A(w->seeds.alloc(n_slots)); A(w->hit.alloc(n_slots));
+    A(w->seeds.alloc(n_slots)); A(w->hit.alloc(n_slots));
     A(w->queue[0].alloc(n_slots)); A(w->queue[1].alloc(n_slots));
     A(w->sh_o.alloc(n_slots)); A(w->sh_d.alloc(n_slots)); A(w->sh_c.alloc(n_slots)); A(w->sh_e.alloc(n_slots)); A(w->sh_n.alloc(n_slots));
     A(w->ctrl.alloc(8));
@@ -202,7 +201,7 @@ int wavefront_alloc(WavefrontBuffers** out, uint32_t n_slots, std::string& err) 
 void wavefront_free(WavefrontBuffers* w) { delete w; }
 
 struct WfView {
-    float4 *ray_o, *ray_d, *thr, *col, *prev;
+    float4 *ray_o, *ray_d, *thr, *col;
     uint2* seeds;
     uint4* hit;
     float4 *sh_o, *sh_d, *sh_c, *sh_e, *sh_n;
@@ -245,7 +244,7 @@ __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView w
     // throughput, colour and previous-hit state start from constants: the first shade launch (FIRST = true)
     // supplies them itself instead of reading them back (saves 48 B written here and 48 B read there per ray)
     wf.ray_o[slot] = make_float4(o.x, o.y, o.z, 0.0f);
-    wf.ray_d[slot] = make_float4(d.x, d.y, d.z, 0.0f);
+    wf.ray_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(ps.seed));  // w: the seed again, for the light-less shade variant
     wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
 }
 
@@ -513,7 +512,7 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                     vec3 o, d;
                     raygen_ray(fp, fp.frame + lane_f * fp.frame_stride, x, y, &seed, &o, &d);
                     o4 = make_float4(o.x, o.y, o.z, 0.0f);
-                    d4 = make_float4(d.x, d.y, d.z, 0.0f);
+                    d4 = make_float4(d.x, d.y, d.z, __uint_as_float(seed));
                     if (i < n) {
                         wf.ray_d[slot[k]] = d4;
                         wf.seeds[slot[k]] = make_uint2(seed, seed);
@@ -706,9 +705,13 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 #ifndef RT_SHADE_LIT_MIN_BLOCKS
 #define RT_SHADE_LIT_MIN_BLOCKS 7  /* the variant with the NEE code: 72 registers + 176 B of spills still beat 6 blocks (1.279 -> 1.262 ms/frame, config 4b) */
 #endif
+#ifndef RT_PACK_SEEDS
+#define RT_PACK_SEEDS 1
+#endif
 template <bool COUNT, bool FIRST, bool LIGHTS>
 __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
                                                        uint32_t q_idx, uint32_t* q_out, int depth, DevCounters* counters) {
+    constexpr bool PACKED = !LIGHTS && RT_PACK_SEEDS;
     const uint32_t n = wf.ctrl[q_idx];
     uint32_t c_hits = 0, c_nee = 0;
     const uint32_t stride = gridDim.x * blockDim.x;
@@ -729,8 +732,8 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
             slot = q_in ? q_in[i] : i;
             // the state behind the miss test is requested together with the hit record (one memory latency, not two)
             prefetch_l1(&wf.ray_d[slot]);
-            prefetch_l1(&wf.seeds[slot]);
-            if (!FIRST && LIGHTS) prefetch_l1(&wf.prev[slot]);
+            if (!PACKED) prefetch_l1(&wf.seeds[slot]);
+            if (!FIRST && LIGHTS) prefetch_l1(&wf.ray_o[slot]);
             const uint4 hrec = wf.hit[slot];
             // first bounce: the payload initialisation of simple.rgen:76-85
             const float4 tv = FIRST ? make_float4(1.0f, 1.0f, 1.0f, 1.0f) : wf.thr[slot];
@@ -746,9 +749,13 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
             } else {
                 // previous hit point and bounce flags feed the emissive rules of simple.rchit:641-686 only: a scene without
                 // lights has no emissive surface, so its variant neither reads nor writes that record (32 B per path and bounce)
-                const float4 pv = (FIRST || !LIGHTS) ? make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(PF_FIRST)) : wf.prev[slot];
+                // With lights: the previous hit point IS the origin of the ray that got here (shade_hit sets both to the hit's
+                // world position), so the record is the ray-origin array itself, bounce flags in its w.
+                const float4 pv = (FIRST || !LIGHTS) ? make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(PF_FIRST)) : wf.ray_o[slot];
                 const float4 dv = wf.ray_d[slot];
-                const uint2 sd = wf.seeds[slot];
+                // light-less variant: throughput.w (previousBrdfPdf) is dead, so the two seeds ride in direction.w / throughput.w
+                // and the seeds array is not touched (first bounce: ray-gen left the one initial seed in direction.w)
+                const uint2 sd = PACKED ? make_uint2(__float_as_uint(dv.w), FIRST ? __float_as_uint(dv.w) : __float_as_uint(tv.w)) : wf.seeds[slot];
                 const uint32_t fl = __float_as_uint(pv.w);
                 ps.prev_hit_pos = mk3(pv.x, pv.y, pv.z);
                 ps.first_bounce = (fl & PF_FIRST) != 0u;
@@ -776,12 +783,11 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
             }
             if (LIGHTS || FIRST || sky) wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, ps.p_sample_light);
             if (push_next) {
-                wf.ray_o[slot] = make_float4(res.next_origin.x, res.next_origin.y, res.next_origin.z, 0.0f);
-                wf.ray_d[slot] = make_float4(res.next_dir.x, res.next_dir.y, res.next_dir.z, 0.0f);
-                wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, ps.prev_brdf_pdf);
-                const uint32_t fl = (ps.is_specular ? PF_SPECULAR : 0u) | (ps.did_direct ? PF_DID_DIRECT : 0u);
-                if (LIGHTS) wf.prev[slot] = make_float4(ps.prev_hit_pos.x, ps.prev_hit_pos.y, ps.prev_hit_pos.z, __uint_as_float(fl));
-                wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
+                const uint32_t fl = LIGHTS ? ((ps.is_specular ? PF_SPECULAR : 0u) | (ps.did_direct ? PF_DID_DIRECT : 0u)) : 0u;
+                wf.ray_o[slot] = make_float4(res.next_origin.x, res.next_origin.y, res.next_origin.z, __uint_as_float(fl));
+                wf.ray_d[slot] = make_float4(res.next_dir.x, res.next_dir.y, res.next_dir.z, PACKED ? __uint_as_float(ps.seed) : 0.0f);
+                wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, PACKED ? __uint_as_float(ps.rr_seed) : ps.prev_brdf_pdf);
+                if (!PACKED) wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
             }
         }
         const uint32_t qi = queue_push(&wf.ctrl[q_idx ^ 1u], push_next);
@@ -1004,7 +1010,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     if (n_slots == 0) return RT_OK;
     if (!w || w->n_slots < n_slots) { err = "wavefront buffers not allocated"; return RT_ERR_NO_TARGET; }
     WfView v;
-    v.ray_o = w->ray_o.p; v.ray_d = w->ray_d.p; v.thr = w->thr.p; v.col = w->col.p; v.prev = w->prev.p;
+    v.ray_o = w->ray_o.p; v.ray_d = w->ray_d.p; v.thr = w->thr.p; v.col = w->col.p;
     v.seeds = w->seeds.p; v.hit = w->hit.p; v.sh_o = w->sh_o.p; v.sh_d = w->sh_d.p; v.sh_c = w->sh_c.p; v.sh_e = w->sh_e.p; v.sh_n = w->sh_n.p;
     v.ctrl = w->ctrl.p;
 #ifndef RT_EXTEND_COOP
