@@ -231,12 +231,13 @@ __global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_cou
 // raygen: simple.rgen:70-85.  All slots enter bounce 0 (unless roulette is enabled from depth 0).
 // A launch covers fp.n_lanes consecutive frames ("lanes"): slot = lane * pixels + pixel, frame = fp.frame + lane * fp.frame_stride.
 __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView wf) {
-    const uint32_t n_px = fp.local_rows * fp.width;
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= n_px * fp.n_lanes) return;
-    const uint32_t lane_f = slot / n_px, px = slot - lane_f * n_px;
-    const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
-    const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+    // grid = (blocks across a row, local rows, lanes): the kernel is issue-bound (16 TEA rounds, IEEE divisions), and four
+    // integer divisions by run-time values to take a linear index apart were a sixth of its instructions
+    const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= fp.width) return;
+    const uint32_t lrow = blockIdx.y, lane_f = blockIdx.z;
+    const uint32_t slot = (lane_f * fp.local_rows + lrow) * fp.width + x;
+    const uint32_t y = fp.strip_count == 1u ? lrow : strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
     fp.frame += lane_f * fp.frame_stride;
     PathState ps;
     vec3 o, d;
@@ -739,7 +740,9 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
             const float4 tv = FIRST ? make_float4(1.0f, 1.0f, 1.0f, 1.0f) : wf.thr[slot];
             // without lights a path's colour is zero until the sky term that ends it: nothing to read, and only that term
             // (or the first bounce, which initialises the slot) to write
-            const float4 cv = (FIRST || !LIGHTS) ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : wf.col[slot];
+            // With lights the colour changes here only through an emissive or sky term that is not deferred to the shadow
+            // pass: it is read then (below), not up front, and p_sample_light rides in direction.w instead of colour.w.
+            const float4 cv = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
             ps.throughput = mk3(tv.x, tv.y, tv.z);
             ps.prev_brdf_pdf = tv.w;
             ps.color = mk3(cv.x, cv.y, cv.z);
@@ -756,6 +759,7 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
                 // light-less variant: throughput.w (previousBrdfPdf) is dead, so the two seeds ride in direction.w / throughput.w
                 // and the seeds array is not touched (first bounce: ray-gen left the one initial seed in direction.w)
                 const uint2 sd = PACKED ? make_uint2(__float_as_uint(dv.w), FIRST ? __float_as_uint(dv.w) : __float_as_uint(tv.w)) : wf.seeds[slot];
+                if (LIGHTS && !FIRST) ps.p_sample_light = dv.w;
                 const uint32_t fl = __float_as_uint(pv.w);
                 ps.prev_hit_pos = mk3(pv.x, pv.y, pv.z);
                 ps.first_bounce = (fl & PF_FIRST) != 0u;
@@ -777,15 +781,20 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
                 }
             }
             push_shadow = LIGHTS && nq.pending;
+            const bool col_term = !push_shadow && (res.emissive_add || sky);
+            if (LIGHTS && !FIRST && col_term) {
+                const float4 c = wf.col[slot];
+                ps.color = mk3(c.x, c.y, c.z);
+            }
             if (!push_shadow) {
                 if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
                 if (sky) ps.color = add3(ps.color, mul3(ps.throughput, clearc));
             }
-            if (LIGHTS || FIRST || sky) wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, ps.p_sample_light);
+            if (FIRST || (LIGHTS ? col_term : sky)) wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, 0.0f);
             if (push_next) {
                 const uint32_t fl = LIGHTS ? ((ps.is_specular ? PF_SPECULAR : 0u) | (ps.did_direct ? PF_DID_DIRECT : 0u)) : 0u;
                 wf.ray_o[slot] = make_float4(res.next_origin.x, res.next_origin.y, res.next_origin.z, __uint_as_float(fl));
-                wf.ray_d[slot] = make_float4(res.next_dir.x, res.next_dir.y, res.next_dir.z, PACKED ? __uint_as_float(ps.seed) : 0.0f);
+                wf.ray_d[slot] = make_float4(res.next_dir.x, res.next_dir.y, res.next_dir.z, PACKED ? __uint_as_float(ps.seed) : (LIGHTS ? ps.p_sample_light : 0.0f));
                 wf.thr[slot] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, PACKED ? __uint_as_float(ps.rr_seed) : ps.prev_brdf_pdf);
                 if (!PACKED) wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
             }
@@ -1026,7 +1035,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         g_shd0 = persistent_grid(wf_shade_kernel<COUNT, false, false>, 128);
         g_nee = persistent_grid(wf_nee_kernel<COUNT>, 128);
     }
-    const uint32_t gb = (n_slots + 255) / 256;
+    if (fp.local_rows > 65535u || fp.n_lanes > 65535u) { err = "wavefront pipeline: more than 65535 image rows or frames in flight"; return RT_ERR_INVALID_ARGUMENT; }
     const uint32_t gb_px = (n_px + 255) / 256;
     KernelProfiler none;
     KernelProfiler& pf = res.prof ? *res.prof : none;
@@ -1034,7 +1043,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     // with packets on the first bounce the ray-gen shader runs inside the packet kernel
     if (!RT_FUSED_RAYGEN || (fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
         pf.begin(RT_K_RAYGEN, stream);
-        wf_raygen_kernel<<<gb, 256, 0, stream>>>(fp, v);
+        wf_raygen_kernel<<<dim3((fp.width + 255u) / 256u, fp.local_rows, fp.n_lanes), 256, 0, stream>>>(fp, v);
         pf.end(stream);
         n_launch++;
     }
