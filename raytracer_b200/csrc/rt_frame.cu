@@ -230,23 +230,30 @@ __global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_cou
 
 // raygen: simple.rgen:70-85.  All slots enter bounce 0 (unless roulette is enabled from depth 0).
 // A launch covers fp.n_lanes consecutive frames ("lanes"): slot = lane * pixels + pixel, frame = fp.frame + lane * fp.frame_stride.
+__device__ __forceinline__ void raygen_slot(const FrameParams& fp, const WfView& wf, uint32_t x, uint32_t lrow, uint32_t lane_f) {
+    const uint32_t slot = (lane_f * fp.local_rows + lrow) * fp.width + x;
+    const uint32_t y = fp.strip_count == 1u ? lrow : strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+    uint32_t seed;
+    vec3 o, d;
+    raygen_ray(fp, fp.frame + lane_f * fp.frame_stride, x, y, &seed, &o, &d);
+    // throughput, colour and previous-hit state start from constants: the first shade launch (FIRST = true)
+    // supplies them itself instead of reading them back (saves 48 B written here and 48 B read there per ray)
+    wf.ray_o[slot] = make_float4(o.x, o.y, o.z, 0.0f);
+    wf.ray_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(seed));  // w: the seed again, for the light-less shade variant
+    wf.seeds[slot] = make_uint2(seed, seed);
+}
+
 __global__ void __launch_bounds__(256) wf_raygen_kernel(FrameParams fp, WfView wf) {
     // grid = (blocks across a row, local rows, lanes): the kernel is issue-bound (16 TEA rounds, IEEE divisions), and four
     // integer divisions by run-time values to take a linear index apart were a sixth of its instructions
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= fp.width) return;
-    const uint32_t lrow = blockIdx.y, lane_f = blockIdx.z;
-    const uint32_t slot = (lane_f * fp.local_rows + lrow) * fp.width + x;
-    const uint32_t y = fp.strip_count == 1u ? lrow : strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
-    fp.frame += lane_f * fp.frame_stride;
-    PathState ps;
-    vec3 o, d;
-    raygen_init(fp, x, y, ps, &o, &d);
-    // throughput, colour and previous-hit state start from constants: the first shade launch (FIRST = true)
-    // supplies them itself instead of reading them back (saves 48 B written here and 48 B read there per ray)
-    wf.ray_o[slot] = make_float4(o.x, o.y, o.z, 0.0f);
-    wf.ray_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(ps.seed));  // w: the seed again, for the light-less shade variant
-    wf.seeds[slot] = make_uint2(ps.seed, ps.rr_seed);
+    if (gridDim.y == fp.local_rows && gridDim.z == fp.n_lanes) {
+        raygen_slot(fp, wf, x, blockIdx.y, blockIdx.z);
+    } else {  // grid dimensions y and z stop at 65535: taller images / more lanes loop (the loop costs the usual case 5 %)
+        for (uint32_t lane_f = blockIdx.z; lane_f < fp.n_lanes; lane_f += gridDim.z)
+            for (uint32_t lrow = blockIdx.y; lrow < fp.local_rows; lrow += gridDim.y) raygen_slot(fp, wf, x, lrow, lane_f);
+    }
 }
 
 // ---- persistent ray fetch -------------------------------------------------------------------------
@@ -1035,7 +1042,6 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         g_shd0 = persistent_grid(wf_shade_kernel<COUNT, false, false>, 128);
         g_nee = persistent_grid(wf_nee_kernel<COUNT>, 128);
     }
-    if (fp.local_rows > 65535u || fp.n_lanes > 65535u) { err = "wavefront pipeline: more than 65535 image rows or frames in flight"; return RT_ERR_INVALID_ARGUMENT; }
     const uint32_t gb_px = (n_px + 255) / 256;
     KernelProfiler none;
     KernelProfiler& pf = res.prof ? *res.prof : none;
@@ -1043,7 +1049,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     // with packets on the first bounce the ray-gen shader runs inside the packet kernel
     if (!RT_FUSED_RAYGEN || (fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
         pf.begin(RT_K_RAYGEN, stream);
-        wf_raygen_kernel<<<dim3((fp.width + 255u) / 256u, fp.local_rows, fp.n_lanes), 256, 0, stream>>>(fp, v);
+        wf_raygen_kernel<<<dim3((fp.width + 255u) / 256u, std::min(fp.local_rows, 65535u), std::min(fp.n_lanes, 65535u)), 256, 0, stream>>>(fp, v);
         pf.end(stream);
         n_launch++;
     }

@@ -267,6 +267,26 @@ def test_many_frames_in_flight_equals_loop():
         b.close()
 
 
+def test_image_taller_than_a_grid_dimension():
+    """The ray-gen launch is a 3-D grid (x blocks, rows, frames in flight) whose y stops at 65535: a 3 x 70000 image takes the
+    loop's second trip and still equals the megakernel (one path per thread, linear index) bit for bit."""
+    scene = fixture_scene("cornell_pbr")
+    cam = _camera_for("cornell_pbr", 3.0 / 70000.0)
+    imgs = []
+    for pipeline in (librt.RT_PIPELINE_WAVEFRONT, librt.RT_PIPELINE_MEGAKERNEL):
+        c = librt.Context(device=0, pipeline=pipeline, frames_in_flight=2)
+        try:
+            c.build_scene(scene)
+            c.resize(3, 70000)
+            c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+            imgs.append(c.readback())
+        finally:
+            c.close()
+    assert imgs[0].shape[0] == 70000
+    assert np.array_equal(imgs[0].view(np.uint32), imgs[1].view(np.uint32))
+    assert len(np.unique(imgs[0][..., :3].reshape(-1, 3), axis=0)) > 100      # not a constant image
+
+
 def test_deeper_paths_and_roulette():
     """max_depth 8 with roulette from depth 3 (north_star's Sponza setting) — still the oracle's numbers."""
     scene = fixture_scene("cornell_pbr")
