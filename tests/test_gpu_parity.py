@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 import raytracer_b200 as rb
+from raytracer_b200.multi_gpu import local_row_count
 from conftest import CLEAR, fixture_scene, random_rays, soup_scene
 from oracle.binding import OracleScene
 from raytracer_b200 import librt
@@ -327,6 +328,7 @@ def test_strips_union_is_bit_identical():
         c.trace_frames(cam.ubo(), CLEAR, 0, 2)
         c.readback(got)
         rows += c.device_image()[1]
+        assert c.device_image()[1] == local_row_count(rank, 3, H, 8)  # the library and multi_gpu.py agree on the partition
         c.close()
     assert rows == H
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
