@@ -708,7 +708,8 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 // Colour terms are added in the reference's order: NEE, emissive, sky.  When the NEE term waits for
 // its visibility ray, the later terms travel with the shadow-queue entry and wf_shadow_kernel adds them.
 #ifndef RT_SHADE_MIN_BLOCKS
-#define RT_SHADE_MIN_BLOCKS 6  /* 80 registers: measured 0.219 -> 0.195 ms/frame against 4 blocks of 128 registers */
+#define RT_SHADE_MIN_BLOCKS 8  /* light-less variant.  6 blocks (80 registers) beat 4 (128): 0.219 -> 0.195 ms/frame; since the path-state diet (r1t) it fits 56 registers
+                                  without spills: 7 / 8 / 9 / 10 blocks per SM -> frame 0.4762 / 0.4717 / 0.4692 / 0.4715 ms (r1u A/B); config 5 (4K, depth 3): 0.752 / 0.744 / 0.850 / - -> 8 */
 #endif
 #ifndef RT_SHADE_LIT_MIN_BLOCKS
 #define RT_SHADE_LIT_MIN_BLOCKS 7  /* the variant with the NEE code: 72 registers + 176 B of spills still beat 6 blocks (1.279 -> 1.262 ms/frame, config 4b) */
