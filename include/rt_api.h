@@ -14,7 +14,9 @@
  * last failure is kept per context (rt_last_error).  Nothing aborts the host (the reference's
  * vk_check calls os.exit(1): src/raytracer/vulkan_context.odin:385-394).  The caller owns every
  * input array; the library copies during the call and keeps no host pointer.  One rt_ctx is
- * used from one host thread at a time; calls are ordered on the context's CUDA stream.
+ * used from one host thread at a time; calls are ordered on the context's CUDA stream.  Every call makes the
+ * context's device the calling thread's current CUDA device and leaves it so (multi-GPU contexts: the last device).
+ * Different contexts may be driven from different threads; nothing is shared between them.
  * There is no CPU fallback: rt_create fails with RT_ERR_NO_DEVICE when no sm_100 GPU is usable.
  */
 #ifndef RT_API_H
@@ -84,8 +86,26 @@ typedef struct rt_config {
      * one frame overlap the long first bounces of the others); the image is bit-identical to
      * frame-by-frame dispatch.  0 -> 8; at most 1024, and capped so the path-state arrays stay below 56 GiB. */
     uint32_t frames_in_flight;
-    uint32_t reserved[6];
+    /* Multi-GPU fan-out INSIDE the library: with n_devices >= 2 the context owns one sub-context per
+     * listed CUDA ordinal, the scene and BVH are replicated on each (deterministic builder -> identical BVH), the image's
+     * strips are dealt to the devices (device k = strip_index k of strip_count n_devices), every rt_* call fans out from
+     * the ONE calling host thread, and rt_readback gathers all strips into the caller's image.  The host's three calls
+     * stay three calls; `device`, `strip_index` and `strip_count` are ignored then.  n_devices 0 or 1 = `device` alone. */
+    uint32_t n_devices;
+    int32_t device_ids[8];
+    /* RT_BALANCE_*: how strips are assigned to the devices / ranks of a strip partition (strip_count > 1) */
+    uint32_t strip_balance;
+    uint32_t reserved[4];
 } rt_config;
+
+enum {
+    RT_BALANCE_ROUND_ROBIN = 0, /* strip s -> rank s % strip_count */
+    /* Strips are dealt by measured cost: whenever an accumulation restarts (frame_number 0) one calibration pass counts
+     * the rays every strip of the full frame costs, and the strips go to the ranks longest-processing-time first.  Every
+     * rank runs the same deterministic pass and so derives the same table without communication; seeds use global pixel
+     * indices, so the image stays bit-identical whatever the assignment. */
+    RT_BALANCE_COST = 1
+};
 
 /* scene.odin:10-13 / ray_common.glsl:48-51 — 24 B */
 typedef struct rt_vertex {
@@ -213,7 +233,9 @@ RT_API int rt_synchronize(rt_ctx* ctx);
 
 /* ---- consume ----------------------------------------------------------------------------
  * rt_readback: synchronises and copies this context's rows into a full-size W*H RGBA32F host
- * image (rows owned by other strips are left untouched). */
+ * image (rows owned by other strips are left untouched).  A multi-GPU context gathers the strips of all its
+ * devices: every device writes its rows straight into dst (side by side over their own PCIe links when dst is
+ * pinned host memory; staged copies otherwise). */
 RT_API int rt_readback(rt_ctx* ctx, float* dst_rgba32f, size_t bytes);
 /* what the blit to B8G8R8A8_SRGB shows (raytracing_renderer.odin:299-316): clamp01 + sRGB OETF */
 RT_API int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst_rgba8, size_t bytes);
@@ -221,6 +243,12 @@ RT_API int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst_rgba8, size_t bytes);
 RT_API int rt_device_image(rt_ctx* ctx, void** device_ptr, uint32_t* local_rows);
 /* checkpoint/resume of a long accumulation: upload a full-size image as the running mean */
 RT_API int rt_upload_accum(rt_ctx* ctx, const float* src_rgba32f, size_t bytes);
+/* strip partition in force (strip_count > 1 or a multi-GPU context): owners[s] = rank / device slot that renders strip s
+ * (rows s*strip_rows ...).  owners may be NULL to query n_strips.  With RT_BALANCE_COST the table changes when an
+ * accumulation restarts after rt_resize or rt_rebalance; every rank of a partition derives the same table. */
+RT_API int rt_get_strip_owners(rt_ctx* ctx, uint32_t* owners, uint32_t capacity, uint32_t* n_strips);
+/* RT_BALANCE_COST: measure the strips again at the next frame_number == 0 trace (the camera settled somewhere else) */
+RT_API int rt_rebalance(rt_ctx* ctx);
 
 /* ---- G-buffer pass: shaders/restir.rgen:43-92, restir.rchit:36-59, restir.rmiss:18-20 ------ */
 RT_API int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]);

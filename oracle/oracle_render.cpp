@@ -178,6 +178,10 @@ static LightSample sampleLight(const Ctx& cx, uint32_t lightIdx, V3 hitPos, uint
     const Mesh& mesh = s.meshes[lo.mesh_index];
     uint32_t numTriangles = light.num_triangles;
     uint32_t triangleIdx = (uint32_t)(rnd(seed) * (float)numTriangles);
+    if (numTriangles == 0u) {  // DEFINED: a light whose mesh is empty (the shader would index triangle 0xFFFFFFFF) gives an
+        rnd(seed); rnd(seed);  // invalid sample; the two point draws are still taken
+        return r;
+    }
     if (triangleIdx > numTriangles - 1u) triangleIdx = numTriangles - 1u;
     const Vertex& v0 = mesh.v[mesh.idx[3 * triangleIdx]];
     const Vertex& v1 = mesh.v[mesh.idx[3 * triangleIdx + 1]];

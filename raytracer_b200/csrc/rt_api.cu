@@ -15,10 +15,22 @@ using namespace rt;
 
 static thread_local std::string g_create_error;
 
+// Every entry point makes the context's device current (and leaves it current: documented in rt_api.h).
 #define CTX_CHECK(ctx)                          \
     if (!(ctx)) return RT_ERR_INVALID_ARGUMENT; \
-    cudaSetDevice((ctx)->device);
+    if ((ctx)->children.empty()) cudaSetDevice((ctx)->device);
 #define set_error ctx->set_error
+// Multi-GPU contexts (rt_config.n_devices >= 2) own one child per device; an entry point that simply applies to every
+// device runs `call` (an expression in `c`) on each child from the calling thread — all of them are stream-ordered, so
+// the devices work concurrently — and reports the first failure.
+#define FANOUT(ctx, call)                                                   \
+    if (!(ctx)->children.empty()) {                                         \
+        for (rt_ctx* c : (ctx)->children) {                                 \
+            const int _rc = (call);                                         \
+            if (_rc != RT_OK) { (ctx)->error = c->error; return _rc; }      \
+        }                                                                   \
+        return RT_OK;                                                       \
+    }
 
 static bool create_side_streams(rt_ctx* ctx) {
     for (int k = 0; k < RT_N_STREAMS; k++)
@@ -47,6 +59,8 @@ void rt_default_config(rt_config* cfg) {
     cfg->strip_index = 0;
     cfg->strip_count = 1;
     cfg->frames_in_flight = 8;
+    cfg->n_devices = 0;
+    cfg->strip_balance = RT_BALANCE_ROUND_ROBIN;
 }
 
 const char* rt_last_error(const rt_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
@@ -69,6 +83,33 @@ int rt_create(const rt_config* cfg_in, rt_ctx** out) {
         g_create_error = "rt_create: only USE_DIRECT_LIGHTING=1, USE_MIS=1 (the shipped shader) is built";
         return RT_ERR_INVALID_ARGUMENT;
     }
+    if (cfg.n_devices > 8 || cfg.strip_balance > RT_BALANCE_COST) {
+        g_create_error = "rt_create: n_devices > 8 or unknown strip_balance";
+        return RT_ERR_INVALID_ARGUMENT;
+    }
+    if (cfg.n_devices >= 2) {
+        // one sub-context per device: device k renders strip_index k of strip_count n_devices
+        rt_ctx* parent = new rt_ctx();
+        parent->cfg = cfg;
+        parent->device = cfg.device_ids[0];
+        for (uint32_t k = 0; k < cfg.n_devices; k++) {
+            rt_config cc = cfg;
+            cc.n_devices = 0;
+            cc.device = cfg.device_ids[k];
+            cc.strip_index = k;
+            cc.strip_count = cfg.n_devices;
+            rt_ctx* child = nullptr;
+            const int rc = rt_create(&cc, &child);
+            if (rc != RT_OK) {
+                g_create_error = "rt_create: device " + std::to_string(cfg.device_ids[k]) + ": " + g_create_error;
+                rt_destroy(parent);
+                return rc;
+            }
+            parent->children.push_back(child);
+        }
+        *out = parent;
+        return RT_OK;
+    }
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
         cudaGetLastError();
@@ -87,11 +128,20 @@ int rt_create(const rt_config* cfg_in, rt_ctx** out) {
     rt_ctx* ctx = new rt_ctx();
     ctx->cfg = cfg;
     ctx->device = dev;
-    {   // keep freed scratch in the device's default pool (PoolBuf): rebuilds then reuse it without a driver round trip
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    {   // a private pool keeps the freed build scratch (PoolBuf): rebuilds then reuse it without a driver round trip, and the
+        // device's default pool — which the embedding host may use — keeps its own release policy
+        cudaMemPoolProps props;
+        memset(&props, 0, sizeof(props));
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        if (cudaMemPoolCreate(&ctx->pool, &props) == cudaSuccess) {
             uint64_t keep = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        } else {
+            cudaGetLastError();
+            ctx->pool = nullptr;  // PoolBuf then falls back to the default pool, untouched
         }
     }
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -109,6 +159,11 @@ int rt_create(const rt_config* cfg_in, rt_ctx** out) {
 
 void rt_destroy(rt_ctx* ctx) {
     if (!ctx) return;
+    if (!ctx->children.empty() || ctx->cfg.n_devices >= 2) {
+        for (rt_ctx* c : ctx->children) rt_destroy(c);
+        delete ctx;
+        return;
+    }
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (cudaStream_t st : ctx->streamx) if (st) cudaStreamSynchronize(st);
@@ -121,7 +176,9 @@ void rt_destroy(rt_ctx* ctx) {
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     for (int k = 0; k < 2; k++) if (ctx->user_ev[k]) cudaEventDestroy(ctx->user_ev[k]);
+    ctx->d_band_strip.release();
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     delete ctx;
 }
 
@@ -208,6 +265,7 @@ static int rebuild_bvh(rt_ctx* ctx) {
     in.n_objects = (uint32_t)ctx->objects.size();
     in.n_tris = ctx->n_tris;
     std::string err;
+    PoolScope pool_scope(ctx->pool);
     const int rc = build_bvh8(in, ctx->bvh, ctx->stream, err);
     if (rc != RT_OK) { set_error("rt_build_scene: " + err); return rc; }
     if (ctx->bvh.depth > RT_MAX_BVH_DEPTH) {
@@ -251,6 +309,7 @@ extern "C" {
 int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const rt_object* objects, uint32_t n_objects,
                    const rt_material* materials, uint32_t n_materials) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_build_scene(c, meshes, n_meshes, objects, n_objects, materials, n_materials));
     if ((n_meshes && !meshes) || (n_objects && !objects) || (n_materials && !materials)) {
         set_error("rt_build_scene: null array");
         return RT_ERR_INVALID_ARGUMENT;
@@ -306,6 +365,11 @@ int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const 
 int rt_scene_info_get(rt_ctx* ctx, rt_scene_info* out) {
     CTX_CHECK(ctx);
     if (!out) return RT_ERR_INVALID_ARGUMENT;
+    if (!ctx->children.empty()) {  // every device holds the same scene and (deterministic builder) the same BVH
+        const int rc0 = rt_scene_info_get(ctx->children[0], out);
+        if (rc0 != RT_OK) ctx->error = ctx->children[0]->error;
+        return rc0;
+    }
     const int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     memset(out, 0, sizeof(*out));
@@ -322,6 +386,7 @@ int rt_scene_info_get(rt_ctx* ctx, rt_scene_info* out) {
 // gpu_scene_update_material (gpu_scene.odin:562-601): overwrite the record, recompile the lights
 int rt_update_material(rt_ctx* ctx, uint32_t material_index, const rt_material* m) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_update_material(c, material_index, m));
     if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
     if (!m || material_index >= ctx->materials.size()) { set_error("rt_update_material: bad index"); return RT_ERR_INDEX_RANGE; }
     ctx->materials[material_index] = *m;
@@ -332,6 +397,7 @@ int rt_update_material(rt_ctx* ctx, uint32_t material_index, const rt_material* 
 // gpu_scene_update_object_transform (gpu_scene.odin:457-483): instance transform + TLAS update
 int rt_update_object_transform(rt_ctx* ctx, uint32_t object_index, const float model[16]) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_update_object_transform(c, object_index, model));
     if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
     if (!model || object_index >= ctx->objects.size()) { set_error("rt_update_object_transform: bad index"); return RT_ERR_INDEX_RANGE; }
     memcpy(ctx->objects[object_index].model, model, 64);
@@ -343,6 +409,7 @@ int rt_update_object_transform(rt_ctx* ctx, uint32_t object_index, const float m
 // gpu_scene_update_object with changed_material (gpu_scene.odin:517-560): the one place light_index is set
 int rt_update_object_material(rt_ctx* ctx, uint32_t object_index, uint32_t material_index) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_update_object_material(c, object_index, material_index));
     if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
     if (object_index >= ctx->objects.size() || material_index >= ctx->materials.size()) {
         set_error("rt_update_object_material: bad index");
@@ -364,6 +431,7 @@ int rt_update_object_material(rt_ctx* ctx, uint32_t object_index, uint32_t mater
 // gpu_scene_update_object_mesh (gpu_scene.odin:485-515)
 int rt_update_object_mesh(rt_ctx* ctx, uint32_t object_index, uint32_t mesh_index) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_update_object_mesh(c, object_index, mesh_index));
     if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
     if (object_index >= ctx->objects.size() || mesh_index >= ctx->meshes.size()) {
         set_error("rt_update_object_mesh: bad index");
@@ -398,6 +466,7 @@ void rt_fill_frame_params(const rt_ctx* ctx, const float* cam, const float* clea
     fp->strip_rows = ctx->cfg.strip_rows;
     fp->strip_index = ctx->cfg.strip_index;
     fp->strip_count = ctx->cfg.strip_count;
+    fp->band_strip = ctx->band_strip.empty() ? nullptr : ctx->d_band_strip.p;
     fp->local_rows = ctx->local_rows;
     fp->max_depth = ctx->cfg.max_depth;
     fp->rr_start = ctx->cfg.rr_start_depth;
@@ -416,6 +485,71 @@ void rt_end_timing(rt_ctx* ctx) {
     ctx->timing_pending = true;
 }
 
+// ---- strips by cost (RT_BALANCE_COST) -------------------------------------------------------------------------------
+// One calibration pass over the FULL frame (every rank runs the same deterministic pass and so derives the same table without
+// talking to anyone), then longest-processing-time-first under the constraint that every rank keeps the NUMBER of strips the
+// round-robin deal gives it — so the compact image, the path state and the frames in flight keep their sizes.
+#ifndef RT_BALANCE_SECONDARY_WEIGHT
+#define RT_BALANCE_SECONDARY_WEIGHT 6u  /* an incoherent continuation ray costs about six packet-traced primary rays */
+#endif
+static int balance_strips(rt_ctx* ctx, const float* camera_ubo, const float* clear_color, uint32_t frame) {
+    ctx->balance_pending = false;
+    const uint32_t sr = ctx->cfg.strip_rows, N = ctx->cfg.strip_count, H = ctx->height, W = ctx->width;
+    const uint32_t n_full = H / sr, n_strips = (H + sr - 1) / sr;
+    if (N <= 1 || n_full == 0) return RT_OK;
+    PoolScope pool_scope(ctx->pool);
+    PoolBuf<uint32_t> d_cost;
+    RT_CUDA_TRY(d_cost.alloc(H, ctx->stream));
+    RT_CUDA_TRY(cudaMemsetAsync(d_cost.p, 0, (size_t)H * 4, ctx->stream));
+    FrameParams fp;
+    rt_fill_frame_params(ctx, camera_ubo, clear_color, frame, &fp);
+    fp.strip_count = 1; fp.strip_index = 0; fp.band_strip = nullptr; fp.local_rows = H;
+    if (!ctx->dims.num_sms) cudaDeviceGetAttribute(&ctx->dims.num_sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    std::string err;
+    int rc = launch_row_cost(rt_scene_view(ctx), fp, d_cost.p, ctx->dims.num_sms > 0 ? ctx->dims.num_sms : 148, ctx->stream, err);
+    if (rc != RT_OK) { set_error(err); return rc; }
+    ctx->launches++;
+    std::vector<uint32_t> rows(H);
+    RT_CUDA_TRY(cudaMemcpyAsync(rows.data(), d_cost.p, (size_t)H * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    std::vector<uint64_t> cost(n_full);
+    for (uint32_t st = 0; st < n_full; st++) {
+        uint64_t extra = 0;
+        for (uint32_t r = 0; r < sr; r++) extra += rows[st * sr + r];
+        cost[st] = (uint64_t)sr * W + (uint64_t)RT_BALANCE_SECONDARY_WEIGHT * extra;
+    }
+    std::vector<uint32_t> order(n_full), cap(N, 0u);
+    for (uint32_t st = 0; st < n_full; st++) { order[st] = st; cap[st % N]++; }
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });  // ties: lower strip first
+    std::vector<uint64_t> load(N, 0ull);
+    ctx->strip_owner.assign(n_strips, 0u);
+    for (uint32_t st : order) {
+        uint32_t best = N;
+        for (uint32_t r = 0; r < N; r++)
+            if (cap[r] && (best == N || load[r] < load[best])) best = r;
+        ctx->strip_owner[st] = best;
+        load[best] += cost[st];
+        cap[best]--;
+    }
+    if (n_strips > n_full) ctx->strip_owner[n_full] = n_full % N;  // the partial last strip stays its round-robin owner's last band
+    ctx->band_strip.clear();
+    for (uint32_t st = 0; st < n_strips; st++)
+        if (ctx->strip_owner[st] == ctx->cfg.strip_index) ctx->band_strip.push_back(st);  // ascending: top to bottom
+    uint32_t rows_mine = 0;
+    for (uint32_t st : ctx->band_strip) rows_mine += std::min(sr, H - st * sr);
+    if (rows_mine != ctx->local_rows) {
+        set_error("balance_strips: row count changed");  // cannot happen: the capacities are the round-robin counts
+        return RT_ERR_CUDA;
+    }
+    RT_CUDA_TRY(ctx->d_band_strip.ensure(ctx->band_strip.size()));
+    if (!ctx->band_strip.empty())
+        RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_band_strip.p, ctx->band_strip.data(), ctx->band_strip.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->rs_history = false;   // per-pixel histories belong to the rows that were here before
+    ctx->has_gbuffer = false;
+    return RT_OK;
+}
+
 extern "C" {
 
 // raytracing_renderer_on_resize (raytracing_renderer.odin:108-126): new output image, accumulation restarts
@@ -425,10 +559,16 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
         set_error("rt_resize: bad extent");
         return RT_ERR_INVALID_ARGUMENT;
     }
+    if (!ctx->children.empty()) { ctx->width = width; ctx->height = height; }
+    FANOUT(ctx, rt_resize(c, width, height));
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->width = width;
     ctx->height = height;
     ctx->local_rows = count_local_rows(ctx->cfg, height);
+    // back to the round-robin assignment; with RT_BALANCE_COST the next frame-0 trace measures the strips of the new target
+    ctx->band_strip.clear();
+    ctx->strip_owner.clear();
+    ctx->balance_pending = ctx->cfg.strip_balance == RT_BALANCE_COST && ctx->cfg.strip_count > 1;
     const size_t n = (size_t)ctx->local_rows * width;
     RT_CUDA_TRY(ctx->image.alloc(n));
     RT_CUDA_TRY(cudaMemsetAsync(ctx->image.p, 0, std::max<size_t>(n, 1) * sizeof(float4), ctx->stream));
@@ -466,14 +606,21 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
 static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
                              uint32_t n_frames, uint32_t frame_stride, uint32_t first_sample) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, trace_frames_impl(c, camera_ubo, clear_color, first_frame, n_frames, frame_stride, first_sample));
     if (!camera_ubo || !clear_color) { set_error("rt_trace_frame: null argument"); return RT_ERR_INVALID_ARGUMENT; }
     if (frame_stride == 0) { set_error("rt_trace_frames_sliced: frame_stride must be >= 1"); return RT_ERR_INVALID_ARGUMENT; }
     int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
+    // an accumulation restarts: the strips may change hands (the image is overwritten by frame 0 anyway)
+    if (ctx->balance_pending && first_sample == 0u) {
+        rc = balance_strips(ctx, camera_ubo, clear_color, first_frame);
+        if (rc != RT_OK) return rc;
+    }
     const SceneView sc = rt_scene_view(ctx);
     FrameResources res;
+    res.dims = &ctx->dims;
     res.image = ctx->image.p;
     res.counters = ctx->counters.p;
     res.wf = ctx->wf;
@@ -543,6 +690,7 @@ int rt_trace_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_co
 
 int rt_synchronize(rt_ctx* ctx) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_synchronize(c));
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     return RT_OK;
 }
@@ -550,6 +698,17 @@ int rt_synchronize(rt_ctx* ctx) {
 int rt_last_trace_ms(rt_ctx* ctx, float* ms) {
     CTX_CHECK(ctx);
     if (!ms) return RT_ERR_INVALID_ARGUMENT;
+    if (!ctx->children.empty()) {  // the devices work side by side: the call took as long as the slowest
+        float worst = 0.0f;
+        for (rt_ctx* c : ctx->children) {
+            float m = 0.0f;
+            const int rc = rt_last_trace_ms(c, &m);
+            if (rc != RT_OK) { ctx->error = c->error; return rc; }
+            worst = std::max(worst, m);
+        }
+        *ms = worst;
+        return RT_OK;
+    }
     if (ctx->timing_pending) {
         RT_CUDA_TRY(cudaEventSynchronize(ctx->ev1));
         RT_CUDA_TRY(cudaEventElapsedTime(&ctx->last_ms, ctx->ev0, ctx->ev1));
@@ -559,47 +718,134 @@ int rt_last_trace_ms(rt_ctx* ctx, float* ms) {
     return RT_OK;
 }
 
-// copy the compact strip image into the rows this context owns of a full-size host image
-static int scatter_rows_to_host(rt_ctx* ctx, const void* d_src, void* dst, size_t bytes, size_t px_bytes) {
+}  // extern "C"
+
+// ---- rows between a context's compact strip image and a full-size host image --------------------------------------
+// global strip of local band b
+static inline uint32_t band_to_strip(const rt_ctx* ctx, uint32_t band) {
+    return ctx->band_strip.empty() ? band * ctx->cfg.strip_count + ctx->cfg.strip_index : ctx->band_strip[band];
+}
+
+// One thread per 16 bytes: the rows of this context's compact image written straight into a full-size image in PINNED host
+// memory (mapped into the device's address space).  One launch per device instead of one copy per band, and with several
+// devices every PCIe link carries its own rows at the same time.
+__global__ void scatter_rows_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, uint32_t row_words, uint32_t local_rows,
+                                    uint32_t strip_rows, uint32_t strip_index, uint32_t strip_count, const uint32_t* band_strip) {
+    const size_t n = (size_t)row_words * local_rows;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t lrow = (uint32_t)(i / row_words), w = (uint32_t)(i - (size_t)lrow * row_words);
+        const uint32_t band = lrow / strip_rows, r = lrow - band * strip_rows;
+        const uint32_t strip = band_strip ? band_strip[band] : band * strip_count + strip_index;
+        dst[(size_t)(strip * strip_rows + r) * row_words + w] = src[i];
+    }
+}
+
+// Queues the copies on the context's stream; the caller synchronises.  px_bytes is 4, 8, 16 or 32.
+static int scatter_rows_async(rt_ctx* ctx, const void* d_src, void* dst, size_t bytes, size_t px_bytes) {
     const size_t need = (size_t)ctx->width * ctx->height * px_bytes;
     if (!dst || bytes < need) { set_error("readback: destination too small"); return RT_ERR_INVALID_ARGUMENT; }
     const size_t row = (size_t)ctx->width * px_bytes;
+    if (ctx->local_rows == 0) return RT_OK;
     if (ctx->cfg.strip_count == 1) {
         RT_CUDA_TRY(cudaMemcpyAsync(dst, d_src, need, cudaMemcpyDeviceToHost, ctx->stream));
-    } else {
-        const uint32_t sr = ctx->cfg.strip_rows;
-        for (uint32_t lrow = 0; lrow < ctx->local_rows; lrow += sr) {  // one copy per band
-            const uint32_t rows = std::min(sr, ctx->local_rows - lrow);
-            const uint32_t y = strip_global_row(lrow, sr, ctx->cfg.strip_index, ctx->cfg.strip_count);
-            RT_CUDA_TRY(cudaMemcpyAsync((char*)dst + (size_t)y * row, (const char*)d_src + (size_t)lrow * row, rows * row,
-                                        cudaMemcpyDeviceToHost, ctx->stream));
-        }
+        return RT_OK;
     }
+    cudaPointerAttributes attr;
+    memset(&attr, 0, sizeof(attr));
+    if (cudaPointerGetAttributes(&attr, dst) != cudaSuccess) { cudaGetLastError(); attr.type = cudaMemoryTypeUnregistered; }
+    if (attr.type == cudaMemoryTypeHost && attr.devicePointer && (row % 16u) == 0u && ((uintptr_t)attr.devicePointer % 16u) == 0u) {
+        const uint32_t row_words = (uint32_t)(row / 16u);
+        const size_t n = (size_t)row_words * ctx->local_rows;
+        const uint32_t grid = (uint32_t)std::min<size_t>((n + 255) / 256, 4096);
+        scatter_rows_kernel<<<grid, 256, 0, ctx->stream>>>(reinterpret_cast<const uint4*>(d_src), reinterpret_cast<uint4*>(attr.devicePointer),
+                                                           row_words, ctx->local_rows, ctx->cfg.strip_rows, ctx->cfg.strip_index,
+                                                           ctx->cfg.strip_count, ctx->band_strip.empty() ? nullptr : ctx->d_band_strip.p);
+        RT_CUDA_TRY(cudaGetLastError());
+        ctx->launches++;
+        return RT_OK;
+    }
+    const uint32_t sr = ctx->cfg.strip_rows;
+    if (ctx->band_strip.empty()) {
+        // round robin: the bands sit at a constant pitch in the full image — one 2-D copy for the full bands, one for the rest
+        const uint32_t full = ctx->local_rows / sr, rest = ctx->local_rows - full * sr;
+        const uint32_t y0 = ctx->cfg.strip_index * sr;
+        if (full)
+            RT_CUDA_TRY(cudaMemcpy2DAsync((char*)dst + (size_t)y0 * row, (size_t)ctx->cfg.strip_count * sr * row, d_src, (size_t)sr * row,
+                                          (size_t)sr * row, full, cudaMemcpyDeviceToHost, ctx->stream));
+        if (rest)
+            RT_CUDA_TRY(cudaMemcpyAsync((char*)dst + (size_t)(band_to_strip(ctx, full) * sr) * row, (const char*)d_src + (size_t)full * sr * row,
+                                        (size_t)rest * row, cudaMemcpyDeviceToHost, ctx->stream));
+        return RT_OK;
+    }
+    for (uint32_t lrow = 0; lrow < ctx->local_rows; lrow += sr) {  // balanced assignment: one copy per band
+        const uint32_t rows = std::min(sr, ctx->local_rows - lrow);
+        const uint32_t y = band_to_strip(ctx, lrow / sr) * sr;
+        RT_CUDA_TRY(cudaMemcpyAsync((char*)dst + (size_t)y * row, (const char*)d_src + (size_t)lrow * row, rows * row,
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    return RT_OK;
+}
+
+static int scatter_rows_to_host(rt_ctx* ctx, const void* d_src, void* dst, size_t bytes, size_t px_bytes) {
+    const int rc = scatter_rows_async(ctx, d_src, dst, bytes, px_bytes);
+    if (rc != RT_OK) return rc;
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     return RT_OK;
 }
 
+// the devices of a multi-GPU context copy their rows side by side: queue everything, then wait for everyone
+template <typename Queue>
+static int gather_children(rt_ctx* ctx, Queue queue) {
+    for (rt_ctx* c : ctx->children) {
+        cudaSetDevice(c->device);
+        const int rc = queue(c);
+        if (rc != RT_OK) { ctx->error = c->error; return rc; }
+    }
+    for (rt_ctx* c : ctx->children) {
+        cudaSetDevice(c->device);
+        const cudaError_t e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) { ctx->error = std::string("readback: ") + cudaGetErrorString(e); return RT_ERR_CUDA; }
+    }
+    return RT_OK;
+}
+
+extern "C" {
+
 int rt_readback(rt_ctx* ctx, float* dst, size_t bytes) {
     CTX_CHECK(ctx);
+    if (!ctx->children.empty())
+        return gather_children(ctx, [&](rt_ctx* c) {
+            const int rc = rt_require_target(c);
+            return rc != RT_OK ? rc : scatter_rows_async(c, c->image.p, dst, bytes, sizeof(float4));
+        });
     const int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     return scatter_rows_to_host(ctx, ctx->image.p, dst, bytes, sizeof(float4));
 }
 
-int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst, size_t bytes) {
-    CTX_CHECK(ctx);
+static int srgb8_async(rt_ctx* ctx, uint8_t* dst, size_t bytes) {
     int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     const size_t n = (size_t)ctx->local_rows * ctx->width;
     RT_CUDA_TRY(ctx->srgb.ensure(n));
     std::string err;
-    rc = launch_srgb8(ctx->image.p, ctx->srgb.p, (uint32_t)n, ctx->stream, err);
+    rc = launch_srgb8(ctx->image.p, ctx->srgb.p, (uint32_t)n, ctx->dims, ctx->stream, err);
     if (rc != RT_OK) { set_error(err); return rc; }
-    return scatter_rows_to_host(ctx, ctx->srgb.p, dst, bytes, sizeof(uchar4));
+    return scatter_rows_async(ctx, ctx->srgb.p, dst, bytes, sizeof(uchar4));
+}
+
+int rt_readback_srgb8(rt_ctx* ctx, uint8_t* dst, size_t bytes) {
+    CTX_CHECK(ctx);
+    if (!ctx->children.empty()) return gather_children(ctx, [&](rt_ctx* c) { return srgb8_async(c, dst, bytes); });
+    const int rc = srgb8_async(ctx, dst, bytes);
+    if (rc != RT_OK) return rc;
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
 }
 
 int rt_device_image(rt_ctx* ctx, void** device_ptr, uint32_t* local_rows) {
     CTX_CHECK(ctx);
+    if (!ctx->children.empty()) { set_error("rt_device_image: a multi-GPU context has one image per device; use rt_readback"); return RT_ERR_INVALID_ARGUMENT; }
     const int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     if (device_ptr) *device_ptr = ctx->image.p;
@@ -609,6 +855,7 @@ int rt_device_image(rt_ctx* ctx, void** device_ptr, uint32_t* local_rows) {
 
 int rt_upload_accum(rt_ctx* ctx, const float* src, size_t bytes) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_upload_accum(c, src, bytes));
     const int rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
     const size_t row = (size_t)ctx->width * sizeof(float4);
@@ -616,17 +863,42 @@ int rt_upload_accum(rt_ctx* ctx, const float* src, size_t bytes) {
     const uint32_t sr = ctx->cfg.strip_rows;
     for (uint32_t lrow = 0; lrow < ctx->local_rows; lrow += sr) {
         const uint32_t rows = std::min(sr, ctx->local_rows - lrow);
-        const uint32_t y = strip_global_row(lrow, sr, ctx->cfg.strip_index, ctx->cfg.strip_count);
+        const uint32_t y = band_to_strip(ctx, lrow / sr) * sr;
         RT_CUDA_TRY(cudaMemcpyAsync((char*)ctx->image.p + (size_t)lrow * row, (const char*)src + (size_t)y * row, rows * row,
                                     cudaMemcpyHostToDevice, ctx->stream));
     }
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->balance_pending = false;  // the rows now hold a running mean: they stay where they are
+    return RT_OK;
+}
+
+// The strip assignment in force: owners[s] = rank (strip_index, or device slot of a multi-GPU context) that renders strip s.
+int rt_get_strip_owners(rt_ctx* ctx, uint32_t* owners, uint32_t capacity, uint32_t* n_strips) {
+    CTX_CHECK(ctx);
+    rt_ctx* c0 = ctx->children.empty() ? ctx : ctx->children[0];
+    const int rc = rt_require_target(c0);
+    if (rc != RT_OK) { ctx->error = c0->error; return rc; }
+    const uint32_t sr = c0->cfg.strip_rows, n = (c0->height + sr - 1) / sr;
+    if (n_strips) *n_strips = n;
+    if (!owners) return RT_OK;
+    if (capacity < n) { set_error("rt_get_strip_owners: capacity too small"); return RT_ERR_INVALID_ARGUMENT; }
+    if (c0->strip_owner.empty()) for (uint32_t s2 = 0; s2 < n; s2++) owners[s2] = s2 % c0->cfg.strip_count;
+    else memcpy(owners, c0->strip_owner.data(), n * sizeof(uint32_t));
+    return RT_OK;
+}
+
+// Ask for a new cost calibration at the next accumulation restart (e.g. after the camera settled somewhere else).
+int rt_rebalance(rt_ctx* ctx) {
+    CTX_CHECK(ctx);
+    FANOUT(ctx, rt_rebalance(c));
+    ctx->balance_pending = ctx->cfg.strip_balance == RT_BALANCE_COST && ctx->cfg.strip_count > 1 && ctx->width != 0;
     return RT_OK;
 }
 
 // ---- G-buffer --------------------------------------------------------------------------------------
 int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_trace_gbuffer(c, camera_ubo));
     if (!camera_ubo) return RT_ERR_INVALID_ARGUMENT;
     int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
@@ -645,7 +917,9 @@ int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]) {
     g.emission = ctx->g_emission.p; g.position_metal = ctx->g_position.p;
     std::string err;
     rt_begin_timing(ctx);
-    rc = launch_gbuffer(rt_scene_view(ctx), fp, g, (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->stream, err);
+    if (!ctx->dims.num_sms) cudaDeviceGetAttribute(&ctx->dims.num_sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    rc = launch_gbuffer(rt_scene_view(ctx), fp, g, (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->dims.num_sms,
+                        ctx->stream, err);
     rt_end_timing(ctx);
     if (rc != RT_OK) { set_error(err); return rc; }
     ctx->has_gbuffer = true;
@@ -655,6 +929,7 @@ int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]) {
 int rt_readback_gbuffer(rt_ctx* ctx, uint8_t* albedo, uint16_t* normal_rough, float* position_metal, uint16_t* emission,
                         uint8_t* output) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_readback_gbuffer(c, albedo, normal_rough, position_metal, emission, output));
     if (!ctx->has_gbuffer) { set_error("rt_readback_gbuffer: no G-buffer traced"); return RT_ERR_NO_TARGET; }
     const size_t px = (size_t)ctx->width * ctx->height;
     int rc = RT_OK;
@@ -670,6 +945,18 @@ int rt_readback_gbuffer(rt_ctx* ctx, uint8_t* albedo, uint16_t* normal_rough, fl
 int rt_get_counters(rt_ctx* ctx, rt_counters* out) {
     CTX_CHECK(ctx);
     if (!out) return RT_ERR_INVALID_ARGUMENT;
+    if (!ctx->children.empty()) {  // sums over the devices; `frames` is the number of calls, the same on each
+        memset(out, 0, sizeof(*out));
+        for (rt_ctx* c : ctx->children) {
+            rt_counters k;
+            const int rc = rt_get_counters(c, &k);
+            if (rc != RT_OK) { ctx->error = c->error; return rc; }
+            out->extend_rays += k.extend_rays; out->shadow_rays += k.shadow_rays; out->nodes += k.nodes; out->tris += k.tris;
+            out->hits += k.hits; out->nee += k.nee; out->shadow_nodes += k.shadow_nodes; out->shadow_tris += k.shadow_tris;
+            out->launches += k.launches; out->frames = k.frames;
+        }
+        return RT_OK;
+    }
     DevCounters c;
     RT_CUDA_TRY(cudaMemcpyAsync(&c, ctx->counters.p, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
@@ -681,6 +968,7 @@ int rt_get_counters(rt_ctx* ctx, rt_counters* out) {
 
 int rt_reset_counters(rt_ctx* ctx) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_reset_counters(c));
     RT_CUDA_TRY(cudaMemsetAsync(ctx->counters.p, 0, sizeof(DevCounters), ctx->stream));
     ctx->frames_traced = 0;
     ctx->launches = 0;
@@ -690,6 +978,7 @@ int rt_reset_counters(rt_ctx* ctx) {
 int rt_event_record(rt_ctx* ctx, int which) {
     CTX_CHECK(ctx);
     if (which < 0 || which > 1) return RT_ERR_INVALID_ARGUMENT;
+    FANOUT(ctx, rt_event_record(c, which));
     if (!ctx->user_ev[which]) RT_CUDA_TRY(cudaEventCreate(&ctx->user_ev[which]));
     RT_CUDA_TRY(cudaEventRecord(ctx->user_ev[which], ctx->stream));
     return RT_OK;
@@ -697,6 +986,17 @@ int rt_event_record(rt_ctx* ctx, int which) {
 
 int rt_event_elapsed_ms(rt_ctx* ctx, float* ms) {
     CTX_CHECK(ctx);
+    if (ms && !ctx->children.empty()) {  // max over the devices, each timed on its own stream
+        float worst = 0.0f;
+        for (rt_ctx* c : ctx->children) {
+            float m = 0.0f;
+            const int rc = rt_event_elapsed_ms(c, &m);
+            if (rc != RT_OK) { ctx->error = c->error; return rc; }
+            worst = std::max(worst, m);
+        }
+        *ms = worst;
+        return RT_OK;
+    }
     if (!ms || !ctx->user_ev[0] || !ctx->user_ev[1]) { set_error("rt_event_elapsed_ms: record both events first"); return RT_ERR_INVALID_ARGUMENT; }
     RT_CUDA_TRY(cudaEventSynchronize(ctx->user_ev[1]));
     RT_CUDA_TRY(cudaEventElapsedTime(ms, ctx->user_ev[0], ctx->user_ev[1]));
@@ -705,6 +1005,7 @@ int rt_event_elapsed_ms(rt_ctx* ctx, float* ms) {
 
 int rt_set_profiling(rt_ctx* ctx, int enable) {
     CTX_CHECK(ctx);
+    FANOUT(ctx, rt_set_profiling(c, enable));
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->prof.enabled = enable != 0;
     ctx->prof.reset();
@@ -715,6 +1016,15 @@ int rt_get_kernel_profile(rt_ctx* ctx, rt_kernel_profile* out) {
     CTX_CHECK(ctx);
     if (!out) return RT_ERR_INVALID_ARGUMENT;
     memset(out, 0, sizeof(*out));
+    if (!ctx->children.empty()) {  // device time summed over the devices
+        for (rt_ctx* c : ctx->children) {
+            rt_kernel_profile k;
+            const int rc = rt_get_kernel_profile(c, &k);
+            if (rc != RT_OK) { ctx->error = c->error; return rc; }
+            for (int i = 0; i < RT_K_COUNT; i++) { out->ms[i] += k.ms[i]; out->launches[i] += k.launches[i]; }
+        }
+        return RT_OK;
+    }
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     for (size_t i = 0; i < ctx->prof.used; i++) {
         float ms = 0.0f;
@@ -731,6 +1041,7 @@ static int trace_rays_common(rt_ctx* ctx, const float* rays, uint32_t n, bool an
     int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     if (n == 0) return RT_OK;
+    if (!ctx->dims.num_sms) cudaDeviceGetAttribute(&ctx->dims.num_sms, cudaDevAttrMultiProcessorCount, ctx->device);
     if (!rays || !out_id || (!any && !out_tuv)) { set_error("rt_trace_rays: null argument"); return RT_ERR_INVALID_ARGUMENT; }
     DevBuf<float> d_rays, d_tuv;
     DevBuf<uint32_t> d_id, d_ig;
@@ -744,7 +1055,7 @@ static int trace_rays_common(rt_ctx* ctx, const float* rays, uint32_t n, bool an
     }
     std::string err;
     rc = launch_trace_rays(rt_scene_view(ctx), d_rays.p, n, any, (any && ignore) ? d_ig.p : nullptr, d_tuv.p, d_id.p,
-                           (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->stream, err);
+                           (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr, ctx->dims.num_sms, ctx->stream, err);
     if (rc != RT_OK) { set_error(err); return rc; }
     RT_CUDA_TRY(cudaMemcpyAsync(out_id, d_id.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (!any) RT_CUDA_TRY(cudaMemcpyAsync(out_tuv, d_tuv.p, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
@@ -752,19 +1063,31 @@ static int trace_rays_common(rt_ctx* ctx, const float* rays, uint32_t n, bool an
     return RT_OK;
 }
 
+// the verification hooks of a multi-GPU context run on its first device (every device holds the same BVH)
+#define FIRST_CHILD(ctx, call)                                  \
+    if (!(ctx)->children.empty()) {                             \
+        rt_ctx* c = (ctx)->children[0];                         \
+        const int _rc = (call);                                 \
+        if (_rc != RT_OK) (ctx)->error = c->error;              \
+        return _rc;                                             \
+    }
+
 int rt_trace_rays_closest(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id) {
     CTX_CHECK(ctx);
+    FIRST_CHILD(ctx, rt_trace_rays_closest(c, rays, n, out_tuv, out_id));
     return trace_rays_common(ctx, rays, n, false, nullptr, out_tuv, out_id);
 }
 
 int rt_trace_rays_any(rt_ctx* ctx, const float* rays, uint32_t n, const uint32_t* ignore_inst, uint32_t* out_occluded) {
     CTX_CHECK(ctx);
+    FIRST_CHILD(ctx, rt_trace_rays_any(c, rays, n, ignore_inst, out_occluded));
     return trace_rays_common(ctx, rays, n, true, ignore_inst, nullptr, out_occluded);
 }
 
 int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t tris_bytes, uint64_t* morton,
                uint32_t* sorted_ids) {
     CTX_CHECK(ctx);
+    FIRST_CHILD(ctx, rt_get_bvh(c, nodes, nodes_bytes, tris, tris_bytes, morton, sorted_ids));
     const int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
     const size_t nb = (size_t)ctx->bvh.n_nodes * sizeof(Node8), tb = (size_t)ctx->n_tris * 48;

@@ -22,15 +22,12 @@ namespace rt {
         }                                                                            \
     } while (0)
 
-static int g_num_sms = 0;
-static int num_sms() {
-    if (g_num_sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        if (g_num_sms <= 0) g_num_sms = 148;
-    }
-    return g_num_sms;
+// SM count of the CURRENT device (the context's: every entry point sets it); cached per context in LaunchDims
+static int query_num_sms() {
+    int dev = 0, n = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n > 0 ? n : 148;
 }
 
 // ---- counters: one atomic per warp -------------------------------------------------------------
@@ -81,9 +78,9 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(SceneView sc, const flo
 }
 
 int launch_trace_rays(const SceneView& sc, const float* d_rays, uint32_t n, bool any, const uint32_t* d_ignore,
-                      float* d_tuv, uint32_t* d_id, DevCounters* counters, cudaStream_t stream, std::string& err) {
+                      float* d_tuv, uint32_t* d_id, DevCounters* counters, int num_sms, cudaStream_t stream, std::string& err) {
     if (n == 0) return RT_OK;
-    const uint32_t grid = std::min<uint32_t>((n + 127) / 128, (uint32_t)num_sms() * 16);
+    const uint32_t grid = std::min<uint32_t>((n + 127) / 128, (uint32_t)num_sms * 16);
     if (any)
         trace_rays_kernel<true><<<grid, 128, 0, stream>>>(sc, reinterpret_cast<const float4*>(d_rays), n, d_ignore, d_tuv,
                                                           d_id, counters);
@@ -103,7 +100,7 @@ __global__ void __launch_bounds__(128) megakernel_frame(SceneView sc, FrameParam
     uint32_t c_ext = 0, c_sh = 0, c_nodes = 0, c_tris = 0, c_hits = 0, c_nee = 0, c_snodes = 0, c_stris = 0;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
         const uint32_t lrow = slot / fp.width, x = slot - lrow * fp.width;
-        const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+        const uint32_t y = strip_global_row(fp, lrow);
         PathState ps;
         vec3 o, d;
         raygen_init(fp, x, y, ps, &o, &d);
@@ -147,12 +144,67 @@ int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameRes
                             std::string& err) {
     const uint32_t n_slots = fp.local_rows * fp.width;
     if (n_slots == 0) return RT_OK;
-    const uint32_t grid = std::min<uint32_t>((n_slots + 127) / 128, (uint32_t)num_sms() * 64);
+    if (res.dims && !res.dims->num_sms) res.dims->num_sms = query_num_sms();
+    const uint32_t grid = std::min<uint32_t>((n_slots + 127) / 128, (uint32_t)(res.dims ? res.dims->num_sms : query_num_sms()) * 64);
     if (fp.flags & RT_FLAG_COUNTERS)
         megakernel_frame<true><<<grid, 128, 0, stream>>>(sc, fp, res.image, res.counters);
     else
         megakernel_frame<false><<<grid, 128, 0, stream>>>(sc, fp, res.image, res.counters);
     if (res.launches) (*res.launches)++;
+    FRAME_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+// Strip-cost calibration (RT_BALANCE_COST): the paths of the full frame once more, nothing stored but how many closest-hit
+// rays beyond the primary one each image row traced.  Incoherent rays cost ~8x a packet-traced primary ray (DESIGN.md
+// §5.2), so rows x width + 8 x this count is the cost the strips are balanced by (rt_api.cu: balance_strips).  Light
+// samples are drawn (the random stream must stay the path's) but not evaluated; visibility rays are not traced.
+__global__ void __launch_bounds__(128) row_cost_kernel(SceneView sc, FrameParams fp, uint32_t* row_cost) {
+    const uint32_t n_px = fp.height * fp.width;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n_px; base += gridDim.x * blockDim.x) {
+        const uint32_t px = base + threadIdx.x;
+        uint32_t extra = 0, y = 0;
+        if (px < n_px) {
+            y = px / fp.width;
+            const uint32_t x = px - y * fp.width;
+            PathState ps;
+            vec3 o, d;
+            raygen_init(fp, x, y, ps, &o, &d);
+            uint32_t nn = 0, nt = 0, nee = 0;
+            for (int depth = 0; depth < fp.max_depth; depth++) {
+                if (!russian_roulette(ps, depth, fp.rr_start)) break;
+                if (depth > 0) extra++;
+                const Hit h = traverse<false, false>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, nn, nt);
+                if (h.id == 0xFFFFFFFFu) break;
+                ShadowRequest sr;
+                NeeRequest nq;
+                const ShadeResult res = shade_hit<true, true>(sc, ps, h, d, sr, nee, &nq);
+                if (!res.alive || throughput_dead(ps.throughput)) break;
+                o = res.next_origin;
+                d = res.next_dir;
+            }
+        }
+        // a warp's pixels lie in at most two rows (width >= 32) — one atomic per row and warp
+        const uint32_t y0 = __shfl_sync(0xFFFFFFFFu, y, 0);
+        uint32_t a = (px < n_px && y == y0) ? extra : 0u, b = (px < n_px && y != y0) ? extra : 0u;
+#pragma unroll
+        for (int o2 = 16; o2 > 0; o2 >>= 1) { a += __shfl_xor_sync(0xFFFFFFFFu, a, o2); b += __shfl_xor_sync(0xFFFFFFFFu, b, o2); }
+        if (fp.width >= 32u) {
+            if ((threadIdx.x & 31u) == 0u) {
+                if (a) atomicAdd(&row_cost[y0], a);
+                if (b && y0 + 1u < fp.height) atomicAdd(&row_cost[y0 + 1u], b);
+            }
+        } else if (px < n_px && extra) {
+            atomicAdd(&row_cost[y], extra);
+        }
+    }
+}
+
+int launch_row_cost(const SceneView& sc, const FrameParams& fp, uint32_t* d_row_cost, int num_sms, cudaStream_t stream, std::string& err) {
+    const uint32_t n_px = fp.height * fp.width;
+    if (n_px == 0) return RT_OK;
+    const uint32_t grid = std::min<uint32_t>((n_px + 127) / 128, (uint32_t)num_sms * 64);
+    row_cost_kernel<<<grid, 128, 0, stream>>>(sc, fp, d_row_cost);
     FRAME_TRY(cudaGetLastError());
     return RT_OK;
 }
@@ -232,7 +284,7 @@ __global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_cou
 // A launch covers fp.n_lanes consecutive frames ("lanes"): slot = lane * pixels + pixel, frame = fp.frame + lane * fp.frame_stride.
 __device__ __forceinline__ void raygen_slot(const FrameParams& fp, const WfView& wf, uint32_t x, uint32_t lrow, uint32_t lane_f) {
     const uint32_t slot = (lane_f * fp.local_rows + lrow) * fp.width + x;
-    const uint32_t y = fp.strip_count == 1u ? lrow : strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+    const uint32_t y = strip_global_row(fp, lrow);
     uint32_t seed;
     vec3 o, d;
     raygen_ray(fp, fp.frame + lane_f * fp.frame_stride, x, y, &seed, &o, &d);
@@ -515,7 +567,7 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                 {
                     const uint32_t lane_f = slot[k] / n_px, px = slot[k] - lane_f * n_px;
                     const uint32_t lrow = px / width, x = px - lrow * width;
-                    const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+                    const uint32_t y = strip_global_row(fp, lrow);
                     uint32_t seed;
                     vec3 o, d;
                     raygen_ray(fp, fp.frame + lane_f * fp.frame_stride, x, y, &seed, &o, &d);
@@ -1012,10 +1064,10 @@ __global__ void __launch_bounds__(256) wf_accumulate_kernel(FrameParams fp, WfVi
 }
 
 template <typename K>
-static int persistent_grid(K kernel, int threads) {
+static int persistent_grid(K kernel, int threads, int num_sms) {
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm <= 0) per_sm = 4;
-    return per_sm * num_sms();
+    return per_sm * num_sms;
 }
 
 template <bool COUNT>
@@ -1033,16 +1085,23 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
 #ifndef RT_EXTEND_COOP
 #define RT_EXTEND_COOP 1
 #endif
-    static int g_ext = 0, g_shw = 0, g_shd = 0, g_shd0 = 0, g_pkt = 0, g_coop = 0, g_nee = 0;
-    if (!g_ext) {
-        g_coop = persistent_grid(wf_extend_coop_kernel<COUNT>, 128);
-        g_pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128);
-        g_ext = persistent_grid(wf_extend_kernel<COUNT>, 128);
-        g_shw = persistent_grid(wf_shadow_kernel<COUNT>, 128);
-        g_shd = persistent_grid(wf_shade_kernel<COUNT, false, true>, 128);
-        g_shd0 = persistent_grid(wf_shade_kernel<COUNT, false, false>, 128);
-        g_nee = persistent_grid(wf_nee_kernel<COUNT>, 128);
+    // persistent grids: per context (res.dims), i.e. per device — nothing process-wide
+    LaunchDims local_dims;
+    LaunchDims& dims = res.dims ? *res.dims : local_dims;
+    if (!dims.num_sms) dims.num_sms = query_num_sms();
+    LaunchDims::Set& ds = dims.set[COUNT ? 1 : 0];
+    if (!ds.ready) {
+        const int sms = dims.num_sms;
+        ds.coop = persistent_grid(wf_extend_coop_kernel<COUNT>, 128, sms);
+        ds.pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128, sms);
+        ds.ext = persistent_grid(wf_extend_kernel<COUNT>, 128, sms);
+        ds.shw = persistent_grid(wf_shadow_kernel<COUNT>, 128, sms);
+        ds.shd = persistent_grid(wf_shade_kernel<COUNT, false, true>, 128, sms);
+        ds.shd0 = persistent_grid(wf_shade_kernel<COUNT, false, false>, 128, sms);
+        ds.nee = persistent_grid(wf_nee_kernel<COUNT>, 128, sms);
+        ds.ready = true;
     }
+    const int g_ext = ds.ext, g_shw = ds.shw, g_shd = ds.shd, g_shd0 = ds.shd0, g_pkt = ds.pkt, g_coop = ds.coop, g_nee = ds.nee;
     const uint32_t gb_px = (n_px + 255) / 256;
     KernelProfiler none;
     KernelProfiler& pf = res.prof ? *res.prof : none;
@@ -1138,7 +1197,7 @@ __global__ void __launch_bounds__(128) gbuffer_kernel(SceneView sc, FrameParams 
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_slots; slot += gridDim.x * blockDim.x) {
         const uint32_t lrow = slot / fp.width, x = slot - lrow * fp.width;
-        const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+        const uint32_t y = strip_global_row(fp, lrow);
         vec3 o, d;
         camera_ray(fp, (float)x, (float)y, false, &o, &d);  // pixel corner, direction not re-normalised
         c_rays++;
@@ -1181,11 +1240,11 @@ __global__ void __launch_bounds__(128) gbuffer_kernel(SceneView sc, FrameParams 
     }
 }
 
-int launch_gbuffer(const SceneView& sc, const FrameParams& fp, const GBufferImages& g, DevCounters* counters,
+int launch_gbuffer(const SceneView& sc, const FrameParams& fp, const GBufferImages& g, DevCounters* counters, int num_sms,
                    cudaStream_t stream, std::string& err) {
     const uint32_t n_slots = fp.local_rows * fp.width;
     if (n_slots == 0) return RT_OK;
-    const uint32_t grid = std::min<uint32_t>((n_slots + 127) / 128, (uint32_t)num_sms() * 32);
+    const uint32_t grid = std::min<uint32_t>((n_slots + 127) / 128, (uint32_t)num_sms * 32);
     gbuffer_kernel<<<grid, 128, 0, stream>>>(sc, fp, g, counters);
     FRAME_TRY(cudaGetLastError());
     return RT_OK;
@@ -1215,9 +1274,8 @@ __global__ void srgb8_kernel(const float4* image, uchar4* out, uint32_t n) {
     out[i] = make_uchar4(srgb8(c.x), srgb8(c.y), srgb8(c.z), 255);
 }
 
-int launch_srgb8(const float4* image, uchar4* out, uint32_t n, cudaStream_t stream, std::string& err) {
-    static bool table_ready = false;
-    if (!table_ready) {
+int launch_srgb8(const float4* image, uchar4* out, uint32_t n, LaunchDims& dims, cudaStream_t stream, std::string& err) {
+    if (!dims.srgb_table_ready) {  // __constant__ memory is per device: once per context
         float t[256];
         t[0] = 0.0f;
         for (int k = 1; k < 256; k++) {
@@ -1225,8 +1283,9 @@ int launch_srgb8(const float4* image, uchar4* out, uint32_t n, cudaStream_t stre
             const double lin = (s <= 0.04045) ? s / 12.92 : pow((s + 0.055) / 1.055, 2.4);
             t[k] = (float)lin;
         }
-        FRAME_TRY(cudaMemcpyToSymbol(c_srgb_thresholds, t, sizeof(t)));
-        table_ready = true;
+        FRAME_TRY(cudaMemcpyToSymbolAsync(c_srgb_thresholds, t, sizeof(t), 0, cudaMemcpyHostToDevice, stream));
+        FRAME_TRY(cudaStreamSynchronize(stream));  // `t` is on this stack frame
+        dims.srgb_table_ready = true;
     }
     if (n == 0) return RT_OK;
     srgb8_kernel<<<(n + 255) / 256, 256, 0, stream>>>(image, out, n);

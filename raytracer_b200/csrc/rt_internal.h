@@ -41,9 +41,19 @@ struct DevBuf {
     DevBuf& operator=(const DevBuf&) = delete;
 };
 
-// Scratch that lives for one call: stream-ordered allocation from the device's default memory pool
-// (cudaMallocAsync).  rt_create raises the pool's release threshold, so after the first build the
-// ~25 temporaries of a rebuild cost microseconds instead of a cudaMalloc + a device-synchronising cudaFree each.
+// Scratch that lives for one call: stream-ordered allocation from the CONTEXT's own memory pool (created in rt_create with
+// an unlimited release threshold, destroyed in rt_destroy; the device's default pool, which the embedding host may be
+// using, is left alone).  After the first build the ~25 temporaries of a rebuild cost microseconds instead of a
+// cudaMalloc + a device-synchronising cudaFree each.  The pool in force is set per calling thread by PoolScope.
+inline cudaMemPool_t& current_pool() {
+    static thread_local cudaMemPool_t pool = nullptr;
+    return pool;
+}
+struct PoolScope {
+    cudaMemPool_t saved;
+    explicit PoolScope(cudaMemPool_t p) : saved(current_pool()) { current_pool() = p; }
+    ~PoolScope() { current_pool() = saved; }
+};
 template <typename T>
 struct PoolBuf {
     T* p = nullptr;
@@ -53,7 +63,9 @@ struct PoolBuf {
         release();
         s = stream;
         if (count == 0) count = 1;
-        cudaError_t e = cudaMallocAsync((void**)&p, count * sizeof(T), stream);
+        cudaMemPool_t pool = current_pool();
+        cudaError_t e = pool ? cudaMallocFromPoolAsync((void**)&p, count * sizeof(T), pool, stream)
+                             : cudaMallocAsync((void**)&p, count * sizeof(T), stream);
         if (e == cudaSuccess) n = count; else p = nullptr;
         return e;
     }
@@ -115,7 +127,16 @@ struct KernelProfiler {
     ~KernelProfiler() { for (auto& sp : spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); } }
 };
 
+// Persistent-grid sizes of the frame kernels, per context (= per device) and per COUNT variant of the templates: filled by
+// the first frame a context launches (occupancy query on ITS device), never shared between contexts.
+struct LaunchDims {
+    int num_sms = 0;
+    struct Set { bool ready = false; int ext = 0, shw = 0, shd = 0, shd0 = 0, pkt = 0, coop = 0, nee = 0; } set[2];
+    bool srgb_table_ready = false;  // c_srgb_thresholds uploaded to this context's device
+};
+
 struct FrameResources {
+    LaunchDims* dims = nullptr;
     float4* image = nullptr;      // local_rows x width RGBA32F running mean
     DevCounters* counters = nullptr;
     WavefrontBuffers* wf = nullptr;
@@ -130,14 +151,17 @@ int launch_frame_wavefront(const SceneView& sc, const FrameParams& fp, FrameReso
                            std::string& err);
 int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
                             std::string& err);
+// strip-cost calibration (RT_BALANCE_COST): one path per pixel of the FULL frame `fp` describes (strip_count must be 1 in
+// it), no image; row_cost[y] += closest-hit rays beyond the primary one that the paths of row y traced
+int launch_row_cost(const SceneView& sc, const FrameParams& fp, uint32_t* d_row_cost, int num_sms, cudaStream_t stream, std::string& err);
 int launch_trace_rays(const SceneView& sc, const float* d_rays, uint32_t n, bool any, const uint32_t* d_ignore,
-                      float* d_tuv, uint32_t* d_id, DevCounters* counters, cudaStream_t stream, std::string& err);
+                      float* d_tuv, uint32_t* d_id, DevCounters* counters, int num_sms, cudaStream_t stream, std::string& err);
 struct GBufferImages {
     uchar4* albedo; ushort4* normal_rough; float4* position_metal; ushort4* emission; uchar4* output;
 };
-int launch_gbuffer(const SceneView& sc, const FrameParams& fp, const GBufferImages& g, DevCounters* counters,
+int launch_gbuffer(const SceneView& sc, const FrameParams& fp, const GBufferImages& g, DevCounters* counters, int num_sms,
                    cudaStream_t stream, std::string& err);
-int launch_srgb8(const float4* image, uchar4* out, uint32_t n, cudaStream_t stream, std::string& err);
+int launch_srgb8(const float4* image, uchar4* out, uint32_t n, LaunchDims& dims, cudaStream_t stream, std::string& err);
 
 }  // namespace rt
 
@@ -156,6 +180,16 @@ struct rt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     std::string error;
+    // multi-GPU fan-out (rt_config.n_devices >= 2): this context then owns no device state of its own; child k renders
+    // strip_index k of strip_count n on device_ids[k], and every entry point loops over the children
+    std::vector<rt_ctx*> children;
+    rt::LaunchDims dims;
+    cudaMemPool_t pool = nullptr;  // private stream-ordered pool for build scratch (PoolBuf)
+    // strip -> rank assignment (RT_BALANCE_COST): global strip of every local band, host + device copies; empty = round robin
+    std::vector<uint32_t> band_strip;
+    std::vector<uint32_t> strip_owner;  // global strip -> rank, for every rank (the calibration is the same everywhere)
+    rt::DevBuf<uint32_t> d_band_strip;
+    bool balance_pending = false;  // calibrate at the next frame_number == 0 trace
 
     // host copies (the reference keeps the Scene on the host too and re-derives tables on edits)
     std::vector<HostMesh> meshes;

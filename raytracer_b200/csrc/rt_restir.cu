@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(128) restir_surface_kernel(SceneView sc, Frame
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     for (uint32_t px = blockIdx.x * blockDim.x + threadIdx.x; px < n_px; px += gridDim.x * blockDim.x) {
         const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
-        const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+        const uint32_t y = strip_global_row(fp, lrow);
         vec3 o, d;
         camera_ray(fp, (float)x, (float)y, false, &o, &d);  // pixel corner, direction not re-normalised
         c_rays++;
@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, Fr
         rt_reservoir res = empty_reservoir();
         if (ss.s.inst == 0xFFFFFFFFu) { out[px] = res; continue; }
         const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
-        const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+        const uint32_t y = strip_global_row(fp, lrow);
         uint32_t seed = tea16((y * fp.width + x) ^ 0x52455354u, fp.frame);  // 'REST': a stream of its own
         const uint32_t L = sc.n_lights < RT_MAXLIGHTS ? sc.n_lights : RT_MAXLIGHTS;
         float total = 0.0f;
@@ -217,6 +217,7 @@ __global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, Fr
                 const float ut = rnd01(seed), q1 = rnd01(seed), q2 = rnd01(seed), uu = rnd01(seed);
                 if (sel == 0xFFFFFFFFu) continue;
                 const uint32_t ntri = __ldg(&sc.lights[sel].num_triangles);
+                if (ntri == 0u) continue;  // a light whose mesh is empty has no point to sample
                 uint32_t tri = (uint32_t)(ut * (float)ntri);
                 if (tri > ntri - 1u) tri = ntri - 1u;
                 const float sq = sqrtf(q1);
@@ -299,7 +300,7 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
             res = empty_reservoir();
         } else {
             const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
-            const uint32_t y = strip_global_row(lrow, fp.strip_rows, fp.strip_index, fp.strip_count);
+            const uint32_t y = strip_global_row(fp, lrow);
             uint32_t seed = tea16((y * fp.width + x) ^ 0x53504154u, fp.frame);  // 'SPAT'
             LightPoint lpw;  // the surviving sample's light point, once it has been reconstructed
             bool have_lpw = false;
@@ -409,6 +410,11 @@ void rt_default_restir_params(rt_restir_params* p) {
 int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t frame_number,
                     const rt_restir_params* params) {
     if (!ctx) return RT_ERR_INVALID_ARGUMENT;
+    for (rt_ctx* c : ctx->children) {  // multi-GPU context: every device shades its own strips
+        const int rc = rt_restir_frame(c, camera_ubo, clear_color, frame_number, params);
+        if (rc != RT_OK) { ctx->error = c->error; return rc; }
+    }
+    if (!ctx->children.empty()) return RT_OK;
     cudaSetDevice(ctx->device);
     if (!camera_ubo || !clear_color) { set_error("rt_restir_frame: null argument"); return RT_ERR_INVALID_ARGUMENT; }
     rt_restir_params prm;
@@ -459,6 +465,11 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
 // the reservoirs the last rt_restir_frame shaded with (after spatial reuse; full-size W*H array; rows of other strips are left untouched)
 int rt_readback_reservoirs(rt_ctx* ctx, rt_reservoir* dst, size_t bytes) {
     if (!ctx) return RT_ERR_INVALID_ARGUMENT;
+    for (rt_ctx* c : ctx->children) {
+        const int rc = rt_readback_reservoirs(c, dst, bytes);
+        if (rc != RT_OK) { ctx->error = c->error; return rc; }
+    }
+    if (!ctx->children.empty()) return RT_OK;
     cudaSetDevice(ctx->device);
     if (!ctx->rs_history) { set_error("rt_readback_reservoirs: no ReSTIR frame traced"); return RT_ERR_NO_TARGET; }
     const size_t row = (size_t)ctx->width * sizeof(rt_reservoir);

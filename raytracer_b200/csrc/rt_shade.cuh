@@ -280,6 +280,7 @@ __device__ __forceinline__ bool nee_evaluate(const SceneView& sc, vec3 x, vec3 N
     const uint32_t lobj = __ldg(&light->object_index);
     const DevObject* lo = sc.objects + lobj;
     const uint32_t ntri = __ldg(&light->num_triangles);
+    if (ntri == 0u) return false;  // DEFINED: a light whose mesh is empty gives an invalid sample (the shader would index triangle 0xFFFFFFFF)
     uint32_t tri = (uint32_t)(r_tri * (float)ntri);
     if (tri > ntri - 1u) tri = ntri - 1u;
     const uint32_t* ip = sc.indices + __ldg(&lo->index_base) + 3u * tri;

@@ -111,7 +111,8 @@ struct FrameParams {
     uint32_t frame_stride;                          // 1, or the world size when ranks take spp slices
     uint32_t sample;                                // running-mean index of lane 0 (simple.rgen:127-136); == frame unless sliced
     uint32_t width, height;
-    uint32_t strip_rows, strip_index, strip_count;  // rows owned: (y / strip_rows) % strip_count == strip_index
+    uint32_t strip_rows, strip_index, strip_count;  // rows owned: (y / strip_rows) % strip_count == strip_index ...
+    const uint32_t* band_strip;                     // ... unless this table (device; local band -> global strip) says otherwise (RT_BALANCE_COST)
     uint32_t local_rows;                            // rows in this context's compact image
     int32_t max_depth;
     int32_t rr_start;
@@ -124,6 +125,14 @@ RT_HD uint32_t strip_global_row(uint32_t local_row, uint32_t strip_rows, uint32_
     uint32_t band = local_row / strip_rows, r = local_row % strip_rows;
     return (band * strip_count + strip_index) * strip_rows + r;
 }
+#if defined(__CUDACC__)
+__device__ __forceinline__ uint32_t strip_global_row(const FrameParams& fp, uint32_t local_row) {
+    if (fp.strip_count == 1u) return local_row;
+    const uint32_t band = local_row / fp.strip_rows, r = local_row - band * fp.strip_rows;
+    const uint32_t strip = fp.band_strip ? __ldg(fp.band_strip + band) : band * fp.strip_count + fp.strip_index;
+    return strip * fp.strip_rows + r;
+}
+#endif
 
 #if defined(__CUDACC__)
 // 256-bit read-only load (sm_100 LDG.256); p must be 32-byte aligned.  A load whose threads sit in different lines costs

@@ -23,6 +23,7 @@ RT_FLAG_DIRECT_LIGHTING, RT_FLAG_MIS, RT_FLAG_COUNTERS, RT_FLAG_PER_RAY_PRIMARY 
 RT_FLAG_DEFAULT = 7
 RT_PIPELINE_WAVEFRONT, RT_PIPELINE_MEGAKERNEL = 0, 1
 RT_RESTIR_TEMPORAL, RT_RESTIR_SPATIAL = 1, 2
+RT_BALANCE_ROUND_ROBIN, RT_BALANCE_COST = 0, 1
 NODE_BYTES, TRI_BYTES = 128, 48  # Node8 / BvhTri records of rt_get_bvh
 
 # every entry point include/rt_api.h declares (checked against the header and `nm -D` by the tests)
@@ -30,7 +31,7 @@ EXPORTS = (
     "rt_create", "rt_destroy", "rt_default_config", "rt_last_error", "rt_version", "rt_build_scene",
     "rt_scene_info_get", "rt_update_material", "rt_update_object_transform", "rt_update_object_material",
     "rt_update_object_mesh", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_trace_frames_sliced", "rt_synchronize", "rt_readback",
-    "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_trace_gbuffer", "rt_readback_gbuffer",
+    "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_get_strip_owners", "rt_rebalance", "rt_trace_gbuffer", "rt_readback_gbuffer",
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
     "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_set_profiling", "rt_get_kernel_profile",
     "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh",
@@ -41,7 +42,8 @@ class RtConfig(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_depth", C.c_int32), ("rr_start_depth", C.c_int32),
                 ("radiance_clamp", C.c_float), ("flags", C.c_uint32), ("pipeline", C.c_uint32),
                 ("strip_rows", C.c_uint32), ("strip_index", C.c_uint32), ("strip_count", C.c_uint32),
-                ("frames_in_flight", C.c_uint32), ("reserved", C.c_uint32 * 6)]
+                ("frames_in_flight", C.c_uint32), ("n_devices", C.c_uint32), ("device_ids", C.c_int32 * 8),
+                ("strip_balance", C.c_uint32), ("reserved", C.c_uint32 * 4)]
 
 
 class RtMesh(C.Structure):
@@ -127,6 +129,8 @@ def load() -> C.CDLL:
     L.rt_readback_srgb8.argtypes = [vp, vp, C.c_size_t]
     L.rt_device_image.argtypes = [vp, C.POINTER(vp), C.POINTER(u32)]
     L.rt_upload_accum.argtypes = [vp, vp, C.c_size_t]
+    L.rt_get_strip_owners.argtypes = [vp, vp, u32, C.POINTER(u32)]
+    L.rt_rebalance.argtypes = [vp]
     L.rt_trace_gbuffer.argtypes = [vp, f32p]
     L.rt_readback_gbuffer.argtypes = [vp, vp, vp, vp, vp, vp]
     L.rt_default_restir_params.argtypes = [C.POINTER(RtRestirParams)]
@@ -156,7 +160,8 @@ class Context:
 
     def __init__(self, device: int = -1, max_depth: int = 3, rr_start_depth: int = 3, radiance_clamp: float = 5.0,
                  counters: bool = True, pipeline: int = RT_PIPELINE_WAVEFRONT, strip_rows: int = 8, strip_index: int = 0,
-                 strip_count: int = 1, frames_in_flight: int = 0, per_ray_primary: bool = False):
+                 strip_count: int = 1, frames_in_flight: int = 0, per_ray_primary: bool = False, devices=None,
+                 strip_balance: int = RT_BALANCE_ROUND_ROBIN):
         self.L = load()
         cfg = RtConfig()
         self.L.rt_default_config(C.byref(cfg))
@@ -168,6 +173,11 @@ class Context:
         cfg.strip_rows, cfg.strip_index, cfg.strip_count = strip_rows, strip_index, strip_count
         if frames_in_flight:
             cfg.frames_in_flight = frames_in_flight
+        cfg.strip_balance = strip_balance
+        if devices is not None and len(devices) >= 2:  # multi-GPU fan-out inside the library: one context, all devices
+            cfg.n_devices = len(devices)
+            for k, d in enumerate(devices):
+                cfg.device_ids[k] = int(d)
         self.cfg = cfg
         h = C.c_void_p()
         rc = self.L.rt_create(C.byref(cfg), C.byref(h))
@@ -275,6 +285,17 @@ class Context:
         ptr, rows = C.c_void_p(), C.c_uint32()
         self._check(self.L.rt_device_image(self.h, C.byref(ptr), C.byref(rows)))
         return ptr.value, rows.value
+
+    def strip_owners(self) -> np.ndarray:
+        """owners[s] = rank (strip_index / device slot) that renders strip s under the assignment in force."""
+        n = C.c_uint32()
+        self._check(self.L.rt_get_strip_owners(self.h, None, 0, C.byref(n)))
+        out = np.zeros(n.value, np.uint32)
+        self._check(self.L.rt_get_strip_owners(self.h, _p(out), n.value, C.byref(n)))
+        return out
+
+    def rebalance(self):
+        self._check(self.L.rt_rebalance(self.h))
 
     def upload_accum(self, image):
         img = np.ascontiguousarray(image, np.float32)

@@ -26,8 +26,10 @@ DEFAULT_BACKGROUND = (0.53, 0.81, 0.92)  # raytracing_renderer.odin:77
 
 
 class RaytracingRenderer:
-    def __init__(self, width: int, height: int, **ctx_kwargs):
-        self.ctx = librt.Context(**ctx_kwargs)
+    def __init__(self, width: int, height: int, ctx=None, **ctx_kwargs):
+        # `ctx`: an already created librt.Context (or any object with its methods: the CPU tests of the frame logic
+        # pass a recorder); otherwise one is created here, which needs librt.so and a B200
+        self.ctx = ctx if ctx is not None else librt.Context(**ctx_kwargs)
         self.scene: Optional[Scene] = None
         self.camera: Optional[Camera] = None
         self.accumulation_frame = 1  # raytracing_renderer.odin:45 (the first render resets it: camera.dirty)
@@ -54,6 +56,24 @@ class RaytracingRenderer:
         self.width, self.height = int(width), int(height)
         self.ctx.resize(self.width, self.height)
         self.accumulation_frame = 0
+
+    def set_accumulation_limit(self, new_limit: int):
+        """The "Set Accumulation Limit" dialog (ui.odin:519-531): a positive limit at or below the current frame restarts
+        the accumulation; zero or negative removes the limit."""
+        if new_limit > 0:
+            if self.accumulation_frame >= new_limit:
+                self.accumulation_frame = 0
+            self.accumulation_limit = int(new_limit)
+        else:
+            self.accumulation_limit = None
+
+    def resume_from(self, image: np.ndarray, frames_done: int):
+        """Checkpoint/resume of a long accumulation: `image` is the RGBA32F running mean over frames
+        0 .. frames_done-1 (as `output_image` returned it); the next render_scene continues with frame `frames_done`."""
+        self.ctx.upload_accum(image)
+        self.accumulation_frame = int(frames_done)
+        if self.camera is not None:
+            self.camera.dirty = False
 
     # ---- frame --------------------------------------------------------------------------------
     def begin_frame(self):

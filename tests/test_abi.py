@@ -47,8 +47,21 @@ def test_library_is_sm100a_only(lib):
     assert archs == {"100a"}, archs
 
 
-def test_struct_sizes_match_the_header(lib):
-    assert C.sizeof(librt.RtConfig) == 64 and C.sizeof(librt.RtObject) == 72 and C.sizeof(librt.RtMesh) == 32
+def test_struct_sizes_match_the_header(lib, tmp_path):
+    """The ctypes mirrors against the header itself: a C program that includes include/rt_api.h prints the sizes (and the
+    offsets of the fields added for the multi-GPU fan-out) as gcc lays them out."""
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "rt_api.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
+                   "sizeof(rt_config),sizeof(rt_object),sizeof(rt_mesh),sizeof(rt_counters),sizeof(rt_scene_info),sizeof(rt_restir_params),"
+                   "sizeof(rt_material),sizeof(rt_vertex),sizeof(rt_reservoir),offsetof(rt_config,n_devices),offsetof(rt_config,strip_balance));return 0;}\n")
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    want = [C.sizeof(librt.RtConfig), C.sizeof(librt.RtObject), C.sizeof(librt.RtMesh), C.sizeof(librt.RtCounters),
+            C.sizeof(librt.RtSceneInfo), C.sizeof(librt.RtRestirParams), 44, 24, librt.RESERVOIR_DTYPE.itemsize,
+            librt.RtConfig.n_devices.offset, librt.RtConfig.strip_balance.offset]
+    assert got == want
+    assert C.sizeof(librt.RtConfig) == 96 and C.sizeof(librt.RtObject) == 72 and C.sizeof(librt.RtMesh) == 32
     assert C.sizeof(librt.RtCounters) == 80 and C.sizeof(librt.RtSceneInfo) == 32 and C.sizeof(librt.RtRestirParams) == 32
 
 

@@ -1,0 +1,182 @@
+"""GPU tests (-m gpu) of the rows SURVEY §8(f) ranks next to the hot path, through the C ABI and the host mirror:
+the camera / accumulation controller (raytracing_renderer.odin:108-126,194-205,346-350, ui.odin:519-531), checkpoint /
+resume of a long accumulation (rt_upload_accum) and the incremental scene updates (gpu_scene.odin:430-601).
+Every image is compared bit for bit with the CPU oracle replaying the same sequence of frame numbers.
+"""
+import numpy as np
+import pytest
+
+import raytracer_b200 as rb
+from conftest import CLEAR, fixture_scene
+from oracle.binding import OracleScene
+from raytracer_b200 import librt
+from raytracer_b200.renderer import RaytracingRenderer
+
+pytestmark = pytest.mark.gpu
+
+
+def _cam(aspect=1.0):
+    return rb.Camera(position=(0.0, 1.0, 4.5), aspect=aspect, target=(0.0, 1.0, 0.0))
+
+
+def _oracle_replay(orc, cam, W, H, frames):
+    img = None
+    for f in frames:
+        img = orc.render(cam.ubo(), CLEAR, f, W, H, image=img)
+    return img
+
+
+def _loop(r, n):
+    for _ in range(n):  # application.odin:109-115
+        r.begin_frame()
+        r.render_scene()
+        r.end_frame()
+
+
+def test_renderer_replay_dirty_camera_limit_and_resize():
+    scene = fixture_scene("cornell_pbr")
+    orc = OracleScene(scene).build_bvh()
+    W, H = 64, 48
+    cam = _cam(W / H)
+    r = RaytracingRenderer(W, H, device=0)
+    try:
+        r.set_scene(scene)
+        r.set_camera(cam)
+        assert r.accumulation_frame == 1  # raytracing_renderer.odin:45; the first render resets it (camera.dirty)
+        _loop(r, 3)
+        assert r.accumulation_frame == 3
+        assert np.array_equal(r.output_image().view(np.uint32), _oracle_replay(orc, cam, W, H, range(3)).view(np.uint32))
+        # camera move -> dirty -> the next frame is frame 0 again (raytracing_renderer.odin:196-199)
+        cam.move("Right", 0.05)
+        assert cam.dirty
+        _loop(r, 2)
+        assert r.accumulation_frame == 2 and not cam.dirty
+        assert np.array_equal(r.output_image().view(np.uint32), _oracle_replay(orc, cam, W, H, range(2)).view(np.uint32))
+        # accumulation limit: frames stop at the limit, the image stays, the counter does not advance (:204-205, :346-350)
+        r.set_accumulation_limit(4)
+        _loop(r, 5)
+        assert r.accumulation_frame == 4
+        at_limit = r.output_image().copy()
+        assert np.array_equal(at_limit.view(np.uint32), _oracle_replay(orc, cam, W, H, range(4)).view(np.uint32))
+        launches = r.ctx.counters()["launches"]
+        _loop(r, 3)
+        assert r.ctx.counters()["launches"] == launches and r.accumulation_frame == 4
+        assert np.array_equal(r.output_image().view(np.uint32), at_limit.view(np.uint32))
+        # a limit at or below the current frame restarts the accumulation (ui.odin:523-526); zero removes it
+        r.set_accumulation_limit(2)
+        assert r.accumulation_frame == 0
+        _loop(r, 3)
+        assert r.accumulation_frame == 2
+        assert np.array_equal(r.output_image().view(np.uint32), _oracle_replay(orc, cam, W, H, range(2)).view(np.uint32))
+        r.set_accumulation_limit(0)
+        assert r.accumulation_limit is None
+        # resize: new target, accumulation restarts, the camera's aspect follows (raytracing_renderer.odin:108-126)
+        W2, H2 = 80, 40
+        r.on_resize(W2, H2)
+        cam.on_resize(W2 / H2)
+        assert r.accumulation_frame == 0
+        _loop(r, 2)
+        got = r.output_image()
+        assert got.shape == (H2, W2, 4)
+        assert np.array_equal(got.view(np.uint32), _oracle_replay(orc, cam, W2, H2, range(2)).view(np.uint32))
+        # the window's resize flag takes the same route at the head of the next frame (:128-136)
+        r.width, r.height, r.framebuffer_resized = W, H, True
+        cam.on_resize(W / H)
+        _loop(r, 1)
+        assert r.output_image().shape == (H, W, 4) and r.accumulation_frame == 1
+        assert np.array_equal(r.output_image().view(np.uint32), _oracle_replay(orc, cam, W, H, range(1)).view(np.uint32))
+    finally:
+        r.destroy()
+
+
+def test_scene_edits_through_the_change_log_restart_the_accumulation():
+    """begin_frame drains Scene.changes into rt_update_* / a rebuild (raytracing_renderer.odin:141-187)."""
+    scene = fixture_scene("cornell_pbr")
+    W = H = 48
+    cam = _cam()
+    r = RaytracingRenderer(W, H, device=0)
+    try:
+        r.set_scene(scene)
+        r.set_camera(cam)
+        _loop(r, 2)
+        scene.update_object_position(3, (0.2, 0.0, 0.1))
+        m = scene.materials[2]
+        scene.update_material(2, rb.Material(m.name, (0.1, 0.8, 0.2), m.emission_color, m.emission_power, 0.4, 0.0))
+        scene.add_material(rb.Material("extra", albedo=(0.9, 0.9, 0.1), roughness=0.7))  # structural: rebuild path
+        scene.add_object("extra plane", scene.add_mesh(rb.create_plane()), len(scene.materials) - 1, (0.0, 0.6, 0.0), (90, 0, 0), (0.5, 0.5, 1))
+        _loop(r, 2)
+        assert r.accumulation_frame == 2 and not scene.changes
+        ref = _oracle_replay(OracleScene(scene).build_bvh(), cam, W, H, range(2))
+        assert np.array_equal(r.output_image().view(np.uint32), ref.view(np.uint32))
+    finally:
+        r.destroy()
+
+
+def test_upload_accum_resumes_a_long_accumulation():
+    """trace 8 frames == trace 4, read back, upload into a NEW context, trace frames 4..7 — bit for bit."""
+    scene = fixture_scene("cornell_pbr")
+    W, H = 96, 64
+    cam = _cam(W / H)
+    a = librt.Context(device=0)
+    b = librt.Context(device=0)
+    try:
+        for c in (a, b):
+            c.build_scene(scene)
+            c.resize(W, H)
+        a.trace_frames(cam.ubo(), CLEAR, 0, 8)
+        want = a.readback().copy()
+        a.trace_frames(cam.ubo(), CLEAR, 0, 4)
+        checkpoint = a.readback().copy()
+        b.upload_accum(checkpoint)
+        assert np.array_equal(b.readback().view(np.uint32), checkpoint.view(np.uint32))
+        b.trace_frames(cam.ubo(), CLEAR, 4, 4)
+        assert np.array_equal(b.readback().view(np.uint32), want.view(np.uint32))
+    finally:
+        a.close()
+        b.close()
+    # the same through the renderer mirror, on strips (each context keeps only its own rows of the checkpoint)
+    got = np.zeros_like(want)
+    for rank in range(2):
+        r = RaytracingRenderer(W, H, device=0, strip_rows=8, strip_index=rank, strip_count=2)
+        try:
+            r.set_scene(scene)
+            r.set_camera(cam)
+            r.resume_from(checkpoint, 4)
+            r.render_frames(4)
+            assert r.accumulation_frame == 8
+            r.ctx.readback(got)
+        finally:
+            r.destroy()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_update_object_mesh_matches_rebuild_and_oracle():
+    """gpu_scene_update_object_mesh (gpu_scene.odin:485-515): the object points at another mesh of the scene."""
+    scene = fixture_scene("cornell_pbr")
+    extra = scene.add_mesh(rb.create_sphere(12, 16))
+    scene.changes.clear()
+    W = H = 64
+    cam = _cam()
+    c = librt.Context(device=0)
+    try:
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+        before = c.readback().copy()
+        victim = max(range(len(scene.objects)), key=lambda i: scene.meshes[scene.objects[i].mesh_index].num_triangles)
+        scene.update_object_mesh(victim, extra)
+        c.update_object_mesh(victim, extra)
+        c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+        got = c.readback().copy()
+        info = c.scene_info()
+        assert info.n_triangles == scene.num_instanced_triangles()
+        ref = _oracle_replay(OracleScene(scene).build_bvh(), cam, W, H, range(2))
+        assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+        assert not np.array_equal(got, before)
+        c.build_scene(scene)  # the same scene from scratch
+        c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+        assert np.array_equal(c.readback().view(np.uint32), got.view(np.uint32))
+        with pytest.raises(librt.RtError):
+            c.update_object_mesh(victim, 10 ** 6)
+    finally:
+        c.close()

@@ -135,3 +135,79 @@ def test_png_round_trip_and_ssim_restatement(tmp_path):
                 acc.append(((2 * ux * uy + c1) * (2 * vxy + c2)) / ((ux * ux + uy * uy + c1) * (vx + vy + c2)))
     assert abs(ssim(a, b) - float(np.mean(acc))) < 1e-9
     assert 0.5 < ssim(a, b) < 1.0
+
+
+class _RecorderCtx:
+    """Stands in for librt.Context in the CPU test of the frame logic: records the frame numbers the controller asks for."""
+
+    def __init__(self):
+        self.calls = []
+
+    def resize(self, w, h):
+        self.calls.append(("resize", w, h))
+
+    def build_scene(self, scene):
+        self.calls.append(("build", len(scene.objects)))
+
+    def trace_frame(self, ubo, clear, frame):
+        self.calls.append(("trace", frame, 1))
+
+    def trace_frames(self, ubo, clear, first, n):
+        self.calls.append(("trace", first, n))
+
+    def upload_accum(self, image):
+        self.calls.append(("upload", image.shape))
+
+    def __getattr__(self, name):  # update_material, update_object_* ...
+        return lambda *a: self.calls.append((name,) + tuple(x for x in a if isinstance(x, int)))
+
+
+def test_accumulation_controller_mirrors_the_reference():
+    """raytracing_renderer.odin:128-205,346-350 and the limit dialog ui.odin:519-531, on a recorder (no GPU)."""
+    from raytracer_b200.renderer import RaytracingRenderer
+
+    rec = _RecorderCtx()
+    r = RaytracingRenderer(32, 16, ctx=rec)
+    scene = fixture_scene("cornell_box")
+    cam = rb.Camera(aspect=2.0)
+    r.set_scene(scene)
+    r.set_camera(cam)
+
+    def loop(n):
+        for _ in range(n):
+            r.begin_frame()
+            r.render_scene()
+            r.end_frame()
+
+    def frames():
+        out = [c[1] for c in rec.calls if c[0] == "trace"]
+        rec.calls.clear()
+        return out
+
+    loop(3)
+    assert frames() == [0, 1, 2]            # the camera starts dirty: frame 0 first
+    cam.move("Forward", 0.1)
+    loop(2)
+    assert frames() == [0, 1]
+    r.set_accumulation_limit(3)
+    loop(4)
+    assert frames() == [2] and r.accumulation_frame == 3   # stops AT the limit, counter frozen
+    r.set_accumulation_limit(2)                               # limit <= current frame: restart
+    loop(3)
+    assert frames() == [0, 1]
+    r.set_accumulation_limit(-1)
+    assert r.accumulation_limit is None
+    loop(1)
+    assert frames() == [2]
+    scene.update_object_position(0, (0.1, 0, 0))              # a scene edit restarts too (:141-187)
+    loop(1)
+    assert ("update_object_transform", 0) in rec.calls and frames() == [0]
+    r.on_resize(40, 20)
+    loop(1)
+    assert rec.calls[0] == ("resize", 40, 20) and frames() == [0]
+    r.resume_from(np.zeros((20, 40, 4), np.float32), 100)     # checkpoint/resume: continue with frame 100
+    r.render_frames(5)
+    assert frames() == [100] and r.accumulation_frame == 105
+    r.set_accumulation_limit(107)
+    r.render_frames(10)                                        # clipped at the limit
+    assert [c for c in rec.calls if c[0] == "trace"] == [("trace", 105, 2)]
