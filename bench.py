@@ -51,6 +51,10 @@ def parse_args():
     ap.add_argument("--pipeline", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=0, help="rows of one frame the CPU sample renders (0 = auto)")
+    ap.add_argument("--balance", default="cost", choices=["cost", "round_robin"], help="strip -> GPU assignment when N > 1")
+    ap.add_argument("--inproc", action="store_true",
+                    help="N > 1 without torchrun: ONE process drives all N GPUs through one multi-GPU rt_ctx (rt_config.device_ids)")
+    ap.add_argument("--no-verify", action="store_true", help="skip the sharded-vs-single-GPU image hash check")
     return ap.parse_args()
 
 
@@ -111,10 +115,20 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
+def host_threads():
+    """All the cores this process may run on (the cgroup / affinity count, not the machine's)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_sample(scene, cam, W, H, max_depth, rows, frames=(1,)):
     """The CPU oracle on `rows` image rows (centred band) of the same workload. Returns (Mrays/s, s, rays, threads)."""
     from oracle.binding import OracleScene, lib
 
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: ask for every core explicitly, whatever the environment says
+    lib().orc_set_num_threads(host_threads())
     orc = OracleScene(scene).build_bvh()
     y0 = max(0, (H - rows) // 2)
     y1 = min(H, y0 + rows)
@@ -159,23 +173,19 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-class _DevArray:
-    """__cuda_array_interface__ view of a device pointer owned by librt (the strip image)."""
-
-    def __init__(self, ptr, shape):
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 3,
-                                         "strides": None}
-
-
 def run_ours(args):
+    import hashlib
+
     import torch
 
     import raytracer_b200 as rb  # noqa: F401
     from raytracer_b200 import librt
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    inproc = bool(args.inproc) and args.gpus > 1
+    world = 1 if inproc else int(os.environ.get("WORLD_SIZE", "1"))
+    rank = 0 if inproc else int(os.environ.get("RANK", "0"))
+    local_rank = 0 if inproc else int(os.environ.get("LOCAL_RANK", "0"))
+    n_gpus = args.gpus if inproc else world
     dist = None
     torch.cuda.set_device(local_rank)
     if world > 1:
@@ -206,12 +216,24 @@ def run_ours(args):
         dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
         return float(t.item())
 
+    def gather_scalars(x):
+        if dist is None:
+            return [x]
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        out = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [float(v.item()) for v in out]
+
     W, H, B, K, Wm = args.width, args.height, args.spp_per_step, args.steps, args.warmup
     scene, cam = make_scene(args.scene, W, H)
     pipe = librt.RT_PIPELINE_WAVEFRONT if args.pipeline == "wavefront" else librt.RT_PIPELINE_MEGAKERNEL
-    kw = dict(device=local_rank, max_depth=args.max_depth, rr_start_depth=3, pipeline=pipe, strip_rows=8, strip_index=rank,
-              strip_count=world, frames_in_flight=max(B, 1))
-    ctx = librt.Context(counters=False, **kw)
+    balance = librt.RT_BALANCE_COST if (args.balance == "cost" and n_gpus > 1) else librt.RT_BALANCE_ROUND_ROBIN
+    kw = dict(max_depth=args.max_depth, rr_start_depth=3, pipeline=pipe, strip_rows=8, frames_in_flight=max(B, 1))
+    if inproc:
+        kw.update(devices=list(range(n_gpus)))   # ONE context, the library fans out (rt_config.device_ids)
+    else:
+        kw.update(device=local_rank, strip_index=rank, strip_count=world)
+    ctx = librt.Context(counters=False, strip_balance=balance, **kw)
     info = ctx.build_scene(scene)
     ctx.resize(W, H)
     ubo = cam.ubo()
@@ -220,7 +242,8 @@ def run_ours(args):
     # ---- ray counts of the timed frames: identical untimed passes on counting contexts -------------------
     # (a) per-ray primary traversal, full depth: the ray counts of `value` and the per-ray work definition of
     #     SURVEY §8d; (b) the same at depth 1: (a) - (b) = nodes / triangles of the bounces >= 1, which is what
-    #     wf_extend_kernel traces; (c) depth 1 with packets: what the packet kernel really fetches.
+    #     wf_extend_coop_kernel traces; (c) depth 1 with packets: what the packet kernel really fetches.
+    # Counting contexts keep the round-robin strips (any partition of the frame gives the same totals).
     def count(per_ray, depth):
         k2 = dict(kw, max_depth=depth)
         c = librt.Context(counters=True, per_ray_primary=per_ray, **k2)
@@ -236,11 +259,14 @@ def run_ours(args):
     cntp = count(False, 1)
     rays_local = cnt["extend_rays"] + cnt["shadow_rays"]
     rays_total = reduce_scalar(float(rays_local), "SUM")
+    primary_total = reduce_scalar(float(cnt1["extend_rays"]), "SUM")
+    secondary_total = reduce_scalar(float(cnt["extend_rays"] - cnt1["extend_rays"]), "SUM")
 
     # ---- device-resident throughput ---------------------------------------------------------------------
     for s in range(Wm):
-        ctx.trace_frames(ubo, CLEAR, s * B, B)
+        ctx.trace_frames(ubo, CLEAR, s * B, B)  # frame 0 comes first: RT_BALANCE_COST measures the strips here
     ctx.synchronize()
+    owners = [int(x) for x in ctx.strip_owners()] if n_gpus > 1 else None
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
@@ -256,13 +282,15 @@ def run_ours(args):
     barrier()
     sampler.stop_flag = True
     launches = ctx.counters()["launches"]
-    ms_max = reduce_scalar(ms, "MAX")
+    ms_ranks = gather_scalars(ms)
+    ms_max = max(ms_ranks)
     value = rays_total / (ms_max * 1e-3) / 1e6
 
     # ---- per-kernel times (CUDA events around every launch, separate pass over the same frames) -----------
     roof = None
     roof_pkt = None
     kprof = None
+    split = None
     if pipe == librt.RT_PIPELINE_WAVEFRONT:
         ctx.set_profiling(True)
         for s in range(K):
@@ -270,74 +298,96 @@ def run_ours(args):
         kprof = ctx.kernel_profile()
         ctx.set_profiling(False)
         ext, pkt = kprof["extend"], kprof["extend_packet"]
-        peaks = {}
+        peaks, gpeaks = {}, {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
+        try:  # tools/mb/gather.cu run on a B200 of this pool: what a divergent gather can do (committed, profiles/)
+            gpeaks = {(r["pattern"], r["table_bytes"]): r for r in json.load(open(os.path.join(ROOT, "profiles", "gather_peaks.json")))["rows"]}
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         total_k = sum(v["ms"] for v in kprof.values())
 
         def alg(c):  # BVH8 nodes 128 B + triangles 48 B fetched by closest-hit rays, ray in 32 B, hit out 16 B
             return (c["nodes"] - c["shadow_nodes"]) * 128 + (c["tris"] - c["shadow_tris"]) * 48 + c["extend_rays"] * 48
 
+        def loads(c):  # (thread, load instruction) pairs of the gather: a node is 4 x LDG.256, a triangle 3 x LDG.128
+            return (c["nodes"] - c["shadow_nodes"]) * 4 + (c["tris"] - c["shadow_tris"]) * 3
+
         sec_rays = cnt["extend_rays"] - cnt1["extend_rays"]
         alg_sec = alg(cnt) - alg(cnt1)
-        achieved = alg_sec / (ext["ms"] * 1e-3) / 1e9 if ext["ms"] > 0 else 0.0
-        traffic, l1_stage = None, None
-        try:  # dram__bytes_read+write per ray of the last committed `ncu --set full` capture of this kernel
-            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_kernel"]
+        loads_sec = loads(cnt) - loads(cnt1)
+        t_ext = ext["ms"] * 1e-3
+        hbm_ratio = alg_sec / t_ext / 1e9 if t_ext > 0 else 0.0
+        achieved = loads_sec / t_ext / 1e9 if t_ext > 0 else 0.0
+        # peak: one (thread, load) per clock per SM when every thread of a warp sits in another 128-byte line — measured
+        # by the microbenchmark with an L1-resident table; the L2-resident figure (the BVH is 18 MB) is reported beside it
+        g_l1 = gpeaks.get(("LDG.256", 65536))
+        g_l2 = gpeaks.get(("128 B = 4 x LDG.256", 16777216))
+        peak_l1 = g_l1["thread_loads_per_s"] / 1e9 if g_l1 else 290.8
+        traffic, l1_stage, tsrc = None, None, None
+        try:  # dram__bytes_read + write per launch and the L1 data-stage share of the last committed `ncu --set full`
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_coop_kernel"]
             traffic = tj["dram_bytes_per_ray"] * sec_rays / max(ext["launches"], 1)
-            l1_stage = tj.get("l1_data_stage")
+            l1_stage, tsrc = tj.get("l1_data_stage"), tj.get("source")
         except Exception:
             pass
-        roof = {"bound": "hbm", "kernel": "wf_extend_coop_kernel (one ray per lane, pooled triangle tests; bounces 1..%d)" % (args.max_depth - 1),
-                "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": "measured" if "hbm_gbs" in peaks else "fallback",
+        roof = {"bound": "l1_data_stage",
+                "kernel": "wf_extend_coop_kernel (one ray per lane, pooled triangle tests; bounces 1..%d)" % (args.max_depth - 1),
+                "achieved": achieved, "peak": peak_l1, "unit": "G thread-loads/s", "frac": achieved / peak_l1,
+                "peak_source": "profiles/gather_peaks.json (tools/mb/gather.cu on a B200 of this pool)" if g_l1 else "fallback 148 SMs x 1.965 GHz",
+                "peak_l2_resident": g_l2["thread_loads_per_s"] / 1e9 if g_l2 else None,
+                "definition": "thread-loads = 4 per BVH8 node (4 x LDG.256) + 3 per triangle (3 x LDG.128) fetched by the rays of bounces >= 1, "
+                              "counted on an identical untimed pass; a divergent load costs the SM's L1 data stage one cycle per thread whatever its width",
+                "traffic": traffic, "traffic_source": tsrc,
                 "launches": ext["launches"], "avg_launch_ms": ext["ms"] / max(ext["launches"], 1),
-                "alg_bytes_per_launch": alg_sec / max(ext["launches"], 1),
-                "bytes_per_ray": alg_sec / max(sec_rays, 1), "rays_per_launch": sec_rays / max(ext["launches"], 1),
+                "thread_loads_per_launch": loads_sec / max(ext["launches"], 1),
+                "rays_per_launch": sec_rays / max(ext["launches"], 1),
+                "nodes_per_ray": (cnt["nodes"] - cnt1["nodes"]) / max(sec_rays, 1), "tris_per_ray": (cnt["tris"] - cnt1["tris"]) / max(sec_rays, 1),
                 "share_of_step": ext["ms"] / total_k if total_k > 0 else None,
-                "note": "the BVH (< 20 MB) is L2/L1-resident, so algorithmic bytes / time is a bookkeeping ratio against the "
-                        "HBM copy peak, not a DRAM utilisation; `traffic` is the DRAM figure",
-                "l1_data_stage": l1_stage,  # what bounds the kernel in practice (ncu, committed capture): L1 wavefronts, not DRAM
+                "l1_data_stage": l1_stage,
+                # the §8(d) byte model, kept as a secondary key: algorithmic bytes / time against the HBM copy peak.  The BVH
+                # is cache-resident, so this is bookkeeping, not a DRAM utilisation, and not the roof that binds.
+                "hbm_bookkeeping": {"alg_bytes_per_launch": alg_sec / max(ext["launches"], 1), "bytes_per_ray": alg_sec / max(sec_rays, 1),
+                                    "achieved_gbs": hbm_ratio, "peak_gbs": hbm_peak, "ratio": hbm_ratio / hbm_peak,
+                                    "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"},
                 "kernel_ms": {k: round(v["ms"], 3) for k, v in kprof.items()}}
+        split = {"primary_mrays_s": cnt1["extend_rays"] / (pkt["ms"] * 1e-3) / 1e6 if pkt["ms"] > 0 else None,
+                 "incoherent_mrays_s": sec_rays / t_ext / 1e6 if t_ext > 0 else None,
+                 "primary_rays_per_step": primary_total / K, "incoherent_rays_per_step": secondary_total / K,
+                 "note": "kernel-only rates of rank 0: first-bounce packets (wf_extend_packet_kernel) and bounces >= 1 (wf_extend_coop_kernel); "
+                         "the reference's loader leaves Sponza all-metal, so ~2/3 of the paths end at their first hit"}
         if pkt["launches"]:
             a_ray, a_pkt = alg(cnt1), alg(cntp)
-            roof_pkt = {"kernel": "wf_extend_packet_kernel (first bounce, 128 rays per warp)", "launches": pkt["launches"],
+            roof_pkt = {"kernel": "wf_extend_packet_kernel (first bounce, 128 rays per warp)", "bound": "issue slots (ncu: 73 %)",
+                        "launches": pkt["launches"],
                         "avg_launch_ms": pkt["ms"] / pkt["launches"], "share_of_step": pkt["ms"] / total_k if total_k > 0 else None,
                         "per_ray_alg_bytes_per_launch": a_ray / pkt["launches"],
-                        "achieved_per_ray_definition": a_ray / (pkt["ms"] * 1e-3) / 1e9,
                         "fetched_bytes_per_launch": a_pkt / pkt["launches"],
-                        "achieved_fetched": a_pkt / (pkt["ms"] * 1e-3) / 1e9, "unit": "GB/s", "peak": peak,
+                        "achieved_fetched": a_pkt / (pkt["ms"] * 1e-3) / 1e9, "unit": "GB/s", "peak": hbm_peak,
                         "rays_per_launch": cnt1["extend_rays"] / pkt["launches"]}
-        else:
-            roof_pkt = None
 
     # ---- end to end through the C ABI with host buffers ------------------------------------------------
-    host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
-    gather = None
+    # N = 1 and --inproc: rt_readback into pinned host memory (a multi-GPU context gathers its devices' strips itself).
+    # N > 1 under torchrun: one host frame shared by the ranks (pinned /dev/shm mapping); every rank's rt_readback writes
+    # its own strips into it over its own PCIe link, then a barrier — no collective, no GPU-side gather.
+    shared = None
     if dist is not None:
         from raytracer_b200 import multi_gpu
 
-        ptr, rows = ctx.device_image()
-        view = torch.as_tensor(_DevArray(ptr, (rows, W, 4)), device="cuda") if rows else torch.empty((0, W, 4), device="cuda")
-        sg = multi_gpu.StripGather(dist, H, W, 4, 8, device="cuda")
-        host_t = torch.from_numpy(host)
-
-        def gather():
-            ctx.synchronize()
-            parts = sg.gather(view)
-            if rank == 0:
-                host_t.copy_(sg.assemble_device(parts), non_blocking=True)  # one D2H of the assembled frame
-                torch.cuda.synchronize()
+        shared = multi_gpu.SharedHostImage(dist, H, W, 4)
+        host = shared.array
+    else:
+        host_t = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+        host = host_t.numpy()
 
     def e2e_step(s):
         ctx.trace_frames(np.array(ubo, copy=True), CLEAR, f0 + s * B, B)  # camera UBO + clear colour from host memory
-        if gather is None:
-            ctx.readback(host)
-        else:
-            gather()
+        ctx.readback(host)
+        if dist is not None:
+            dist.barrier()
 
     for s in range(min(Wm, 3)):
         e2e_step(s)
@@ -351,9 +401,32 @@ def run_ours(args):
     e2e_value = rays_total / e2e_s / 1e6
     sampler.join(timeout=1.0)
 
+    # ---- verification: the sharded image is the one-GPU image, bit for bit ---------------------------------
+    verify = None
+    if not args.no_verify:
+        V = min(B, 16)
+        ctx.trace_frames(ubo, CLEAR, 0, V)
+        ctx.readback(host)
+        if dist is not None:
+            dist.barrier()
+        if rank == 0:
+            verify = {"frames": V, "sha256": hashlib.sha256(np.ascontiguousarray(host).tobytes()).hexdigest()}
+            if n_gpus > 1:
+                one = librt.Context(counters=False, device=local_rank, max_depth=args.max_depth, rr_start_depth=3, pipeline=pipe,
+                                    frames_in_flight=V)
+                one.build_scene(scene)
+                one.resize(W, H)
+                one.trace_frames(ubo, CLEAR, 0, V)
+                ref = one.readback()
+                one.close()
+                verify["sha256_single_gpu"] = hashlib.sha256(ref.tobytes()).hexdigest()
+                verify["equal"] = verify["sha256"] == verify["sha256_single_gpu"]
+        if dist is not None:
+            dist.barrier()
+
     # ---- CPU baseline (rank 0, N = 1 only) --------------------------------------------------------------
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
         # bounded sample: whole frames 1..n of the same workload, n sized for ~15 s of CPU work
         _, dt, _, _, _ = cpu_sample(scene, cam, W, H, args.max_depth, args.cpu_rows or H)
         n = int(max(1, min(64, round(15.0 / max(dt, 1e-3)))))
@@ -363,22 +436,33 @@ def run_ours(args):
                          f"(oracle/ CPU restatement, OpenMP; the reference has no CPU path)"}
 
     if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
                 "ms_per_step": ms_max / K, "ms_per_frame": ms_max / (K * B), "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"{args.scene} {W}x{H} depth {args.max_depth} rr 3, {B} spp per step",
                            "scene": {"triangles": info.n_triangles, "objects": info.n_objects, "lights": info.n_lights,
                                      "bvh8_nodes": info.n_nodes, "bvh_depth": info.bvh_depth, "build_ms": round(info.build_ms, 3)},
-                           "pipeline": args.pipeline, "partition": f"8-row screen strips over {world} GPU(s), scene replicated",
+                           "pipeline": args.pipeline,
+                           "partition": f"8-row screen strips over {n_gpus} GPU(s), scene replicated, strips assigned by "
+                                        f"{'measured cost (RT_BALANCE_COST)' if balance else 'round robin'}; "
+                                        + ("one process, one multi-GPU rt_ctx" if inproc else "one process per GPU"),
                            "l2": "per-step working set (path state + queues + image, > 300 MB at 1080p) exceeds the 126 MB L2; "
                                  "the BVH (< 20 MB) stays L2-resident frame to frame, as in the reference's use",
                            "rays_per_step": rays_total / K,
-                           "e2e_includes": "camera UBO from host + trace + RGBA32F image to pinned host memory every step "
-                                           "(NCCL gather of strips to rank 0 first when N > 1); scene build is outside, "
-                                           "as gpu_scene_init is in the reference"},
+                           "e2e_includes": "camera UBO from host + trace + RGBA32F image into pinned host memory every step "
+                                           "(N > 1: every GPU writes its strips into the one shared host frame, then a barrier); "
+                                           "scene build is outside, as gpu_scene_init is in the reference"},
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 64 * 4 + 12,
                         "d2h_bytes_per_step": W * H * 16, "ms_per_step": 1e3 * e2e_s / K},
                 "gpu_launches": int(launches), "clocks": sampler.summary()}
+        if n_gpus > 1:
+            line["ranks"] = {"ms_per_step": [round(m / K, 4) for m in ms_ranks], "slowest_over_mean": ms_max / (sum(ms_ranks) / len(ms_ranks)),
+                             "strips_per_rank": [owners.count(r) for r in range(n_gpus)] if owners else None}
+        if split:
+            line.update({k: split[k] for k in ("primary_mrays_s", "incoherent_mrays_s")})
+            line["ray_split"] = split
+        if verify:
+            line["verify"] = verify
         if roof:
             line["roofline"] = roof
             if roof_pkt:
@@ -387,6 +471,8 @@ def run_ours(args):
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
     ctx.close()
+    if shared is not None:
+        shared.close()
     if dist is not None:
         dist.destroy_process_group()
 

@@ -113,3 +113,60 @@ class SppSliceReduce:
             return None
         self.buf[..., 3] = 1.0
         return self.buf
+
+
+class SharedHostImage:
+    """One full-size host image shared by the ranks of a box: the consume step of N one-GPU processes.
+
+    The accumulation image only ever has to reach HOST memory (the reference blits it; `rt_readback` hands it to the
+    caller), so the ranks do not gather on a GPU first: rank 0 creates a /dev/shm file, every rank maps it and pins the
+    mapping (`cudaHostRegister`), and `rt_readback(ctx, image)` on each rank writes that rank's strips straight into it
+    — N PCIe links side by side, no collective, no staging.  One `barrier()` later rank 0 holds the whole frame.
+    `dist` is only used for the file name and the barrier (NCCL on the GPU box, gloo in the CPU tests, where
+    `register=False` leaves the mapping unpinned and the ranks write with numpy)."""
+
+    def __init__(self, dist, height: int, width: int, channels: int = 4, dtype=np.float32, register: bool = True):
+        import mmap
+        import os
+        import tempfile
+
+        self.dist = dist
+        self.rank = dist.get_rank() if dist is not None else 0
+        nbytes = int(height) * int(width) * int(channels) * np.dtype(dtype).itemsize
+        name = [None]
+        if self.rank == 0:
+            fd, path = tempfile.mkstemp(prefix="rt_frame_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+            os.ftruncate(fd, nbytes)
+            os.close(fd)
+            name[0] = path
+        if dist is not None and dist.get_world_size() > 1:
+            dist.broadcast_object_list(name, src=0)
+        self.path = name[0]
+        self._f = open(self.path, "r+b")
+        self._mm = mmap.mmap(self._f.fileno(), nbytes)
+        self.array = np.frombuffer(self._mm, dtype=dtype).reshape(height, width, channels)
+        self._registered = False
+        if register:
+            import torch
+
+            rc = torch.cuda.cudart().cudaHostRegister(self.array.ctypes.data, nbytes, 3)  # portable | mapped
+            if int(rc) != 0:
+                raise RuntimeError(f"cudaHostRegister of the shared frame failed: {rc}")
+            self._registered = True
+        if dist is not None and dist.get_world_size() > 1:
+            dist.barrier()
+        if self.rank == 0:
+            os.unlink(self.path)  # every rank holds its mapping; the name can go
+
+    def close(self):
+        if self._registered:
+            import torch
+
+            torch.cuda.cudart().cudaHostUnregister(self.array.ctypes.data)
+            self._registered = False
+        self.array = None
+        try:
+            self._mm.close()
+        except BufferError:
+            pass  # a numpy view is still alive somewhere; the mapping goes with it
+        self._f.close()

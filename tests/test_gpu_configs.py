@@ -239,7 +239,7 @@ def test_edge_object_without_normals_in_the_lit_path_tracer():
     W, H = 192, 128
     cam = rb.Camera(aspect=W / H)
     ref, _ = _run_vs_oracle(scene, cam, W, H, 3, 3, "normal-less object, lit scene")
-    sky = (ref[..., :3].view(np.uint32) == np.asarray(CLEAR, np.float32).view(np.uint32)).all(axis=2)
+    sky = np.abs(ref[..., :3] - np.asarray(CLEAR, np.float32)).max(axis=2) < 1e-6  # the running mean of equal values rounds
     assert 0.01 < sky.mean() < 0.5  # the ball's silhouette; the rest of the room is lit
     assert np.isfinite(ref).all()
 

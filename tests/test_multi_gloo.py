@@ -116,3 +116,49 @@ def test_two_rank_spp_slices_reduce_to_the_sequential_mean(tmp_path, oracle_lib)
         ref = orc.render(cam.ubo(), CLEAR, f, W, H, image=ref)
     assert np.allclose(got[..., :3], ref[..., :3], rtol=1e-5, atol=1e-6)
     assert np.all(got[..., 3] == 1.0)
+
+
+def _shared_worker(rank, world, port, W, H, strip, owners, out_path):
+    import torch.distributed as dist
+
+    from oracle.binding import OracleScene
+    from raytracer_b200 import multi_gpu
+    import raytracer_b200 as rb
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # the consume step of bench.py at N > 1: one host frame shared by the ranks, each writes its own strips into it
+        # (the GPU path pins the mapping and rt_readback writes the rows; here the oracle writes them), then a barrier
+        shared = multi_gpu.SharedHostImage(dist, H, W, 4, register=False)
+        orc = OracleScene(fixture_scene("cornell_pbr")).build_bvh()
+        cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+        for f in range(2):
+            for s, owner in enumerate(owners):   # an arbitrary (cost-balanced) strip -> rank table, not round robin
+                if owner == rank:
+                    orc.render(cam.ubo(), CLEAR, f, W, H, image=shared.array, y0=s * strip, y1=min(H, (s + 1) * strip))
+        dist.barrier()
+        if rank == 0:
+            np.save(out_path, np.array(shared.array, copy=True))
+        dist.barrier()
+        shared.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_write_their_strips_into_one_shared_host_frame(tmp_path, oracle_lib):
+    import torch.multiprocessing as mp
+
+    import raytracer_b200 as rb
+
+    W, H, strip = 32, 44, 8
+    owners = [1, 1, 0, 1, 0, 0]  # 6 strips (the last one partial), dealt unevenly on purpose
+    out = str(tmp_path / "img.npy")
+    mp.spawn(_shared_worker, args=(2, _free_port(), W, H, strip, owners, out), nprocs=2, join=True)
+    got = np.load(out)
+    orc = oracle_lib.OracleScene(fixture_scene("cornell_pbr")).build_bvh()
+    cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+    ref = None
+    for f in range(2):
+        ref = orc.render(cam.ubo(), CLEAR, f, W, H, image=ref)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))

@@ -41,6 +41,10 @@ __global__ void k(const uint4* table, uint32_t lines, uint32_t* out, int iters) 
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 
+static FILE* g_json = nullptr;  // optional: tools/mb/gather out.json -> the measured peaks bench.py's roofline reads
+static bool g_first = true;
+static double g_clock_hz = 1.965e9;
+
 template <int MODE>
 void run(const char* name, const uint4* table, uint32_t lines, uint32_t* out, int loads, int bytes) {
     cudaEvent_t a, b;
@@ -54,12 +58,26 @@ void run(const char* name, const uint4* table, uint32_t lines, uint32_t* out, in
     float ms;
     cudaEventElapsedTime(&ms, a, b);
     const double warp_iters = (double)blocks * threads / 32 * iters;
-    const double clk = ms * 1e-3 * 1.965e9 * 148;  // SM-cycles at the bench clock
+    const double clk = ms * 1e-3 * g_clock_hz * 148;  // SM-cycles at the bench clock
     printf("%-28s lines %6u: %.3f ms  %.1f cycles per warp-iteration per SM, %.3f warp-loads/clk/SM, %.1f B/clk/SM\n", name, lines, ms,
            clk / warp_iters, warp_iters * loads / clk, warp_iters * 32 * bytes / clk);
+    if (g_json) {
+        fprintf(g_json, "%s\n  {\"pattern\": \"%s\", \"table_bytes\": %llu, \"ms\": %.4f, \"cycles_per_warp_iteration\": %.2f, "
+                        "\"thread_loads_per_s\": %.4e, \"warp_iterations_per_s\": %.4e}",
+                g_first ? "" : ",", name, (unsigned long long)lines * 128ull, ms, clk / warp_iters, warp_iters * 32.0 * loads / (ms * 1e-3),
+                warp_iters / (ms * 1e-3));
+        g_first = false;
+    }
 }
 
-int main() {
+int main(int argc, char** argv) {
+    if (argc > 1) g_json = fopen(argv[1], "w");
+    {
+        int khz = 0;
+        if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, 0) == cudaSuccess && khz > 0) g_clock_hz = khz * 1e3;
+    }
+    if (g_json) fprintf(g_json, "{\"what\": \"divergent gather: every thread of a warp reads from its own random 128-byte line (tools/mb/gather.cu)\", "
+                                "\"sm_clock_hz\": %.4e, \"sms\": 148, \"blocks\": %d, \"threads\": 128, \"rows\": [", g_clock_hz, 148 * 8);
     uint4* table;
     uint32_t* out;
     const uint32_t max_lines = 1u << 20;  // 128 MB
@@ -76,5 +94,6 @@ int main() {
         run<4>("128 B = 8 x LDG.128", table, lines, out, 8, 128);
         run<5>("128 B = 4 x LDG.256", table, lines, out, 4, 128);
     }
+    if (g_json) { fprintf(g_json, "\n]}\n"); fclose(g_json); }
     return 0;
 }
