@@ -126,6 +126,29 @@ def inverse3(m):
     return [[c[r][col] for r in range(3)] for col in range(3)]
 
 
+class CommittedInstances:
+    """What rayQueryGetIntersectionInstanceCustomIndexEXT returns under the policy "all" (tools/spirv_golden.py): with
+    gl_RayFlagsTerminateOnFirstHitEXT the hit a ray query commits is whichever the traversal meets first — implementation
+    defined — so the value stands for EVERY instance the ray meets in range, and compares equal to x only when x is the
+    only one.  `instIdx == lightInstanceCustomIndex` (simple.rchit:381) then reads "no other instance occludes", the
+    deterministic semantics both the oracle and the CUDA path define."""
+
+    def __init__(self, first, others):
+        self.first, self.others = int(first), bool(others)
+
+    def __and__(self, mask):
+        return self
+
+    def __eq__(self, x):
+        return (not self.others) and self.first == (int(x) & 0xFFFFFFFF)
+
+    def __ne__(self, x):
+        return not self.__eq__(x)
+
+    def __int__(self):
+        return self.first
+
+
 class Module:
     def __init__(self, path):
         data = open(path, "rb").read()
@@ -257,13 +280,14 @@ class Machine:
         self.addresses = {}           # device address -> root cell of a buffer_reference block
         self.trace_ray = None         # callback(machine, origin, tmin, direction, tmax, payload_ptr)
         self.ray_query = None         # callback(origin, tmin, direction, tmax) -> None | instance custom index
-        self.image = None             # numpy (H, W, 4) float32
+        self.images = {}              # variable name -> numpy (H, W, 4) float32 (storage images; texel conversion is the caller's)
         self.sincos = sincos          # callable(float32) -> (sin, cos) of the arithmetic contract
         for vid, tid, storage in module.globals_decl:
             pointee = module.types[tid][2]
-            p = Ptr([module.default(pointee)])
-            self.g[vid] = p
             name = module.names.get(vid, f"%{vid}")
+            # an image variable "holds" its own name: OpLoad hands it to OpImageRead / OpImageWrite, which look the array up
+            p = Ptr([name if module.types[pointee][0] == "image" else module.default(pointee)])
+            self.g[vid] = p
             self.vars[name] = p
             b = module.decor.get(vid, {}).get(DEC_BUILTIN)
             if b is not None:
@@ -471,13 +495,14 @@ class Machine:
                 elif op == 4479:  # committed intersection type: 0 none, 1 triangle
                     v[a[1]] = 0 if val(a[2]).load()[1] is None else 1
                 elif op == 6019:  # committed instance custom index
-                    v[a[1]] = int(val(a[2]).load()[1])
+                    c = val(a[2]).load()[1]
+                    v[a[1]] = c if isinstance(c, CommittedInstances) else int(c)
                 elif op == 98:    # ImageRead
                     c = val(a[3])
-                    v[a[1]] = [F32(x) for x in self.image[_signed(c[1]), _signed(c[0])]]
+                    v[a[1]] = [F32(x) for x in self.images[val(a[2])][_signed(c[1]), _signed(c[0])]]
                 elif op == 99:    # ImageWrite
                     c = val(a[1])
-                    self.image[_signed(c[1]), _signed(c[0])] = [F32(x) for x in val(a[2])]
+                    self.images[val(a[0])][_signed(c[1]), _signed(c[0])] = [F32(x) for x in val(a[2])]
                 else:
                     raise NotImplementedError(f"{self.m.path}: opcode {op} {a}")
                 if nxt is not None:
@@ -525,7 +550,7 @@ class Machine:
         if inst == 4:
             return _ew1(o[0], np.abs)
         if inst == 6:
-            return _ew1(o[0], lambda x: F32(float((x > 0) - (x < 0))))
+            return _ew1(o[0], lambda x: F32(float(int(x > 0) - int(x < 0))))
         if inst == 26:  # pow: the shaders only raise to the fifth power (simple.rchit:97): ((x^2)^2) x
             if float(o[1]) != 5.0:
                 raise NotImplementedError(f"pow(x, {o[1]})")
