@@ -564,3 +564,46 @@ def test_restir_history_restarts_on_camera_or_scene_change():
             c.restir_frame(cam.ubo(), CLEAR, 0, prm)
     finally:
         c.close()
+
+
+# ---- the reference's SHIPPED shader binaries (tests/golden/spirv_frames.npz, tools/spirv_golden.py) ------------------------
+@pytest.mark.parametrize("pipeline", ["packets", "per_ray", "megakernel"])
+@pytest.mark.parametrize("name,W,H,n", [("cornell_box", 32, 32, 3), ("cornell_pbr", 32, 32, 3), ("conference", 32, 20, 2),
+                                         ("multi_dispersion", 32, 18, 2)])
+def test_frames_of_the_shipped_spirv_binaries(name, W, H, n, pipeline):
+    """What rgen.spv / rchit.spv / rmiss.spv compute when executed instruction by instruction on the reference's scene
+    files == what the CUDA path computes, bit for bit, frame after frame, in all three pipelines."""
+    import os
+
+    from conftest import GOLDEN
+
+    z = np.load(os.path.join(GOLDEN, "spirv_frames.npz"))
+    c = librt.Context(device=0, pipeline=librt.RT_PIPELINE_MEGAKERNEL if pipeline == "megakernel" else librt.RT_PIPELINE_WAVEFRONT,
+                      per_ray_primary=pipeline == "per_ray")
+    try:
+        c.build_scene(fixture_scene(name))
+        c.resize(W, H)
+        for f in range(n):
+            c.trace_frame(z[name + "/camera"], z["clear"], f)
+            got = c.readback()
+            bad = (got.view(np.uint32) != z[name + "/frames"][f].view(np.uint32)).any(axis=2)
+            assert not bad.any(), f"{name} frame {f}: {int(bad.sum())} pixels differ from the shipped SPIR-V"
+        dev = c.counters()
+        assert [dev["extend_rays"], dev["shadow_rays"], dev["hits"]] == [int(x) for x in z[name + "/rays"]]
+    finally:
+        c.close()
+
+
+@pytest.mark.parametrize("name,W,H", [("cornell_pbr", 32, 32), ("conference", 32, 20)])
+def test_gbuffer_of_the_shipped_spirv_binaries(ctx, name, W, H):
+    import os
+
+    from conftest import GOLDEN
+
+    z = np.load(os.path.join(GOLDEN, "spirv_frames.npz"))
+    ctx.build_scene(fixture_scene(name))
+    ctx.resize(W, H)
+    ctx.trace_gbuffer(z[name + "/camera"])
+    got = ctx.readback_gbuffer()
+    for k in ("albedo", "output", "normal_rough", "position_metal", "emission"):
+        assert np.array_equal(got[k].view(np.uint8), z[f"{name}/gbuffer/{k}"].view(np.uint8)), k

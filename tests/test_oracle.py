@@ -213,3 +213,85 @@ def test_shipped_call_graph_is_the_restated_one():
     text = "".join(open(os.path.join(root, "oracle", f)).read() for f in ("oracle_render.cpp", "oracle_math.h"))
     uncited = [f for f in set(chit["reachable"]) | set(gen["reachable"]) if f != "main" and f not in text]
     assert not uncited, f"functions of the shipped shaders the oracle does not cite: {uncited}"
+
+
+# ---- the reference's SHIPPED shader binaries, executed (tools/spirv_interp.py) --------------------------------------------
+# tests/golden/spirv_frames.npz holds what rgen.spv / rchit.spv / rmiss.spv (and restir_rgen / restir_rchit.spv) compute when
+# an interpreter runs them instruction by instruction on the reference's own scene files (tools/spirv_golden.py).  That pins
+# evaluation order, association, branch structure and the order of the random draws of the binary — not just its constants.
+def _spirv_fixture():
+    return np.load(os.path.join(GOLDEN, "spirv_frames.npz"))
+
+
+SPIRV_CASES = {"cornell_box": (32, 32, 3), "cornell_pbr": (32, 32, 3), "conference": (32, 20, 2), "multi_dispersion": (32, 18, 2)}
+
+
+@pytest.mark.parametrize("name", sorted(SPIRV_CASES))
+def test_oracle_reproduces_the_frames_of_the_shipped_binaries(oracle_lib, name):
+    z = _spirv_fixture()
+    W, H, n = SPIRV_CASES[name]
+    orc = oracle_lib.OracleScene(fixture_scene(name)).build_bvh()
+    cnt = np.zeros(6, np.uint64)
+    img = None
+    for f in range(n):
+        img = orc.render(z[name + "/camera"], z["clear"], f, W, H, image=img, counters=cnt)
+        want = z[name + "/frames"][f]
+        bad = (img.view(np.uint32) != want.view(np.uint32)).any(axis=2)
+        assert not bad.any(), f"{name} frame {f}: {int(bad.sum())} pixels differ from what the shipped SPIR-V computes"
+    # the same rays: OpTraceRayKHR executions, ray queries, closest-hit shader invocations
+    assert [int(cnt[0]), int(cnt[1]), int(cnt[4])] == [int(x) for x in z[name + "/rays"]]
+    assert img[..., :3].max() > 0.05
+
+
+@pytest.mark.parametrize("name", ["cornell_pbr", "conference"])
+def test_oracle_reproduces_the_gbuffer_of_the_shipped_binaries(oracle_lib, name):
+    z = _spirv_fixture()
+    W, H, _ = SPIRV_CASES[name]
+    g = oracle_lib.OracleScene(fixture_scene(name)).build_bvh().gbuffer(z[name + "/camera"], W, H)
+    for k in ("albedo", "output", "normal_rough", "position_metal", "emission"):
+        assert np.array_equal(g[k].view(np.uint8), z[f"{name}/gbuffer/{k}"].view(np.uint8)), k
+
+
+def test_oracle_reproduces_the_function_vectors_of_rchit_spv(oracle_lib):
+    """sampleBRDF / evaluateFullBRDF of rchit.spv (and everything they reach: D_GGX, G_Smith, F_Schlick, microfacetF,
+    microfacetPDF, sampleGGX, getSpecularProbability, generateCosineWeightedDirection) on 256 random inputs incl. grazing
+    directions and the roughness / metallic extremes: same bits, same seed afterwards."""
+    import ctypes as C
+
+    z = _spirv_fixture()
+    L = oracle_lib.lib()
+    n = len(z["units/wo"])
+    assert n >= 256 and 0.1 < z["units/sampleBRDF"][:, 7].mean() < 0.9  # both lobes occur
+    for k in range(n):
+        m, wo, wi = (np.ascontiguousarray(z[f"units/{q}"][k]) for q in ("materials", "wo", "wi"))
+        seed = C.c_uint32(int(z["units/seed_in"][k]))
+        out = np.zeros(8, np.float32)
+        L.orc_unit_sample_brdf(m.ctypes.data, wo.ctypes.data, float(z["units/xi"][k, 0]), float(z["units/xi"][k, 1]), C.byref(seed), out.ctypes.data)
+        assert np.array_equal(out.view(np.uint32), z["units/sampleBRDF"][k].view(np.uint32)), k
+        assert seed.value == int(z["units/seed_out"][k])
+        o4 = np.zeros(4, np.float32)
+        L.orc_unit_eval_brdf(m.ctypes.data, wo.ctypes.data, wi.ctypes.data, o4.ctypes.data)
+        assert np.array_equal(o4[:3].view(np.uint32), z["units/evaluateFullBRDF"][k].view(np.uint32)), k
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/shaders"), reason="reference mount absent (the fixture itself is committed)")
+def test_the_fixture_is_what_the_binaries_compute(oracle_lib):
+    """Re-executes a sample of pixels from /root/reference/shaders/*.spv: the committed frames really come from the binaries."""
+    import sys
+
+    sys.path.insert(0, os.path.join(os.path.dirname(GOLDEN), os.pardir, "tools"))
+    import spirv_golden as G
+
+    z = _spirv_fixture()
+    sincos = G.make_sincos()
+    for name, px in (("cornell_pbr", [(16, 16), (20, 12), (5, 5), (10, 28), (27, 19)]), ("conference", [(13, 0), (24, 5), (6, 14), (18, 9)])):
+        scene, cam, W, H, n = G.load_case(name)
+        vm = G.ShaderVM("/root/reference", scene, oracle_lib.OracleScene(scene).build_bvh(), sincos)
+        img = z[name + "/frames"][0].copy()   # frame 1 reads the previous mean of the pixels it touches
+        vm.render(z[name + "/camera"], z["clear"], 1, W, H, image=img, pixels=px)
+        for (x, y) in px:
+            assert np.array_equal(img[y, x].view(np.uint32), z[name + "/frames"][1][y, x].view(np.uint32)), (name, x, y)
+    # the ray-query policy matters where the fixture says it does: a driver committing the closest hit lights more pixels
+    a, b = z["conference/frames"], z["conference/frames_closest_commit"]
+    d = (a.view(np.uint32) != b.view(np.uint32)).any(axis=3)
+    assert 0 < d.sum() < 0.1 * d.size and (b[d][:, :3].sum(axis=1) >= a[d][:, :3].sum(axis=1) - 1e-6).mean() > 0.9

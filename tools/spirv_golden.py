@@ -192,6 +192,40 @@ class ShaderVM:
         raise KeyError("payload")
 
 
+def unit_vectors(ref_dir, sincos, n=256, seed=7):
+    """Function-level vectors from rchit.spv: sampleBRDF (simple.rchit:403-449; reaches getSpecularProbability, sampleGGX,
+    generateCosineWeightedDirection, microfacetF, microfacetPDF, D_GGX, G_Smith, F_Schlick) and evaluateFullBRDF (:118-166)
+    on random materials and directions, grazing angles and the roughness extremes included — inputs the small frames
+    need not contain.  Returned as arrays: inputs, then what the BINARY computes."""
+    mod = si.Module(os.path.join(ref_dir, "shaders", "rchit.spv"))
+    vm = si.Machine(mod, sincos)
+    f_sample, f_eval = mod.function_named("sampleBRDF"), mod.function_named("evaluateFullBRDF")
+    rng = np.random.default_rng(seed)
+    mats = np.zeros((n, 11), np.float32)      # the 44-byte Material record
+    mats[:, 0:3] = rng.random((n, 3))
+    mats[:, 7] = np.where(rng.random(n) < 0.2, rng.choice([0.0, 0.02, 1.0], n), rng.random(n))   # roughness
+    mats[:, 8] = np.where(rng.random(n) < 0.5, rng.choice([0.0, 1.0], n), rng.random(n))         # metallic
+    def dirs(k):
+        d = rng.standard_normal((k, 3)).astype(np.float32)
+        d[:, 2] = np.abs(d[:, 2]) * np.where(rng.random(k) < 0.25, 0.02, 1.0)   # a quarter of them grazing
+        return (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    wo, wi = dirs(n), dirs(n)
+    xi = rng.random((n, 2)).astype(np.float32)
+    seeds = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    ident = [_vec(c) for c in np.eye(3, dtype=np.float32)]
+    sample_out, eval_out, seed_out = np.zeros((n, 8), np.float32), np.zeros((n, 3), np.float32), np.zeros(n, np.uint32)
+    for k in range(n):
+        m = mats[k]
+        mat = [_vec(m[0:3]), _vec(m[3:6]), F32(m[6]), F32(m[7]), F32(m[8]), F32(m[9]), F32(m[10])]
+        vm.vars["payload"].at([4]).store(int(seeds[k]))   # RayPayload.seed: the lobe choice draws from it (simple.rchit:408)
+        r = vm.run(f_sample, [si.Ptr([_vec(wo[k])]), si.Ptr([mat]), si.Ptr([_vec(xi[k])]), si.Ptr([ident])])
+        sample_out[k] = list(r[0]) + list(r[1]) + [r[2], F32(1.0 if r[3] else 0.0)]
+        seed_out[k] = vm.vars["payload"].at([4]).load()
+        eval_out[k] = vm.run(f_eval, [si.Ptr([_vec(wo[k])]), si.Ptr([_vec(wi[k])]), si.Ptr([mat])])
+    return {"units/materials": mats, "units/wo": wo, "units/wi": wi, "units/xi": xi, "units/seed_in": seeds,
+            "units/sampleBRDF": sample_out, "units/seed_out": seed_out, "units/evaluateFullBRDF": eval_out}
+
+
 def make_sincos():
     from oracle import binding
 
@@ -215,12 +249,15 @@ def main():
     ap.add_argument("--ref", default="/root/reference")
     ap.add_argument("--out", default=os.path.join(ROOT, "tests", "golden", "spirv_frames.npz"))
     ap.add_argument("--cases", default=",".join(CASES))
+    ap.add_argument("--only-units", action="store_true", help="regenerate the function vectors only")
     a = ap.parse_args()
     from oracle.binding import OracleScene
 
     sincos = make_sincos()
     out = {}
-    for name in a.cases.split(","):
+    if a.only_units:
+        a.cases = ""
+    for name in [c for c in a.cases.split(",") if c]:
         scene, cam, W, H, n = load_case(name)
         orc = OracleScene(scene).build_bvh()
         vm = ShaderVM(a.ref, scene, orc, sincos)
@@ -255,7 +292,14 @@ def main():
         print(f"{name}: G-buffer {W}x{H}, {vm.rays}, {time.time() - t0:.1f} s", flush=True)
         for k, v in gb.items():
             out[f"{name}/gbuffer/{k}"] = v
+    t0 = time.time()
+    out.update(unit_vectors(a.ref, sincos))
+    print(f"function vectors: {len(out['units/wo'])} x (sampleBRDF, evaluateFullBRDF), {time.time() - t0:.1f} s", flush=True)
     out["clear"] = np.asarray(CLEAR, np.float32)
+    if a.only_units:   # keep the frames of the existing fixture
+        old = dict(np.load(a.out))
+        old.update({k: v for k, v in out.items() if k.startswith("units/")})
+        out = old
     np.savez_compressed(a.out, **out)
     print("wrote", a.out)
 
