@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--inproc", action="store_true",
                     help="N > 1 without torchrun: ONE process drives all N GPUs through one multi-GPU rt_ctx (rt_config.device_ids)")
     ap.add_argument("--no-verify", action="store_true", help="skip the sharded-vs-single-GPU image hash check")
+    ap.add_argument("--balance-rounds", type=int, default=8,
+                    help="N > 1, --balance cost: feedback rounds (measured rank times -> strip trades) before the warm-up")
     return ap.parse_args()
 
 
@@ -262,6 +264,38 @@ def run_ours(args):
     primary_total = reduce_scalar(float(cnt1["extend_rays"]), "SUM")
     secondary_total = reduce_scalar(float(cnt["extend_rays"] - cnt1["extend_rays"]), "SUM")
 
+    # ---- N > 1: strips by cost.  The library's calibration pass deals them by its cost model at the first frame 0; measured
+    # rank times then refine the deal (multi_gpu.StripBalancer: every rank feeds the same gathered times to the same
+    # deterministic rule, the library installs the table).  All of it happens before the warm-up, outside the timed region.
+    balance_log = None
+    if balance and n_gpus > 1:
+        from raytracer_b200 import multi_gpu
+
+        ctx.trace_frames(ubo, CLEAR, 0, B)
+        ctx.synchronize()
+        rows = ctx.measure_row_costs(ubo, 0).astype(np.float64)
+        per_row = multi_gpu.MODEL_WEIGHTS[0] * W + rows[:, :3] @ np.asarray(multi_gpu.MODEL_WEIGHTS[1:], np.float64)
+        n_strips = (H + 7) // 8
+        costs = np.add.reduceat(per_row, np.arange(0, H, 8))[:n_strips]
+        bal = multi_gpu.StripBalancer(H, n_gpus, 8, owners=ctx.strip_owners(), costs=costs)
+        balance_log = []
+
+        def rank_times():
+            ctx.event_record(0)
+            for _ in range(2):
+                ctx.trace_frames(ubo, CLEAR, 0, B)
+            ctx.event_record(1)
+            return ctx.event_elapsed_per_device() if inproc else gather_scalars(ctx.event_elapsed_ms())
+
+        for _ in range(max(args.balance_rounds, 0)):
+            t = rank_times()
+            balance_log.append(round(max(t) / (sum(t) / len(t)), 4))
+            ctx.set_strip_owners(bal.update(t))
+        t = rank_times()
+        balance_log.append(round(max(t) / (sum(t) / len(t)), 4))
+        bal.update(t)
+        ctx.set_strip_owners(bal.best_owners())
+
     # ---- device-resident throughput ---------------------------------------------------------------------
     for s in range(Wm):
         ctx.trace_frames(ubo, CLEAR, s * B, B)  # frame 0 comes first: RT_BALANCE_COST measures the strips here
@@ -282,7 +316,7 @@ def run_ours(args):
     barrier()
     sampler.stop_flag = True
     launches = ctx.counters()["launches"]
-    ms_ranks = gather_scalars(ms)
+    ms_ranks = ctx.event_elapsed_per_device() if inproc else gather_scalars(ms)
     ms_max = max(ms_ranks)
     value = rays_total / (ms_max * 1e-3) / 1e6
 
@@ -457,7 +491,8 @@ def run_ours(args):
                 "gpu_launches": int(launches), "clocks": sampler.summary()}
         if n_gpus > 1:
             line["ranks"] = {"ms_per_step": [round(m / K, 4) for m in ms_ranks], "slowest_over_mean": ms_max / (sum(ms_ranks) / len(ms_ranks)),
-                             "strips_per_rank": [owners.count(r) for r in range(n_gpus)] if owners else None}
+                             "strips_per_rank": [owners.count(r) for r in range(n_gpus)] if owners else None,
+                             "balance_rounds_slowest_over_mean": balance_log}
         if split:
             line.update({k: split[k] for k in ("primary_mrays_s", "incoherent_mrays_s")})
             line["ray_split"] = split

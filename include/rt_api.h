@@ -247,6 +247,12 @@ RT_API int rt_upload_accum(rt_ctx* ctx, const float* src_rgba32f, size_t bytes);
  * (rows s*strip_rows ...).  owners may be NULL to query n_strips.  With RT_BALANCE_COST the table changes when an
  * accumulation restarts after rt_resize or rt_rebalance; every rank of a partition derives the same table. */
 RT_API int rt_get_strip_owners(rt_ctx* ctx, uint32_t* owners, uint32_t capacity, uint32_t* n_strips);
+/* the calibration pass on its own: out4[4 y + k] = {traversal work of the primary rays, of the continuation rays, closest-hit
+ * shader invocations, continuation rays} of image row y for the frame `frame_number` (capacity_rows >= height) */
+RT_API int rt_measure_row_costs(rt_ctx* ctx, const float camera_ubo[64], uint32_t frame_number, uint32_t* out4, uint32_t capacity_rows);
+/* a strip -> rank table decided by the host (measured step times, say); every rank keeps its round-robin row count; the
+ * accumulation must restart with frame_number 0 afterwards, because image rows change hands */
+RT_API int rt_set_strip_owners(rt_ctx* ctx, const uint32_t* owners, uint32_t n_strips);
 /* RT_BALANCE_COST: measure the strips again at the next frame_number == 0 trace (the camera settled somewhere else) */
 RT_API int rt_rebalance(rt_ctx* ctx);
 
@@ -273,6 +279,8 @@ RT_API int rt_last_trace_ms(rt_ctx* ctx, float* ms);
  * synchronises on the stop event.  Lets a caller time any sequence of calls on the device. */
 RT_API int rt_event_record(rt_ctx* ctx, int which);
 RT_API int rt_event_elapsed_ms(rt_ctx* ctx, float* ms);
+/* the same pair per device of a multi-GPU context (one entry otherwise); ms may be NULL to query n_devices */
+RT_API int rt_event_elapsed_per_device(rt_ctx* ctx, float* ms, uint32_t capacity, uint32_t* n_devices);
 /* per-kernel device times of the wavefront pipeline: when enabled, every launch is bracketed by CUDA
  * events on the launching stream; rt_get_kernel_profile sums them since the last enable/reset. */
 /* RT_K_EXTEND: per-ray closest-hit traversal (all bounces but the first, and first-bounce tiles the packet kernel

@@ -489,58 +489,51 @@ void rt_end_timing(rt_ctx* ctx) {
 // One calibration pass over the FULL frame (every rank runs the same deterministic pass and so derives the same table without
 // talking to anyone), then longest-processing-time-first under the constraint that every rank keeps the NUMBER of strips the
 // round-robin deal gives it — so the compact image, the path state and the frames in flight keep their sizes.
-#ifndef RT_BALANCE_SECONDARY_WEIGHT
-#define RT_BALANCE_SECONDARY_WEIGHT 6u  /* an incoherent continuation ray costs about six packet-traced primary rays */
+// cost of a strip = sum over its rows of W_PX * pixels + W_PRIMARY * c0 + W_SECONDARY * c1 + W_HIT * c2 (row_cost_kernel's
+// counters); the weights are tenths of a picosecond of device time per unit, fitted by non-negative least squares to the 16
+// per-rank step times of two 8-way partitions on a B200 (tools/fit_balance.py: rms error 1.0 %)
+#ifndef RT_BALANCE_W_PX
+#define RT_BALANCE_W_PX 267u
+#define RT_BALANCE_W_PRIMARY 9u
+#define RT_BALANCE_W_SECONDARY 12u
+#define RT_BALANCE_W_HIT 1572u
 #endif
-static int balance_strips(rt_ctx* ctx, const float* camera_ubo, const float* clear_color, uint32_t frame) {
-    ctx->balance_pending = false;
-    const uint32_t sr = ctx->cfg.strip_rows, N = ctx->cfg.strip_count, H = ctx->height, W = ctx->width;
-    const uint32_t n_full = H / sr, n_strips = (H + sr - 1) / sr;
-    if (N <= 1 || n_full == 0) return RT_OK;
+static int measure_row_costs(rt_ctx* ctx, const float* camera_ubo, const float* clear_color, uint32_t frame, std::vector<uint32_t>& rows) {
+    const uint32_t H = ctx->height;
     PoolScope pool_scope(ctx->pool);
     PoolBuf<uint32_t> d_cost;
-    RT_CUDA_TRY(d_cost.alloc(H, ctx->stream));
-    RT_CUDA_TRY(cudaMemsetAsync(d_cost.p, 0, (size_t)H * 4, ctx->stream));
+    RT_CUDA_TRY(d_cost.alloc((size_t)H * 4, ctx->stream));
+    RT_CUDA_TRY(cudaMemsetAsync(d_cost.p, 0, (size_t)H * 16, ctx->stream));
     FrameParams fp;
     rt_fill_frame_params(ctx, camera_ubo, clear_color, frame, &fp);
     fp.strip_count = 1; fp.strip_index = 0; fp.band_strip = nullptr; fp.local_rows = H;
     if (!ctx->dims.num_sms) cudaDeviceGetAttribute(&ctx->dims.num_sms, cudaDevAttrMultiProcessorCount, ctx->device);
     std::string err;
-    int rc = launch_row_cost(rt_scene_view(ctx), fp, d_cost.p, ctx->dims.num_sms > 0 ? ctx->dims.num_sms : 148, ctx->stream, err);
+    const int rc = launch_row_cost(rt_scene_view(ctx), fp, d_cost.p, ctx->dims.num_sms > 0 ? ctx->dims.num_sms : 148, ctx->stream, err);
     if (rc != RT_OK) { set_error(err); return rc; }
     ctx->launches++;
-    std::vector<uint32_t> rows(H);
-    RT_CUDA_TRY(cudaMemcpyAsync(rows.data(), d_cost.p, (size_t)H * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    rows.resize((size_t)H * 4);
+    RT_CUDA_TRY(cudaMemcpyAsync(rows.data(), d_cost.p, (size_t)H * 16, cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
-    std::vector<uint64_t> cost(n_full);
-    for (uint32_t st = 0; st < n_full; st++) {
-        uint64_t extra = 0;
-        for (uint32_t r = 0; r < sr; r++) extra += rows[st * sr + r];
-        cost[st] = (uint64_t)sr * W + (uint64_t)RT_BALANCE_SECONDARY_WEIGHT * extra;
-    }
-    std::vector<uint32_t> order(n_full), cap(N, 0u);
-    for (uint32_t st = 0; st < n_full; st++) { order[st] = st; cap[st % N]++; }
-    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });  // ties: lower strip first
-    std::vector<uint64_t> load(N, 0ull);
-    ctx->strip_owner.assign(n_strips, 0u);
-    for (uint32_t st : order) {
-        uint32_t best = N;
-        for (uint32_t r = 0; r < N; r++)
-            if (cap[r] && (best == N || load[r] < load[best])) best = r;
-        ctx->strip_owner[st] = best;
-        load[best] += cost[st];
-        cap[best]--;
-    }
-    if (n_strips > n_full) ctx->strip_owner[n_full] = n_full % N;  // the partial last strip stays its round-robin owner's last band
-    ctx->band_strip.clear();
-    for (uint32_t st = 0; st < n_strips; st++)
-        if (ctx->strip_owner[st] == ctx->cfg.strip_index) ctx->band_strip.push_back(st);  // ascending: top to bottom
+    return RT_OK;
+}
+
+// Installs a strip -> rank table: this context's bands (ascending strips), host + device copies.
+static int install_owners(rt_ctx* ctx, const uint32_t* owners, uint32_t n_strips) {
+    const uint32_t sr = ctx->cfg.strip_rows, H = ctx->height;
+    std::vector<uint32_t> mine;
     uint32_t rows_mine = 0;
-    for (uint32_t st : ctx->band_strip) rows_mine += std::min(sr, H - st * sr);
-    if (rows_mine != ctx->local_rows) {
-        set_error("balance_strips: row count changed");  // cannot happen: the capacities are the round-robin counts
-        return RT_ERR_CUDA;
+    for (uint32_t st = 0; st < n_strips; st++)
+        if (owners[st] == ctx->cfg.strip_index) { mine.push_back(st); rows_mine += std::min(sr, H - st * sr); }
+    const uint32_t n_full = H / sr;
+    if (rows_mine != ctx->local_rows || (n_strips > n_full && !mine.empty() && owners[n_full] == ctx->cfg.strip_index && mine.back() != n_full)) {
+        set_error("strip owners: every rank must keep the row count of the round-robin deal (the partial last strip stays where it is)");
+        return RT_ERR_INVALID_ARGUMENT;
     }
+    RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    for (cudaStream_t st : ctx->streamx) if (st) RT_CUDA_TRY(cudaStreamSynchronize(st));
+    ctx->strip_owner.assign(owners, owners + n_strips);
+    ctx->band_strip.swap(mine);
     RT_CUDA_TRY(ctx->d_band_strip.ensure(ctx->band_strip.size()));
     if (!ctx->band_strip.empty())
         RT_CUDA_TRY(cudaMemcpyAsync(ctx->d_band_strip.p, ctx->band_strip.data(), ctx->band_strip.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -548,6 +541,40 @@ static int balance_strips(rt_ctx* ctx, const float* camera_ubo, const float* cle
     ctx->rs_history = false;   // per-pixel histories belong to the rows that were here before
     ctx->has_gbuffer = false;
     return RT_OK;
+}
+
+static int balance_strips(rt_ctx* ctx, const float* camera_ubo, const float* clear_color, uint32_t frame) {
+    ctx->balance_pending = false;
+    const uint32_t sr = ctx->cfg.strip_rows, N = ctx->cfg.strip_count, H = ctx->height, W = ctx->width;
+    const uint32_t n_full = H / sr, n_strips = (H + sr - 1) / sr;
+    if (N <= 1 || n_full == 0) return RT_OK;
+    std::vector<uint32_t> rows;
+    int rc = measure_row_costs(ctx, camera_ubo, clear_color, frame, rows);
+    if (rc != RT_OK) return rc;
+    std::vector<uint64_t> cost(n_full);
+    for (uint32_t st = 0; st < n_full; st++) {
+        uint64_t c = (uint64_t)RT_BALANCE_W_PX * sr * W;
+        for (uint32_t r = 0; r < sr; r++) {
+            const uint32_t* q = &rows[(size_t)(st * sr + r) * 4];
+            c += (uint64_t)RT_BALANCE_W_PRIMARY * q[0] + (uint64_t)RT_BALANCE_W_SECONDARY * q[1] + (uint64_t)RT_BALANCE_W_HIT * q[2];
+        }
+        cost[st] = c;
+    }
+    std::vector<uint32_t> order(n_full), cap(N, 0u);
+    for (uint32_t st = 0; st < n_full; st++) { order[st] = st; cap[st % N]++; }
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });  // ties: lower strip first
+    std::vector<uint64_t> load(N, 0ull);
+    std::vector<uint32_t> owner(n_strips, 0u);
+    for (uint32_t st : order) {
+        uint32_t best = N;
+        for (uint32_t r = 0; r < N; r++)
+            if (cap[r] && (best == N || load[r] < load[best])) best = r;
+        owner[st] = best;
+        load[best] += cost[st];
+        cap[best]--;
+    }
+    if (n_strips > n_full) owner[n_full] = n_full % N;  // the partial last strip stays its round-robin owner's last band
+    return install_owners(ctx, owner.data(), n_strips);
 }
 
 extern "C" {
@@ -887,6 +914,44 @@ int rt_get_strip_owners(rt_ctx* ctx, uint32_t* owners, uint32_t capacity, uint32
     return RT_OK;
 }
 
+// The calibration pass on its own (tools/fit_balance.py): four counters per image row, see row_cost_kernel.
+int rt_measure_row_costs(rt_ctx* ctx, const float camera_ubo[64], uint32_t frame_number, uint32_t* out4, uint32_t capacity_rows) {
+    CTX_CHECK(ctx);
+    if (!ctx->children.empty()) {
+        const int rc0 = rt_measure_row_costs(ctx->children[0], camera_ubo, frame_number, out4, capacity_rows);
+        if (rc0 != RT_OK) ctx->error = ctx->children[0]->error;
+        return rc0;
+    }
+    if (!camera_ubo || !out4) return RT_ERR_INVALID_ARGUMENT;
+    int rc = rt_flush_scene(ctx);
+    if (rc != RT_OK) return rc;
+    rc = rt_require_target(ctx);
+    if (rc != RT_OK) return rc;
+    if (capacity_rows < ctx->height) { set_error("rt_measure_row_costs: capacity too small"); return RT_ERR_INVALID_ARGUMENT; }
+    const float clear[3] = {0.0f, 0.0f, 0.0f};
+    std::vector<uint32_t> rows;
+    rc = measure_row_costs(ctx, camera_ubo, clear, frame_number, rows);
+    if (rc != RT_OK) return rc;
+    memcpy(out4, rows.data(), rows.size() * sizeof(uint32_t));
+    return RT_OK;
+}
+
+// A strip -> rank table decided by the HOST (e.g. from measured per-rank step times: raytracer_b200.multi_gpu.StripBalancer).
+// Every rank must keep the number of rows the round-robin deal gives it.  The image rows change hands: the accumulation
+// must restart (frame_number 0) after this call; a pending cost calibration is cancelled.
+int rt_set_strip_owners(rt_ctx* ctx, const uint32_t* owners, uint32_t n_strips) {
+    CTX_CHECK(ctx);
+    FANOUT(ctx, rt_set_strip_owners(c, owners, n_strips));
+    const int rc = rt_require_target(ctx);
+    if (rc != RT_OK) return rc;
+    const uint32_t sr = ctx->cfg.strip_rows;
+    if (!owners || n_strips != (ctx->height + sr - 1) / sr) { set_error("rt_set_strip_owners: one owner per strip"); return RT_ERR_INVALID_ARGUMENT; }
+    for (uint32_t st = 0; st < n_strips; st++)
+        if (owners[st] >= ctx->cfg.strip_count) { set_error("rt_set_strip_owners: owner out of range"); return RT_ERR_INDEX_RANGE; }
+    ctx->balance_pending = false;
+    return install_owners(ctx, owners, n_strips);
+}
+
 // Ask for a new cost calibration at the next accumulation restart (e.g. after the camera settled somewhere else).
 int rt_rebalance(rt_ctx* ctx) {
     CTX_CHECK(ctx);
@@ -1000,6 +1065,22 @@ int rt_event_elapsed_ms(rt_ctx* ctx, float* ms) {
     if (!ms || !ctx->user_ev[0] || !ctx->user_ev[1]) { set_error("rt_event_elapsed_ms: record both events first"); return RT_ERR_INVALID_ARGUMENT; }
     RT_CUDA_TRY(cudaEventSynchronize(ctx->user_ev[1]));
     RT_CUDA_TRY(cudaEventElapsedTime(ms, ctx->user_ev[0], ctx->user_ev[1]));
+    return RT_OK;
+}
+
+// the same event pair per device of a multi-GPU context (a single-device context has one entry): what a host-side strip
+// balancer feeds on
+int rt_event_elapsed_per_device(rt_ctx* ctx, float* ms, uint32_t capacity, uint32_t* n_devices) {
+    CTX_CHECK(ctx);
+    const uint32_t n = ctx->children.empty() ? 1u : (uint32_t)ctx->children.size();
+    if (n_devices) *n_devices = n;
+    if (!ms) return RT_OK;
+    if (capacity < n) { set_error("rt_event_elapsed_per_device: capacity too small"); return RT_ERR_INVALID_ARGUMENT; }
+    if (ctx->children.empty()) return rt_event_elapsed_ms(ctx, ms);
+    for (uint32_t k = 0; k < n; k++) {
+        const int rc = rt_event_elapsed_ms(ctx->children[k], ms + k);
+        if (rc != RT_OK) { ctx->error = ctx->children[k]->error; return rc; }
+    }
     return RT_OK;
 }
 

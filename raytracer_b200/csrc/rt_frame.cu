@@ -155,27 +155,33 @@ int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameRes
     return RT_OK;
 }
 
-// Strip-cost calibration (RT_BALANCE_COST): the paths of the full frame once more, nothing stored but how many closest-hit
-// rays beyond the primary one each image row traced.  Incoherent rays cost ~8x a packet-traced primary ray (DESIGN.md
-// §5.2), so rows x width + 8 x this count is the cost the strips are balanced by (rt_api.cu: balance_strips).  Light
-// samples are drawn (the random stream must stay the path's) but not evaluated; visibility rays are not traced.
+// Strip-cost calibration (RT_BALANCE_COST): the paths of the full frame once more, nothing stored but what each image row
+// costs: row_cost[4 y + 0] = nodes + triangles a per-ray walk of its PRIMARY rays fetches (the proxy for the packet kernel's
+// work), [4 y + 1] = nodes + triangles of its continuation rays (wf_extend_coop_kernel), [4 y + 2] = closest-hit shader
+// invocations, [4 y + 3] = continuation rays.  rt_api.cu (balance_strips) weighs them with the measured cost of each
+// (tools/fit_balance.py).  Light samples are drawn (the random stream must stay the path's) but not evaluated;
+// visibility rays are not traced.
 __global__ void __launch_bounds__(128) row_cost_kernel(SceneView sc, FrameParams fp, uint32_t* row_cost) {
     const uint32_t n_px = fp.height * fp.width;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n_px; base += gridDim.x * blockDim.x) {
         const uint32_t px = base + threadIdx.x;
-        uint32_t extra = 0, y = 0;
+        uint32_t c[4] = {0u, 0u, 0u, 0u};
+        uint32_t y = 0;
         if (px < n_px) {
             y = px / fp.width;
             const uint32_t x = px - y * fp.width;
             PathState ps;
             vec3 o, d;
             raygen_init(fp, x, y, ps, &o, &d);
-            uint32_t nn = 0, nt = 0, nee = 0;
+            uint32_t nee = 0;
             for (int depth = 0; depth < fp.max_depth; depth++) {
                 if (!russian_roulette(ps, depth, fp.rr_start)) break;
-                if (depth > 0) extra++;
-                const Hit h = traverse<false, false>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, nn, nt);
+                uint32_t nn = 0, nt = 0;
+                const Hit h = traverse<false, true>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, nn, nt);
+                c[depth == 0 ? 0 : 1] += nn + nt;
+                if (depth > 0) c[3]++;
                 if (h.id == 0xFFFFFFFFu) break;
+                c[2]++;
                 ShadowRequest sr;
                 NeeRequest nq;
                 const ShadeResult res = shade_hit<true, true>(sc, ps, h, d, sr, nee, &nq);
@@ -184,18 +190,22 @@ __global__ void __launch_bounds__(128) row_cost_kernel(SceneView sc, FrameParams
                 d = res.next_dir;
             }
         }
-        // a warp's pixels lie in at most two rows (width >= 32) — one atomic per row and warp
+        // a warp's pixels lie in at most two rows when the image is at least a warp wide: one atomic per row, warp and counter
         const uint32_t y0 = __shfl_sync(0xFFFFFFFFu, y, 0);
-        uint32_t a = (px < n_px && y == y0) ? extra : 0u, b = (px < n_px && y != y0) ? extra : 0u;
+        const bool in0 = px < n_px && y == y0, in1 = px < n_px && y != y0;
 #pragma unroll
-        for (int o2 = 16; o2 > 0; o2 >>= 1) { a += __shfl_xor_sync(0xFFFFFFFFu, a, o2); b += __shfl_xor_sync(0xFFFFFFFFu, b, o2); }
-        if (fp.width >= 32u) {
-            if ((threadIdx.x & 31u) == 0u) {
-                if (a) atomicAdd(&row_cost[y0], a);
-                if (b && y0 + 1u < fp.height) atomicAdd(&row_cost[y0 + 1u], b);
+        for (int k = 0; k < 4; k++) {
+            uint32_t a = in0 ? c[k] : 0u, b = in1 ? c[k] : 0u;
+#pragma unroll
+            for (int o2 = 16; o2 > 0; o2 >>= 1) { a += __shfl_xor_sync(0xFFFFFFFFu, a, o2); b += __shfl_xor_sync(0xFFFFFFFFu, b, o2); }
+            if (fp.width >= 32u) {
+                if ((threadIdx.x & 31u) == 0u) {
+                    if (a) atomicAdd(&row_cost[4u * y0 + k], a);
+                    if (b && y0 + 1u < fp.height) atomicAdd(&row_cost[4u * (y0 + 1u) + k], b);
+                }
+            } else if (px < n_px && c[k]) {
+                atomicAdd(&row_cost[4u * y + k], c[k]);
             }
-        } else if (px < n_px && extra) {
-            atomicAdd(&row_cost[y], extra);
         }
     }
 }

@@ -152,7 +152,7 @@ int launch_frame_wavefront(const SceneView& sc, const FrameParams& fp, FrameReso
 int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
                             std::string& err);
 // strip-cost calibration (RT_BALANCE_COST): one path per pixel of the FULL frame `fp` describes (strip_count must be 1 in
-// it), no image; row_cost[y] += closest-hit rays beyond the primary one that the paths of row y traced
+// it), no image; row_cost[4 y + k] += {primary traversal work, continuation traversal work, hits, continuation rays} of row y
 int launch_row_cost(const SceneView& sc, const FrameParams& fp, uint32_t* d_row_cost, int num_sms, cudaStream_t stream, std::string& err);
 int launch_trace_rays(const SceneView& sc, const float* d_rays, uint32_t n, bool any, const uint32_t* d_ignore,
                       float* d_tuv, uint32_t* d_id, DevCounters* counters, int num_sms, cudaStream_t stream, std::string& err);

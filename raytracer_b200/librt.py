@@ -31,9 +31,9 @@ EXPORTS = (
     "rt_create", "rt_destroy", "rt_default_config", "rt_last_error", "rt_version", "rt_build_scene",
     "rt_scene_info_get", "rt_update_material", "rt_update_object_transform", "rt_update_object_material",
     "rt_update_object_mesh", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_trace_frames_sliced", "rt_synchronize", "rt_readback",
-    "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_get_strip_owners", "rt_rebalance", "rt_trace_gbuffer", "rt_readback_gbuffer",
+    "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_get_strip_owners", "rt_rebalance", "rt_measure_row_costs", "rt_set_strip_owners", "rt_trace_gbuffer", "rt_readback_gbuffer",
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
-    "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_set_profiling", "rt_get_kernel_profile",
+    "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_event_elapsed_per_device", "rt_set_profiling", "rt_get_kernel_profile",
     "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh",
 )
 
@@ -131,6 +131,8 @@ def load() -> C.CDLL:
     L.rt_upload_accum.argtypes = [vp, vp, C.c_size_t]
     L.rt_get_strip_owners.argtypes = [vp, vp, u32, C.POINTER(u32)]
     L.rt_rebalance.argtypes = [vp]
+    L.rt_measure_row_costs.argtypes = [vp, f32p, u32, vp, u32]
+    L.rt_set_strip_owners.argtypes = [vp, vp, u32]
     L.rt_trace_gbuffer.argtypes = [vp, f32p]
     L.rt_readback_gbuffer.argtypes = [vp, vp, vp, vp, vp, vp]
     L.rt_default_restir_params.argtypes = [C.POINTER(RtRestirParams)]
@@ -142,6 +144,7 @@ def load() -> C.CDLL:
     L.rt_last_trace_ms.argtypes = [vp, C.POINTER(C.c_float)]
     L.rt_event_record.argtypes = [vp, C.c_int]
     L.rt_event_elapsed_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.rt_event_elapsed_per_device.argtypes = [vp, vp, u32, C.POINTER(u32)]
     L.rt_set_profiling.argtypes = [vp, C.c_int]
     L.rt_get_kernel_profile.argtypes = [vp, C.POINTER(RtKernelProfile)]
     L.rt_trace_rays_closest.argtypes = [vp, f32p, u32, vp, vp]
@@ -294,6 +297,18 @@ class Context:
         self._check(self.L.rt_get_strip_owners(self.h, _p(out), n.value, C.byref(n)))
         return out
 
+    def measure_row_costs(self, camera_ubo, frame_number=0) -> np.ndarray:
+        """(H, 4) counters of the strip-cost calibration pass: primary work, continuation work, hits, continuation rays."""
+        cam = np.ascontiguousarray(camera_ubo, np.float32).reshape(64)
+        out = np.zeros((self.height, 4), np.uint32)
+        self._check(self.L.rt_measure_row_costs(self.h, _p(cam), frame_number, _p(out), self.height))
+        return out
+
+    def set_strip_owners(self, owners):
+        """Install a host-decided strip -> rank table; restart the accumulation (frame 0) afterwards."""
+        o = np.ascontiguousarray(owners, np.uint32)
+        self._check(self.L.rt_set_strip_owners(self.h, _p(o), len(o)))
+
     def rebalance(self):
         self._check(self.L.rt_rebalance(self.h))
 
@@ -341,6 +356,13 @@ class Context:
         ms = C.c_float(0)
         self._check(self.L.rt_event_elapsed_ms(self.h, C.byref(ms)))
         return ms.value
+
+    def event_elapsed_per_device(self) -> list:
+        n = C.c_uint32()
+        self._check(self.L.rt_event_elapsed_per_device(self.h, None, 0, C.byref(n)))
+        out = np.zeros(n.value, np.float32)
+        self._check(self.L.rt_event_elapsed_per_device(self.h, _p(out), n.value, C.byref(n)))
+        return [float(x) for x in out]
 
     def set_profiling(self, enable: bool):
         self._check(self.L.rt_set_profiling(self.h, int(enable)))

@@ -170,3 +170,78 @@ class SharedHostImage:
         except BufferError:
             pass  # a numpy view is still alive somewhere; the mapping goes with it
         self._f.close()
+
+
+# the cost model of RT_BALANCE_COST (rt_api.cu: RT_BALANCE_W_*): tenths of a picosecond per pixel, per unit of primary /
+# continuation traversal work, per closest-hit invocation (tools/fit_balance.py)
+MODEL_WEIGHTS = (267.0, 9.0, 12.0, 1572.0)
+
+
+class StripBalancer:
+    """Strip -> rank assignment from MEASURED step times (host logic; the library only installs the table:
+    `rt_set_strip_owners`).  The cost model of RT_BALANCE_COST predicts a rank's time to ~1 %, but single strips are off by
+    more, and at N = 8 the slowest rank sets the step.  Feedback closes the gap: after a step, the cost estimates of every
+    rank's strips are scaled so that they add up to the time the rank really took, and the strips are dealt again —
+    longest processing time first, every rank keeping the NUMBER of strips the round-robin deal gives it (so no buffer
+    changes size), the partial last strip staying with its round-robin owner.  Deterministic: ranks that feed it the same
+    times (one all_gather) derive the same table without further talk.  The image is bit-identical under any table."""
+
+    def __init__(self, height: int, world: int, strip_rows: int = DEFAULT_STRIP_ROWS, owners=None, costs=None):
+        self.world, self.strip_rows = int(world), int(strip_rows)
+        self.n_strips = (height + strip_rows - 1) // strip_rows
+        self.n_full = height // strip_rows
+        rr = np.arange(self.n_strips) % self.world
+        self.owners = np.asarray(owners if owners is not None else rr, np.int64).copy()
+        self.capacity = [int((rr[: self.n_full] == r).sum()) for r in range(self.world)]
+        self.cost = np.asarray(costs, np.float64).copy() if costs is not None else np.ones(self.n_strips, np.float64)
+        self.best = (float("inf"), self.owners.copy())
+
+    def deal(self) -> np.ndarray:
+        """Capacity-constrained LPT over the current cost estimates (ties: lower strip, lower rank)."""
+        order = sorted(range(self.n_full), key=lambda s: (-self.cost[s], s))
+        load, cap = [0.0] * self.world, list(self.capacity)
+        owners = np.zeros(self.n_strips, np.int64)
+        for s in order:
+            r = min((r for r in range(self.world) if cap[r]), key=lambda r: (load[r], r))
+            owners[s] = r
+            load[r] += self.cost[s]
+            cap[r] -= 1
+        if self.n_strips > self.n_full:
+            owners[self.n_full] = self.n_full % self.world
+        return owners
+
+    def update(self, rank_ms) -> np.ndarray:
+        """rank_ms[r] = the step time rank r measured under the current table.  Returns the next table to try: the estimates
+        of each rank's strips are scaled to add up to its measured time, then the slowest rank trades ONE strip with the
+        fastest, the second slowest with the second fastest, ... — the pair of strips whose estimated cost difference
+        comes closest to half the time difference.  A trade moves a fraction of one strip's cost, so an error of the
+        per-strip estimates costs a fraction of a per cent of a rank's time, not a re-deal of everything."""
+        t = np.asarray(rank_ms, np.float64)
+        ratio = float(t.max() / t.mean())
+        if ratio < self.best[0]:
+            self.best = (ratio, self.owners.copy())
+        for r in range(self.world):
+            mine = np.nonzero(self.owners[: self.n_full] == r)[0]
+            est = self.cost[mine].sum()
+            if len(mine) and est > 0 and t[r] > 0:
+                self.cost[mine] *= t[r] / est
+        order = np.argsort(-t, kind="stable")
+        owners = self.owners.copy()
+        for k in range(self.world // 2):
+            slow, fast = int(order[k]), int(order[self.world - 1 - k])
+            want = 0.5 * (t[slow] - t[fast])
+            if want <= 0.001 * t.mean():
+                break
+            a = np.nonzero(owners[: self.n_full] == slow)[0]
+            b = np.nonzero(owners[: self.n_full] == fast)[0]
+            if not len(a) or not len(b):
+                continue
+            diff = self.cost[a][:, None] - self.cost[b][None, :]     # what the slow rank sheds by trading a[i] for b[j]
+            i, j = np.unravel_index(np.argmin(np.abs(diff - want)), diff.shape)
+            if 0.0 < diff[i, j] < 2.0 * want:
+                owners[a[i]], owners[b[j]] = fast, slow
+        self.owners = owners
+        return self.owners
+
+    def best_owners(self) -> np.ndarray:
+        return self.best[1]

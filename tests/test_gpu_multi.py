@@ -200,3 +200,48 @@ def test_two_devices_through_the_c_abi_only():
             assert dev["extend_rays"] == cnt["extend_rays"] and dev["hits"] == cnt["hits"]
         finally:
             c.close()
+
+
+def test_host_decided_strip_table_is_bit_identical_and_validated():
+    """rt_set_strip_owners: any table that keeps every rank's round-robin strip count gives the single-context image (the
+    multi-GPU context and strip contexts alike); a table that changes a rank's row count is refused."""
+    scene = fixture_scene("cornell_pbr")
+    W, H, n, world = 96, 84, 3, 3   # 10 full strips + a partial one
+    cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+    want, _, _ = _single(scene, cam, W, H, n)
+    table = np.array([2, 0, 1, 0, 1, 2, 0, 2, 1, 0, 1], np.uint32)  # counts 4 / 3 / 3 as round robin; strip 10 (partial) stays with rank 1
+    c = librt.Context(devices=[0, 0, 0], frames_in_flight=n)
+    try:
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(cam.ubo(), CLEAR, 0, n)
+        c.set_strip_owners(table)
+        assert np.array_equal(c.strip_owners(), table)
+        c.trace_frames(cam.ubo(), CLEAR, 0, n)   # the accumulation restarts: rows changed hands
+        assert np.array_equal(c.readback().view(np.uint32), want.view(np.uint32))
+        ms = c.event_elapsed_per_device() if False else None
+        bad = table.copy()
+        bad[0] = 0                                # rank 0 would own 5 strips
+        with pytest.raises(librt.RtError):
+            c.set_strip_owners(bad)
+        with pytest.raises(librt.RtError):
+            c.set_strip_owners(table[:-1])
+        cost = c.measure_row_costs(cam.ubo(), 0)
+        assert cost.shape == (H, 4) and cost[:, 0].min() > 0 and cost[:, 2].max() <= 3 * W
+    finally:
+        c.close()
+    got = np.zeros_like(want)
+    for rank in range(world):
+        s = librt.Context(device=0, strip_index=rank, strip_count=world, frames_in_flight=n)
+        try:
+            s.build_scene(scene)
+            s.resize(W, H)
+            s.set_strip_owners(table)
+            s.event_record(0)
+            s.trace_frames(cam.ubo(), CLEAR, 0, n)
+            s.event_record(1)
+            assert len(s.event_elapsed_per_device()) == 1
+            s.readback(got)
+        finally:
+            s.close()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))

@@ -211,3 +211,25 @@ def test_accumulation_controller_mirrors_the_reference():
     r.set_accumulation_limit(107)
     r.render_frames(10)                                        # clipped at the limit
     assert [c for c in rec.calls if c[0] == "trace"] == [("trace", 105, 2)]
+
+
+def test_strip_balancer_keeps_the_partition_and_converges():
+    """multi_gpu.StripBalancer on a synthetic cost field with 8 % per-strip model error: every table is a partition with
+    the round-robin strip counts, the partial last strip never moves, and the measured slowest/mean ratio drops."""
+    H, world, sr = 1084, 8, 8   # 135 full strips + a partial one
+    rng = np.random.default_rng(3)
+    n_strips, n_full = (H + sr - 1) // sr, H // sr
+    true = 1.0 + 0.5 * np.sin(np.arange(n_strips) / 7.0) + 0.2 * rng.random(n_strips)
+    model = true * (1.0 + 0.08 * rng.standard_normal(n_strips))
+    b = multi_gpu.StripBalancer(H, world, sr, costs=model)
+    rr = np.arange(n_strips) % world
+    assert np.array_equal(b.owners, rr)
+    ratios = []
+    for _ in range(8):
+        t = np.array([true[b.owners == r].sum() for r in range(world)])
+        ratios.append(t.max() / t.mean())
+        o = b.update(t)
+        assert [int((o[:n_full] == r).sum()) for r in range(world)] == [int((rr[:n_full] == r).sum()) for r in range(world)]
+        assert o[n_full] == n_full % world
+    assert b.best[0] < 1.012 < ratios[0]
+    assert [int((b.best_owners() == r).sum()) for r in range(world)] == [int((rr == r).sum()) for r in range(world)]
