@@ -51,6 +51,8 @@ def lib():
         L.orc_gbuffer.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_direct_reference.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p]
+        L.orc_direct_reference_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                                C.c_int, C.c_int, C.c_void_p]
         L.orc_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
         L.orc_tea.argtypes = [C.c_uint32, C.c_uint32]
@@ -161,12 +163,13 @@ class OracleScene:
                            _ptr(out["position_metal"]), _ptr(out["emission"]), _ptr(out["output"]))
         return out
 
-    def direct_reference(self, cam_ubo, clear, W, H, samples_per_axis=4, use_bvh=True):
-        """Brute-force direct lighting of the primary hits (ground truth of the ReSTIR DI tests)."""
+    def direct_reference(self, cam_ubo, clear, W, H, samples_per_axis=4, use_bvh=True, y0=0, y1=None):
+        """Brute-force direct lighting of the primary hits (ground truth of the ReSTIR DI tests); rows y0 .. y1-1."""
         cam = np.ascontiguousarray(cam_ubo, np.float32)
         clr = np.ascontiguousarray(clear, np.float32)
         img = np.zeros((H, W, 4), np.float32)
-        self.L.orc_direct_reference(self.h, _ptr(cam), _ptr(clr), W, H, int(use_bvh), int(samples_per_axis), _ptr(img))
+        self.L.orc_direct_reference_rows(self.h, _ptr(cam), _ptr(clr), W, H, y0, H if y1 is None else y1, int(use_bvh),
+                                         int(samples_per_axis), _ptr(img))
         return img
 
     def trace_rays(self, rays, mode="bvh", any_hit=False, ignore_inst=None, counters=None):

@@ -106,6 +106,15 @@ int orc_direct_reference(void* h, const float* cam64, const float* clear3, uint3
     return 0;
 }
 
+// the same on the rows y0 .. y1-1 only (full-size image; the other rows are left alone): full-resolution checks of a band
+int orc_direct_reference_rows(void* h, const float* cam64, const float* clear3, uint32_t W, uint32_t H, uint32_t y0, uint32_t y1,
+                              int use_bvh, int spt, float* image_rgba) {
+    Scene* s = (Scene*)h;
+    if (use_bvh && !s->has_bvh) build_bvh8(*s);
+    direct_reference_rows(*s, use_bvh, cam64, clear3, W, H, y0, y1 < H ? y1 : H, spt, image_rgba);
+    return 0;
+}
+
 // rays: n x 8 floats (ox,oy,oz,tmin, dx,dy,dz,tmax). mode: 0 brute closest, 1 bvh closest, 2 brute any, 3 bvh any.
 // out_tuv: n x 3 (closest modes), out_id: flat id or 0xFFFFFFFF (closest); 1/0 occluded flag (any modes).
 int orc_trace_rays(void* h, const float* rays, uint32_t n, int mode, const uint32_t* ignore_inst, float* out_tuv,

@@ -540,6 +540,7 @@ static int install_owners(rt_ctx* ctx, const uint32_t* owners, uint32_t n_strips
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->rs_history = false;   // per-pixel histories belong to the rows that were here before
     ctx->has_gbuffer = false;
+    ctx->band_epoch++;
     return RT_OK;
 }
 
@@ -595,6 +596,7 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     // back to the round-robin assignment; with RT_BALANCE_COST the next frame-0 trace measures the strips of the new target
     ctx->band_strip.clear();
     ctx->strip_owner.clear();
+    ctx->band_epoch++;
     ctx->balance_pending = ctx->cfg.strip_balance == RT_BALANCE_COST && ctx->cfg.strip_count > 1;
     const size_t n = (size_t)ctx->local_rows * width;
     RT_CUDA_TRY(ctx->image.alloc(n));

@@ -230,6 +230,9 @@ struct rt_ctx {
     // ReSTIR DI (rt_restir.cu): primary surfaces, this frame's reservoirs, the history
     rt::DevBuf<float4> rs_surf;
     rt::DevBuf<rt_reservoir> rs_cur, rs_hist[2];
+    rt::DevBuf<uint32_t> rs_rows;   // global rows passes 1 and 2 cover: own rows + halo (strip partitions only)
+    uint32_t rs_n_rows = 0, rs_rows_halo = 0, rs_rows_epoch = 0;
+    uint32_t band_epoch = 1;        // bumped whenever the strip table or the target changes
     int rs_flip = 0;
     bool rs_history = false;   // rs_hist[rs_flip] holds last frame's reservoirs for rs_cam
     float rs_cam[64] = {0};

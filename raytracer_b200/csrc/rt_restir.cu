@@ -48,12 +48,19 @@ __device__ __forceinline__ RSurf load_surf(const float4* s, uint32_t px) {
 __device__ __forceinline__ float luminance(vec3 c) { return dot3(c, mk3(0.2126f, 0.7152f, 0.0722f)); }
 
 // ---- pass 1: primary visibility (restir.rgen:43-59 + restir.rchit:36-59 / restir.rmiss:18-20) ---------------
-__global__ void __launch_bounds__(128) restir_surface_kernel(SceneView sc, FrameParams fp, float4* surf, DevCounters* counters) {
-    const uint32_t n_px = fp.local_rows * fp.width;
+// Passes 1 and 2 run over a LIST of global image rows (rows == nullptr: all of them): the rows this context owns plus the
+// halo of ceil(spatial_radius) rows around them, so that pass 3 finds every neighbour it may pick — computed here, not fetched
+// from the rank that owns it ("recompute G-buffer + candidates for the halo rows locally (no comms)").  Every value
+// of a pixel depends on its GLOBAL coordinates only, so two ranks that both process a row get the same bits, and the image
+// does not depend on how many ranks share the frame.  All per-pixel arrays of this file are indexed by global pixel.
+__global__ void __launch_bounds__(128) restir_surface_kernel(SceneView sc, FrameParams fp, const uint32_t* rows, uint32_t n_rows,
+                                                             float4* surf, DevCounters* counters) {
+    const uint32_t n_px = n_rows * fp.width;
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
-    for (uint32_t px = blockIdx.x * blockDim.x + threadIdx.x; px < n_px; px += gridDim.x * blockDim.x) {
-        const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
-        const uint32_t y = strip_global_row(fp, lrow);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_px; i += gridDim.x * blockDim.x) {
+        const uint32_t r = i / fp.width, x = i - r * fp.width;
+        const uint32_t y = rows ? __ldg(rows + r) : r;
+        const uint32_t px = y * fp.width + x;
         vec3 o, d;
         camera_ray(fp, (float)x, (float)y, false, &o, &d);  // pixel corner, direction not re-normalised
         c_rays++;
@@ -185,16 +192,17 @@ __device__ __forceinline__ float target_of(const SceneView& sc, const SurfShade&
 
 // ---- pass 2: initial candidates (RIS) + temporal reuse ---------------------------------------------------
 __global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, FrameParams fp, rt_restir_params prm,
-                                                                const float4* surf, const rt_reservoir* prev,
-                                                                rt_reservoir* out, DevCounters* counters) {
-    const uint32_t n_px = fp.local_rows * fp.width;
+                                                                const uint32_t* rows, uint32_t n_rows, const float4* surf,
+                                                                const rt_reservoir* prev, rt_reservoir* out, DevCounters* counters) {
+    const uint32_t n_px = n_rows * fp.width;
     uint32_t c_nee = 0;
-    for (uint32_t px = blockIdx.x * blockDim.x + threadIdx.x; px < n_px; px += gridDim.x * blockDim.x) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_px; i += gridDim.x * blockDim.x) {
+        const uint32_t r = i / fp.width, x = i - r * fp.width;
+        const uint32_t y = rows ? __ldg(rows + r) : r;
+        const uint32_t px = y * fp.width + x;
         const SurfShade ss = prepare_surface(sc, surf, px);
         rt_reservoir res = empty_reservoir();
         if (ss.s.inst == 0xFFFFFFFFu) { out[px] = res; continue; }
-        const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
-        const uint32_t y = strip_global_row(fp, lrow);
         uint32_t seed = tea16((y * fp.width + x) ^ 0x52455354u, fp.frame);  // 'REST': a stream of its own
         const uint32_t L = sc.n_lights < RT_MAXLIGHTS ? sc.n_lights : RT_MAXLIGHTS;
         float total = 0.0f;
@@ -274,13 +282,6 @@ __global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, Fr
 
 // ---- pass 3: spatial reuse + shading + accumulation -----------------------------------------------------------
 #define RT_RESTIR_MAX_NEIGHBOURS 8
-// global row -> row of this context's compact image, or -1 when another strip owns it
-__device__ __forceinline__ int local_row_of(const FrameParams& fp, int gy) {
-    if (gy < 0 || gy >= (int)fp.height) return -1;
-    const uint32_t band = (uint32_t)gy / fp.strip_rows;
-    if (band % fp.strip_count != fp.strip_index) return -1;
-    return (int)((band / fp.strip_count) * fp.strip_rows + (uint32_t)gy % fp.strip_rows);
-}
 
 #ifndef RT_RESOLVE_MIN_BLOCKS
 #define RT_RESOLVE_MIN_BLOCKS 4  /* 128 registers, no spills: 2.015 -> 1.886 ms/frame (3 blocks x 152 registers before) */
@@ -291,7 +292,11 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
     const uint32_t n_px = fp.local_rows * fp.width;
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     const vec3 clearc = mk3(fp.clear[0], fp.clear[1], fp.clear[2]);
-    for (uint32_t px = blockIdx.x * blockDim.x + threadIdx.x; px < n_px; px += gridDim.x * blockDim.x) {
+    // this context's own rows only; lpx indexes its compact image, px (global) everything else
+    for (uint32_t lpx = blockIdx.x * blockDim.x + threadIdx.x; lpx < n_px; lpx += gridDim.x * blockDim.x) {
+        const uint32_t lrow = lpx / fp.width, x = lpx - lrow * fp.width;
+        const uint32_t y = strip_global_row(fp, lrow);
+        const uint32_t px = y * fp.width + x;
         const SurfShade ss = prepare_surface(sc, surf, px);
         vec3 color = splat3(0.0f);
         rt_reservoir res = in[px];
@@ -299,8 +304,6 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
             color = clearc;  // restir.rmiss: nothing hit -> background
             res = empty_reservoir();
         } else {
-            const uint32_t lrow = px / fp.width, x = px - lrow * fp.width;
-            const uint32_t y = strip_global_row(fp, lrow);
             uint32_t seed = tea16((y * fp.width + x) ^ 0x53504154u, fp.frame);  // 'SPAT'
             LightPoint lpw;  // the surviving sample's light point, once it has been reconstructed
             bool have_lpw = false;
@@ -318,9 +321,9 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
                     sincos_rt(RT_TWO_PI * ua, &sn, &cs);
                     const float rad = prm.spatial_radius * sqrtf(ur);
                     const int qx = (int)x + (int)rintf(rad * cs), qy = (int)y + (int)rintf(rad * sn);
-                    const int qrow = local_row_of(fp, qy);
-                    if (qx < 0 || qx >= (int)fp.width || qrow < 0) continue;
-                    const uint32_t qpx = (uint32_t)qrow * fp.width + (uint32_t)qx;
+                    // |qy - y| <= ceil(spatial_radius): inside the halo passes 1 and 2 covered, whoever owns the row
+                    if (qx < 0 || qx >= (int)fp.width || qy < 0 || qy >= (int)fp.height) continue;
+                    const uint32_t qpx = (uint32_t)qy * fp.width + (uint32_t)qx;
                     if (qpx == px) continue;
                     const RSurf qs = load_surf(surf, qpx);
                     // reuse only across similar surfaces: normals within ~25 degrees, depths within 10 %
@@ -373,7 +376,7 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
             if (ss.mat.emission_power > 0.0f) color = add3(color, scale3(ss.mat.emission_color, ss.mat.emission_power));
         }
         out[px] = res;
-        image[px] = accumulate_pixel(fp.frame ? image[px] : make_float4(0.f, 0.f, 0.f, 0.f), color, fp.clamp, fp.frame);
+        image[lpx] = accumulate_pixel(fp.frame ? image[lpx] : make_float4(0.f, 0.f, 0.f, 0.f), color, fp.clamp, fp.frame);
     }
     if (counters) {
         unsigned long long* dst[5] = {&counters->shadow_rays, &counters->nodes, &counters->tris, &counters->shadow_nodes, &counters->shadow_tris};
@@ -427,12 +430,41 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     if (rc != RT_OK) return rc;
     rc = rt_require_target(ctx);
     if (rc != RT_OK) return rc;
-    const size_t n = (size_t)ctx->local_rows * ctx->width;
+    if (ctx->local_rows == 0) return RT_OK;
+    const size_t n = (size_t)ctx->height * ctx->width;  // every per-pixel array is indexed by GLOBAL pixel (halo rows included)
     RT_CUDA_TRY(ctx->rs_surf.ensure(3 * n));
     RT_CUDA_TRY(ctx->rs_cur.ensure(n));
     RT_CUDA_TRY(ctx->rs_hist[0].ensure(n));
     RT_CUDA_TRY(ctx->rs_hist[1].ensure(n));
-    if (n == 0) return RT_OK;
+    // the rows of passes 1 and 2: own rows + halo.  A strip partition with few ranks and 8-row strips makes that the whole
+    // frame (radius 16 >= the gap between a rank's strips up to N = 5); beyond, it is 5 x the own rows at most.
+    const uint32_t halo = (prm.flags & RT_RESTIR_SPATIAL) && prm.spatial_samples ? (uint32_t)ceilf(prm.spatial_radius) : 0u;
+    uint32_t n_rows = ctx->height;
+    const uint32_t* d_rows = nullptr;
+    if (ctx->cfg.strip_count > 1) {
+        if (ctx->rs_rows_halo != halo || ctx->rs_rows_epoch != ctx->band_epoch || ctx->rs_rows.n == 0) {
+            std::vector<uint8_t> mark(ctx->height, 0);
+            const uint32_t sr = ctx->cfg.strip_rows;
+            for (uint32_t lrow = 0; lrow < ctx->local_rows; lrow++) {
+                const uint32_t band = lrow / sr;
+                const uint32_t strip = ctx->band_strip.empty() ? band * ctx->cfg.strip_count + ctx->cfg.strip_index : ctx->band_strip[band];
+                const uint32_t y = strip * sr + lrow % sr;
+                const uint32_t y0 = y > halo ? y - halo : 0u, y1 = std::min(ctx->height - 1u, y + halo);
+                for (uint32_t q = y0; q <= y1; q++) mark[q] = 1;
+            }
+            std::vector<uint32_t> rows;
+            for (uint32_t y = 0; y < ctx->height; y++) if (mark[y]) rows.push_back(y);
+            RT_CUDA_TRY(ctx->rs_rows.ensure(rows.size()));
+            RT_CUDA_TRY(cudaMemcpyAsync(ctx->rs_rows.p, rows.data(), rows.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+            RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+            if (halo > ctx->rs_rows_halo || ctx->rs_rows_epoch != ctx->band_epoch) ctx->rs_history = false;  // rows without a history joined
+            ctx->rs_n_rows = (uint32_t)rows.size();
+            ctx->rs_rows_halo = halo;
+            ctx->rs_rows_epoch = ctx->band_epoch;
+        }
+        n_rows = ctx->rs_n_rows;
+        d_rows = ctx->rs_rows.p;
+    }
     // the history follows the camera, not the accumulation counter: frame 0 overwrites the image but may still reuse
     if (ctx->rs_history && memcmp(ctx->rs_cam, camera_ubo, sizeof(ctx->rs_cam)) != 0) ctx->rs_history = false;
     rt::FrameParams fp;
@@ -441,7 +473,8 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     rt::DevCounters* cnt = (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr;
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    const uint32_t grid = (uint32_t)std::min<size_t>((n + 127) / 128, (size_t)sms * 32);
+    const uint32_t grid = (uint32_t)std::min<size_t>(((size_t)n_rows * ctx->width + 127) / 128, (size_t)sms * 32);
+    const uint32_t grid3 = (uint32_t)std::min<size_t>(((size_t)ctx->local_rows * ctx->width + 127) / 128, (size_t)sms * 32);
     // History = the reservoirs after candidates + temporal reuse.  The spatially combined reservoirs are used for
     // shading only: feeding them back lets one lucky sample spread to its neighbours and return through the
     // temporal pass every frame (measured: fireflies persisting for the whole history length, mean +37 % after
@@ -449,9 +482,9 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     const rt_reservoir* prev = ctx->rs_history ? ctx->rs_hist[ctx->rs_flip].p : nullptr;
     rt_reservoir* temporal = ctx->rs_hist[ctx->rs_flip ^ 1].p;
     rt_begin_timing(ctx);
-    rt::restir_surface_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, ctx->rs_surf.p, cnt);
-    rt::restir_candidates_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, prm, ctx->rs_surf.p, prev, temporal, cnt);
-    rt::restir_resolve_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, prm, ctx->rs_surf.p, temporal, ctx->rs_cur.p, ctx->image.p, cnt);
+    rt::restir_surface_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, d_rows, n_rows, ctx->rs_surf.p, cnt);
+    rt::restir_candidates_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, prm, d_rows, n_rows, ctx->rs_surf.p, prev, temporal, cnt);
+    rt::restir_resolve_kernel<<<grid3, 128, 0, ctx->stream>>>(sc, fp, prm, ctx->rs_surf.p, temporal, ctx->rs_cur.p, ctx->image.p, cnt);
     rt_end_timing(ctx);
     RT_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
@@ -474,12 +507,13 @@ int rt_readback_reservoirs(rt_ctx* ctx, rt_reservoir* dst, size_t bytes) {
     if (!ctx->rs_history) { set_error("rt_readback_reservoirs: no ReSTIR frame traced"); return RT_ERR_NO_TARGET; }
     const size_t row = (size_t)ctx->width * sizeof(rt_reservoir);
     if (!dst || bytes < row * ctx->height) { set_error("rt_readback_reservoirs: destination too small"); return RT_ERR_INVALID_ARGUMENT; }
-    const rt_reservoir* src = ctx->rs_cur.p;
+    const rt_reservoir* src = ctx->rs_cur.p;  // indexed by global pixel: this context's own rows are the ones it resolved
     const uint32_t sr = ctx->cfg.strip_rows;
     for (uint32_t lrow = 0; lrow < ctx->local_rows; lrow += sr) {
         const uint32_t rows = std::min(sr, ctx->local_rows - lrow);
-        const uint32_t y = rt::strip_global_row(lrow, sr, ctx->cfg.strip_index, ctx->cfg.strip_count);
-        RT_CUDA_TRY(cudaMemcpyAsync((char*)dst + (size_t)y * row, (const char*)src + (size_t)lrow * row, rows * row,
+        const uint32_t band = lrow / sr;
+        const uint32_t y = (ctx->band_strip.empty() ? band * ctx->cfg.strip_count + ctx->cfg.strip_index : ctx->band_strip[band]) * sr;
+        RT_CUDA_TRY(cudaMemcpyAsync((char*)dst + (size_t)y * row, (const char*)src + (size_t)y * row, rows * row,
                                     cudaMemcpyDeviceToHost, ctx->stream));
     }
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
