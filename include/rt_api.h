@@ -164,7 +164,7 @@ typedef struct rt_scene_info {
     uint32_t n_objects;
     uint32_t n_materials;
     float build_ms;         /* device time of the last BVH build */
-    uint32_t reserved;
+    uint32_t refits;        /* box refits (rt_update_object_transform) since that build */
 } rt_scene_info;
 
 /* 32-byte reservoir, shaders/restir/restir_structs.glsl:1-12 */
@@ -212,6 +212,14 @@ RT_API int rt_update_material(rt_ctx* ctx, uint32_t material_index, const rt_mat
 RT_API int rt_update_object_transform(rt_ctx* ctx, uint32_t object_index, const float model[16]); /* :457-515 */
 RT_API int rt_update_object_material(rt_ctx* ctx, uint32_t object_index, uint32_t material_index); /* :517-560 */
 RT_API int rt_update_object_mesh(rt_ctx* ctx, uint32_t object_index, uint32_t mesh_index);       /* :562-601 */
+
+/* add / remove (gpu_scene.odin:430-455, dispatched at raytracing_renderer.odin:163-183).  rt_add_object instances a mesh the
+ * scene already holds.  rt_remove_material follows scene_delete_material (scene.odin:104-116): the LAST material moves into the
+ * freed slot, objects that used the removed one fall back to material 0.  rt_remove_object shifts later objects down by one. */
+RT_API int rt_add_material(rt_ctx* ctx, const rt_material* m, uint32_t* index_out);
+RT_API int rt_remove_material(rt_ctx* ctx, uint32_t material_index);
+RT_API int rt_add_object(rt_ctx* ctx, const rt_object* o, uint32_t* index_out);
+RT_API int rt_remove_object(rt_ctx* ctx, uint32_t object_index);
 
 /* ---- target: raytracing_renderer_on_resize (raytracing_renderer.odin:108-126) -------------- */
 RT_API int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height);

@@ -276,13 +276,48 @@ static int rebuild_bvh(rt_ctx* ctx) {
     return RT_OK;
 }
 
+// Object transforms changed and nothing else about the geometry: refit the boxes over the existing topology (the reference
+// updates its TLAS in place: acceleration_structure.odin:91 `mode = update ? .UPDATE : .BUILD`, gpu_scene.odin:457-483).
+// Closest hits do not depend on the tree, so the image is the one a rebuild gives; the tree is rebuilt when its
+// surface-area sum has grown past RT_REFIT_REBUILD_RATIO times the one it was built with.
+#ifndef RT_REFIT_REBUILD_RATIO
+#define RT_REFIT_REBUILD_RATIO 1.5
+#endif
+static int refit_bvh(rt_ctx* ctx, bool* rebuild) {
+    const uint32_t no = (uint32_t)ctx->objects.size();
+    std::vector<uint8_t> dirty(no, 0);
+    for (uint32_t i : ctx->refit_objects) if (i < no) dirty[i] = 1;
+    PoolScope pool_scope(ctx->pool);
+    PoolBuf<uint8_t> d_dirty;
+    RT_CUDA_TRY(d_dirty.alloc(no, ctx->stream));
+    RT_CUDA_TRY(cudaMemcpyAsync(d_dirty.p, dirty.data(), no, cudaMemcpyHostToDevice, ctx->stream));
+    BuildInput in;
+    in.d_objects = ctx->d_objects.p;
+    in.d_tri_offsets = ctx->d_tri_offsets.p;
+    in.d_vertices = ctx->d_vertices.p;
+    in.d_indices = ctx->d_indices.p;
+    in.n_objects = no;
+    in.n_tris = ctx->n_tris;
+    std::string err;
+    double sa_now = 0.0;
+    const int rc = refit_bvh8(in, ctx->bvh, d_dirty.p, &sa_now, ctx->stream, err);  // synchronises: `dirty` may go out of scope
+    if (rc != RT_OK) { set_error("refit: " + err); return rc; }
+    *rebuild = ctx->bvh.sa_build > 0.0 && sa_now > RT_REFIT_REBUILD_RATIO * ctx->bvh.sa_build;
+    return RT_OK;
+}
+
 int rt_flush_scene(rt_ctx* ctx) {
     if (!ctx->has_scene) { set_error("no scene: call rt_build_scene first"); return RT_ERR_NO_SCENE; }
     if (ctx->tables_dirty || ctx->geometry_dirty) {
-        const bool geo = ctx->geometry_dirty;
+        bool geo = ctx->geometry_dirty;
         ctx->rs_history = false;  // reservoirs refer to the old light tables
         int rc = upload_tables(ctx);
         if (rc != RT_OK) return rc;
+        if (!geo && !ctx->refit_objects.empty() && ctx->n_tris != 0) {
+            rc = refit_bvh(ctx, &geo);
+            if (rc != RT_OK) return rc;
+        }
+        ctx->refit_objects.clear();
         if (geo) { rc = rebuild_bvh(ctx); if (rc != RT_OK) return rc; }
     }
     return RT_OK;
@@ -380,6 +415,7 @@ int rt_scene_info_get(rt_ctx* ctx, rt_scene_info* out) {
     out->n_objects = (uint32_t)ctx->objects.size();
     out->n_materials = (uint32_t)ctx->materials.size();
     out->build_ms = ctx->bvh.build_ms;
+    out->refits = ctx->bvh.refits;
     return RT_OK;
 }
 
@@ -402,7 +438,7 @@ int rt_update_object_transform(rt_ctx* ctx, uint32_t object_index, const float m
     if (!model || object_index >= ctx->objects.size()) { set_error("rt_update_object_transform: bad index"); return RT_ERR_INDEX_RANGE; }
     memcpy(ctx->objects[object_index].model, model, 64);
     ctx->tables_dirty = true;
-    ctx->geometry_dirty = true;
+    ctx->refit_objects.push_back(object_index);  // boxes are refitted at the next flush; no rebuild unless the tree degrades
     return RT_OK;
 }
 
@@ -425,6 +461,97 @@ int rt_update_object_material(rt_ctx* ctx, uint32_t object_index, uint32_t mater
     }
     ctx->light_index[object_index] = li;
     ctx->tables_dirty = true;
+    return RT_OK;
+}
+
+// ---- add / remove: gpu_scene_add_object / remove_object / add_material / remove_material (gpu_scene.odin:430-455), which the
+// renderer dispatches on Object_Added / Object_Removed / Material_Added / Material_Removed (raytracing_renderer.odin:163-183).
+// The reference recompiles the object / light / material tables from its host scene; here the host scene lives behind the ABI
+// (the copies rt_build_scene made), so the calls carry the change itself.  Meshes are not re-uploaded: an added object
+// instances a mesh the scene already holds (scene.odin has no change event for meshes either).
+int rt_add_material(rt_ctx* ctx, const rt_material* m, uint32_t* index_out) {
+    CTX_CHECK(ctx);
+    if (!ctx->children.empty()) {
+        for (rt_ctx* c : ctx->children) {
+            const int rc = rt_add_material(c, m, index_out);
+            if (rc != RT_OK) { ctx->error = c->error; return rc; }
+        }
+        return RT_OK;
+    }
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    if (!m) { set_error("rt_add_material: null material"); return RT_ERR_INVALID_ARGUMENT; }
+    ctx->materials.push_back(*m);  // scene_add_material: append (scene.odin:95-98)
+    if (index_out) *index_out = (uint32_t)ctx->materials.size() - 1u;
+    ctx->tables_dirty = true;
+    return RT_OK;
+}
+
+// scene_delete_material (scene.odin:104-116): unordered_remove — the LAST material moves into the freed slot — and every
+// object that used the removed material falls back to material 0 (through scene_update_object_material, hence its
+// light_index is recomputed as in rt_update_object_material).  Objects that used the moved material follow it to its new
+// index (the reference leaves their index pointing past the end of the table: defined here).
+int rt_remove_material(rt_ctx* ctx, uint32_t material_index) {
+    CTX_CHECK(ctx);
+    FANOUT(ctx, rt_remove_material(c, material_index));
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    const uint32_t n = (uint32_t)ctx->materials.size();
+    if (material_index >= n) { set_error("rt_remove_material: bad index"); return RT_ERR_INDEX_RANGE; }
+    if (n == 1) { set_error("rt_remove_material: the scene's last material cannot go (objects fall back to material 0)"); return RT_ERR_INVALID_ARGUMENT; }
+    const uint32_t last = n - 1u;
+    ctx->materials[material_index] = ctx->materials[last];
+    ctx->materials.pop_back();
+    std::vector<uint32_t> fell_back;
+    for (uint32_t i = 0; i < ctx->objects.size(); i++) {
+        uint32_t& mi = ctx->objects[i].material_index;
+        if (mi == material_index) { mi = 0u; fell_back.push_back(i); }
+        else if (mi == last) mi = material_index;
+    }
+    ctx->tables_dirty = true;
+    for (uint32_t i : fell_back) {
+        const int rc = rt_update_object_material(ctx, i, 0u);
+        if (rc != RT_OK) return rc;
+    }
+    return RT_OK;
+}
+
+// scene_add_object (scene.odin:165-194): append an instance of an existing mesh.  Its triangles enter the BVH (rebuild);
+// light_index starts at 0 like every baked object (gpu_scene.odin:333-336).
+int rt_add_object(rt_ctx* ctx, const rt_object* o, uint32_t* index_out) {
+    CTX_CHECK(ctx);
+    if (!ctx->children.empty()) {
+        for (rt_ctx* c : ctx->children) {
+            const int rc = rt_add_object(c, o, index_out);
+            if (rc != RT_OK) { ctx->error = c->error; return rc; }
+        }
+        return RT_OK;
+    }
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    if (!o) { set_error("rt_add_object: null object"); return RT_ERR_INVALID_ARGUMENT; }
+    if (o->mesh_index >= ctx->meshes.size()) { set_error("rt_add_object: Invalid mesh index"); return RT_ERR_INDEX_RANGE; }          // scene.odin:176
+    if (o->material_index >= ctx->materials.size()) { set_error("rt_add_object: Invalid material index"); return RT_ERR_INDEX_RANGE; }  // scene.odin:177
+    uint64_t total = ctx->meshes[o->mesh_index].idx.size() / 3;
+    for (const rt_object& q : ctx->objects) total += ctx->meshes[q.mesh_index].idx.size() / 3;
+    if (total >= 0x7FFFFFFFull) { set_error("rt_add_object: scene too large for 32-bit triangle ids"); return RT_ERR_INVALID_ARGUMENT; }
+    ctx->objects.push_back(*o);
+    ctx->light_index.push_back(0u);
+    if (index_out) *index_out = (uint32_t)ctx->objects.size() - 1u;
+    ctx->tables_dirty = true;
+    ctx->geometry_dirty = true;
+    return RT_OK;
+}
+
+// Object_Removed: the objects behind it move down one index (instanceCustomIndex = object index, gpu_scene.odin:135, so the
+// order of the remaining objects — and with it the order of the lights — is kept).
+int rt_remove_object(rt_ctx* ctx, uint32_t object_index) {
+    CTX_CHECK(ctx);
+    FANOUT(ctx, rt_remove_object(c, object_index));
+    if (!ctx->has_scene) { set_error("no scene"); return RT_ERR_NO_SCENE; }
+    if (object_index >= ctx->objects.size()) { set_error("rt_remove_object: bad index"); return RT_ERR_INDEX_RANGE; }
+    ctx->objects.erase(ctx->objects.begin() + object_index);
+    ctx->light_index.erase(ctx->light_index.begin() + object_index);
+    ctx->refit_objects.clear();
+    ctx->tables_dirty = true;
+    ctx->geometry_dirty = true;
     return RT_OK;
 }
 

@@ -185,12 +185,22 @@ struct BuildScratch {
     uint32_t scene_box[6];   // encoded lo.xyz, hi.xyz
     uint32_t level_int;      // internal children of the level just collapsed
     uint32_t level_tris;     // triangles emitted by that level
+    double sa_sum;           // half surface areas of all wide nodes (refit quality measure only: summation order is free)
 };
 
 __global__ void init_scratch_kernel(BuildScratch* s) {
     s->scene_box[0] = s->scene_box[1] = s->scene_box[2] = 0xFFFFFFFFu;
     s->scene_box[3] = s->scene_box[4] = s->scene_box[5] = 0u;
     s->level_int = 0; s->level_tris = 0;
+    s->sa_sum = 0.0;
+}
+
+// world-space vertex of an instance: the one evaluation order the flatten pass, the refit pass and the CPU twin share
+__device__ __forceinline__ vec3 instance_vertex(const DevObject* o, const rt_vertex* v) {
+    const vec3 q = mk3(v->pos[0], v->pos[1], v->pos[2]);
+    const float* m = o->model;
+    return mk3(((m[0] * q.x + m[3] * q.y) + m[6] * q.z) + m[9], ((m[1] * q.x + m[4] * q.y) + m[7] * q.z) + m[10],
+               ((m[2] * q.x + m[5] * q.y) + m[8] * q.z) + m[11]);
 }
 
 // 1. flat triangle i -> (object, primitive) by binary search over the object offsets
@@ -209,13 +219,7 @@ __global__ void flatten_kernel(BuildInput in, float4* flat, float4* box_lo, floa
         const rt_vertex* vb = in.d_vertices + o->vertex_base;
         vec3 p[3];
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
-            const rt_vertex* v = vb + ip[k];
-            const vec3 q = mk3(v->pos[0], v->pos[1], v->pos[2]);
-            const float* m = o->model;
-            p[k] = mk3(((m[0] * q.x + m[3] * q.y) + m[6] * q.z) + m[9], ((m[1] * q.x + m[4] * q.y) + m[7] * q.z) + m[10],
-                       ((m[2] * q.x + m[5] * q.y) + m[8] * q.z) + m[11]);
-        }
+        for (int k = 0; k < 3; k++) p[k] = instance_vertex(o, vb + ip[k]);
         flat[3 * (size_t)i + 0] = make_float4(p[0].x, p[0].y, p[0].z, __uint_as_float(i));
         flat[3 * (size_t)i + 1] = make_float4(p[1].x, p[1].y, p[1].z, __uint_as_float(a));
         flat[3 * (size_t)i + 2] = make_float4(p[2].x, p[2].y, p[2].z, __uint_as_float(prim));
@@ -442,11 +446,15 @@ __device__ __forceinline__ void quantize_axis(float lo, float hi, int* e_out, fl
 __global__ void emit_kernel(TreeView bt, const uint32_t* level, uint32_t n_level, const uint32_t* child_slots,
                             const uint32_t* int_prefix, const uint32_t* tri_prefix, uint32_t level_first,
                             uint32_t nodes_total, uint32_t tris_total, const uint32_t* sorted_ids, const float4* flat,
-                            Node8* nodes, float4* btris, uint32_t* next_level, BuildScratch* scratch) {
+                            Node8* nodes, float4* btris, uint32_t* next_level, BuildScratch* scratch, float4* node_lo,
+                            float4* node_hi) {
     const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= n_level) return;
     const uint32_t b = level[w];
     const float4 nlo = bt.lo[b], nhi = bt.hi[b];
+    node_lo[level_first + w] = nlo;
+    node_hi[level_first + w] = nhi;
+    atomicAdd(&scratch->sa_sum, (double)bt.half_area(b));
     Node8 nd;
     int e[3];
     quantize_axis(nlo.x, nhi.x, &e[0], &nd.p[0]);
@@ -539,8 +547,13 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
     BUILD_TRY(out.tris.ensure((size_t)n * 3));
     BUILD_TRY(out.morton.ensure(n));
     BUILD_TRY(out.sorted_ids.ensure(n));
+    BUILD_TRY(out.node_lo.ensure(max_nodes));
+    BUILD_TRY(out.node_hi.ensure(max_nodes));
     out.n_nodes = 1;
     out.depth = 1;
+    out.level_first.assign(1, 0u);
+    out.sa_build = 0.0;
+    out.refits = 0;
     if (n == 0) {
         empty_root_kernel<<<1, 1, 0, stream>>>(reinterpret_cast<Node8*>(out.nodes.p));
         BUILD_TRY(cudaGetLastError());
@@ -621,12 +634,14 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
         scanner.run(n_tri.p, n_level, stream);
         emit_kernel<<<g, 128, 0, stream>>>(bt, cur, n_level, child_slots.p, n_int.p, n_tri.p, level_first, nodes_total,
                                            tris_total, out.sorted_ids.p, flat.p, reinterpret_cast<Node8*>(out.nodes.p),
-                                           out.tris.p, nxt, scratch.p);
+                                           out.tris.p, nxt, scratch.p, out.node_lo.p, out.node_hi.p);
         BUILD_TRY(cudaGetLastError());
         BuildScratch hs;
         BUILD_TRY(cudaMemcpyAsync(&hs, scratch.p, sizeof(hs), cudaMemcpyDeviceToHost, stream));
         BUILD_TRY(cudaStreamSynchronize(stream));
         level_first += n_level;
+        out.level_first.push_back(level_first);
+        out.sa_build = hs.sa_sum;
         n_level = hs.level_int;
         nodes_total += hs.level_int;
         tris_total += hs.level_tris;
@@ -641,6 +656,114 @@ int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std:
     cudaEventElapsedTime(&out.build_ms, ev0, ev1);
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// refit: object transforms changed, the topology stays (the TLAS `mode = .UPDATE` of the reference:
+// src/raytracer/acceleration_structure.odin:91, gpu_scene.odin:457-483)
+// ------------------------------------------------------------------------------------------------
+__global__ void refit_tris_kernel(BuildInput in, const uint8_t* dirty, float4* btris) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= in.n_tris) return;
+    const uint32_t inst = __float_as_uint(btris[3 * (size_t)i + 1].w);
+    if (!dirty[inst]) return;
+    const uint32_t prim = __float_as_uint(btris[3 * (size_t)i + 2].w);
+    const DevObject* o = in.d_objects + inst;
+    const uint32_t* ip = in.d_indices + o->index_base + 3u * prim;
+    const rt_vertex* vb = in.d_vertices + o->vertex_base;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const vec3 p = instance_vertex(o, vb + ip[k]);
+        float4 q = btris[3 * (size_t)i + k];
+        q.x = p.x; q.y = p.y; q.z = p.z;
+        btris[3 * (size_t)i + k] = q;
+    }
+}
+
+// one thread per wide node of a level (deepest level first): exact child boxes from the triangles (leaves) or from the
+// children's own boxes (already refitted), the node's box as their union, then the same quantisation as emit_kernel
+__global__ void refit_level_kernel(Node8* nodes, const float4* btris, float4* node_lo, float4* node_hi, uint32_t first, uint32_t n_level,
+                                   double* sa_sum) {
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_level) return;
+    Node8 nd = nodes[first + w];
+    float clo[8][3], chi[8][3];
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    uint32_t n_int = 0;
+    for (int sl = 0; sl < 8; sl++) {
+        const uint32_t meta = nd.meta[sl];
+        if (meta == 0u) continue;
+        float l[3] = {INFINITY, INFINITY, INFINITY}, h[3] = {-INFINITY, -INFINITY, -INFINITY};
+        if ((meta & 0x38u) == 0x38u && (meta >> 5) == 1u) {   // internal child: 0x20 | (24 + slot)
+            const uint32_t c = nd.child_base + n_int++;
+            const float4 a = node_lo[c], b = node_hi[c];
+            l[0] = a.x; l[1] = a.y; l[2] = a.z; h[0] = b.x; h[1] = b.y; h[2] = b.z;
+        } else {                                               // leaf: unary count << 5 | offset from tri_base
+            const uint32_t un = meta >> 5, cnt = un == 1u ? 1u : (un == 3u ? 2u : 3u), off = meta & 31u;
+            for (uint32_t q = 0; q < cnt; q++)
+                for (int k = 0; k < 3; k++) {
+                    const float4 p = btris[3 * (size_t)(nd.tri_base + off + q) + k];
+                    l[0] = fminf(l[0], p.x); l[1] = fminf(l[1], p.y); l[2] = fminf(l[2], p.z);
+                    h[0] = fmaxf(h[0], p.x); h[1] = fmaxf(h[1], p.y); h[2] = fmaxf(h[2], p.z);
+                }
+        }
+        for (int a = 0; a < 3; a++) { clo[sl][a] = l[a]; chi[sl][a] = h[a]; lo[a] = fminf(lo[a], l[a]); hi[a] = fmaxf(hi[a], h[a]); }
+    }
+    if (lo[0] == INFINITY) return;  // a node without children (the root of an empty scene)
+    node_lo[first + w] = make_float4(lo[0], lo[1], lo[2], 0.0f);
+    node_hi[first + w] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+    {
+        const float ex = hi[0] - lo[0], ey = hi[1] - lo[1], ez = hi[2] - lo[2];
+        atomicAdd(sa_sum, (double)((ex * ey + ey * ez) + ez * ex));
+    }
+    int e[3];
+    float inv_scale[3];
+    for (int a = 0; a < 3; a++) {
+        quantize_axis(lo[a], hi[a], &e[a], &nd.p[a]);
+        nd.e[a] = (uint8_t)(e[a] + 127);
+        inv_scale[a] = __uint_as_float((uint32_t)(127 - e[a]) << 23);
+    }
+    for (int sl = 0; sl < 8; sl++) {
+        if (nd.meta[sl] == 0u) continue;  // empty slots keep their inverted box
+        for (int a = 0; a < 3; a++) {
+            const int ql = (int)floorf((clo[sl][a] - nd.p[a]) * inv_scale[a]) - 1;
+            const int qh = (int)ceilf((chi[sl][a] - nd.p[a]) * inv_scale[a]) + 1;
+            nd.q[a][0][sl] = half_of_int(min(max(ql, 0), RT_QMAX));
+            nd.q[a][1][sl] = half_of_int(min(max(qh, 0), RT_QMAX));
+        }
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(&nd);
+    uint4* dst = reinterpret_cast<uint4*>(nodes + first + w);
+#pragma unroll
+    for (int k = 0; k < (int)RT_NODE_WORDS; k++) dst[k] = src[k];
+}
+
+int refit_bvh8(const BuildInput& in, BuildOutput& out, const uint8_t* d_dirty, double* sa_now, cudaStream_t stream, std::string& err) {
+    const uint32_t n = in.n_tris;
+    if (n == 0 || out.level_first.size() < 2) { *sa_now = out.sa_build; return RT_OK; }
+    cudaEvent_t ev0, ev1;
+    BUILD_TRY(cudaEventCreate(&ev0));
+    BUILD_TRY(cudaEventCreate(&ev1));
+    BUILD_TRY(cudaEventRecord(ev0, stream));
+    PoolBuf<double> sa;
+    BUILD_TRY(sa.alloc(1, stream));
+    BUILD_TRY(cudaMemsetAsync(sa.p, 0, sizeof(double), stream));
+    refit_tris_kernel<<<(n + 255) / 256, 256, 0, stream>>>(in, d_dirty, out.tris.p);
+    for (size_t d = out.level_first.size() - 1; d-- > 0;) {
+        const uint32_t first = out.level_first[d], n_level = out.level_first[d + 1] - first;
+        if (n_level == 0) continue;
+        refit_level_kernel<<<(n_level + 127) / 128, 128, 0, stream>>>(reinterpret_cast<Node8*>(out.nodes.p), out.tris.p, out.node_lo.p,
+                                                                      out.node_hi.p, first, n_level, sa.p);
+    }
+    BUILD_TRY(cudaGetLastError());
+    BUILD_TRY(cudaMemcpyAsync(sa_now, sa.p, sizeof(double), cudaMemcpyDeviceToHost, stream));
+    BUILD_TRY(cudaEventRecord(ev1, stream));
+    BUILD_TRY(cudaEventSynchronize(ev1));
+    cudaEventElapsedTime(&out.refit_ms, ev0, ev1);
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    out.refits++;
     return RT_OK;
 }
 

@@ -96,9 +96,20 @@ struct BuildOutput {
     uint32_t n_nodes = 0;
     uint32_t depth = 0;
     float build_ms = 0.0f;
+    // kept for refits: the exact box of every wide node, the first node of every level (nodes are in level order, so a
+    // bottom-up pass is "levels last to first"), and the surface-area sum of the tree as built
+    DevBuf<float4> node_lo, node_hi;
+    std::vector<uint32_t> level_first;  // level_first[d] .. level_first[d + 1] - 1 = nodes of depth d; size depth + 1
+    double sa_build = 0.0;
+    uint32_t refits = 0;                // refits since the last build
+    float refit_ms = 0.0f;
 };
 // returns rt_status; err receives a message on failure
 int build_bvh8(const BuildInput& in, BuildOutput& out, cudaStream_t stream, std::string& err);
+// Refit after object transforms changed: the triangles of the objects flagged in d_dirty (one byte per object) are flattened
+// again in place, then every node's boxes are recomputed bottom-up over the unchanged topology.  *sa_now = the surface-area
+// sum afterwards (compare with out.sa_build to decide whether the tree has degraded enough to rebuild).
+int refit_bvh8(const BuildInput& in, BuildOutput& out, const uint8_t* d_dirty, double* sa_now, cudaStream_t stream, std::string& err);
 
 // ---- frame kernels (rt_frame.cu) -----------------------------------------------------------
 struct WavefrontBuffers;  // opaque to the API layer
@@ -198,6 +209,7 @@ struct rt_ctx {
     std::vector<uint32_t> light_index;  // per object, 0 after a bake (gpu_scene.odin:333-336)
     bool has_scene = false;
     bool geometry_dirty = false;  // BVH must be rebuilt before the next trace
+    std::vector<uint32_t> refit_objects;  // objects whose transform changed since the last flush (refit, not rebuild)
     bool tables_dirty = false;    // objects / lights / materials must be re-uploaded
 
     // device scene

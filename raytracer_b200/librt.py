@@ -30,7 +30,7 @@ NODE_BYTES, TRI_BYTES = 128, 48  # Node8 / BvhTri records of rt_get_bvh
 EXPORTS = (
     "rt_create", "rt_destroy", "rt_default_config", "rt_last_error", "rt_version", "rt_build_scene",
     "rt_scene_info_get", "rt_update_material", "rt_update_object_transform", "rt_update_object_material",
-    "rt_update_object_mesh", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_trace_frames_sliced", "rt_synchronize", "rt_readback",
+    "rt_update_object_mesh", "rt_add_material", "rt_remove_material", "rt_add_object", "rt_remove_object", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_trace_frames_sliced", "rt_synchronize", "rt_readback",
     "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_get_strip_owners", "rt_rebalance", "rt_measure_row_costs", "rt_set_strip_owners", "rt_trace_gbuffer", "rt_readback_gbuffer",
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
     "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_event_elapsed_per_device", "rt_set_profiling", "rt_get_kernel_profile",
@@ -73,7 +73,7 @@ class RtKernelProfile(C.Structure):
 class RtSceneInfo(C.Structure):
     _fields_ = [("n_triangles", C.c_uint32), ("n_nodes", C.c_uint32), ("bvh_depth", C.c_uint32),
                 ("n_lights", C.c_uint32), ("n_objects", C.c_uint32), ("n_materials", C.c_uint32),
-                ("build_ms", C.c_float), ("reserved", C.c_uint32)]
+                ("build_ms", C.c_float), ("refits", C.c_uint32)]
 
 
 class RtRestirParams(C.Structure):
@@ -120,6 +120,10 @@ def load() -> C.CDLL:
     L.rt_update_object_transform.argtypes = [vp, u32, f32p]
     L.rt_update_object_material.argtypes = [vp, u32, u32]
     L.rt_update_object_mesh.argtypes = [vp, u32, u32]
+    L.rt_add_material.argtypes = [vp, vp, C.POINTER(u32)]
+    L.rt_remove_material.argtypes = [vp, u32]
+    L.rt_add_object.argtypes = [vp, C.POINTER(RtObject), C.POINTER(u32)]
+    L.rt_remove_object.argtypes = [vp, u32]
     L.rt_resize.argtypes = [vp, u32, u32]
     L.rt_trace_frame.argtypes = [vp, f32p, f32p, u32]
     L.rt_trace_frames.argtypes = [vp, f32p, f32p, u32, u32]
@@ -242,6 +246,26 @@ class Context:
 
     def update_object_mesh(self, index, mesh_index):
         self._check(self.L.rt_update_object_mesh(self.h, index, mesh_index))
+
+    def add_material(self, material) -> int:
+        rec = np.ascontiguousarray(material.packed().reshape(1))
+        idx = C.c_uint32()
+        self._check(self.L.rt_add_material(self.h, _p(rec), C.byref(idx)))
+        return idx.value
+
+    def remove_material(self, index):
+        self._check(self.L.rt_remove_material(self.h, index))
+
+    def add_object(self, mesh_index, material_index, model16) -> int:
+        o = RtObject()
+        o.mesh_index, o.material_index = mesh_index, material_index
+        o.model[:] = [float(x) for x in np.asarray(model16, np.float32).reshape(16)]
+        idx = C.c_uint32()
+        self._check(self.L.rt_add_object(self.h, C.byref(o), C.byref(idx)))
+        return idx.value
+
+    def remove_object(self, index):
+        self._check(self.L.rt_remove_object(self.h, index))
 
     # ---- target / trace -----------------------------------------------------------------------
     def resize(self, width, height):

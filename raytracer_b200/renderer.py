@@ -47,6 +47,7 @@ class RaytracingRenderer:
         assert scene is not None
         self.scene = scene
         self.scene_info = self.ctx.build_scene(scene)
+        self.scene_info_meshes = len(scene.meshes)
         scene.changes.clear()
 
     def set_camera(self, camera: Camera):
@@ -83,7 +84,7 @@ class RaytracingRenderer:
         sc = self.scene
         if sc is not None and sc.changes:
             self.accumulation_frame = 0
-            structural = False
+            n_meshes = self.scene_info_meshes
             for ch in sc.changes:
                 t = ch.type
                 if t == SceneChangeType.Material_Changed:
@@ -94,12 +95,20 @@ class RaytracingRenderer:
                     self.ctx.update_object_transform(ch.index, sc.objects[ch.index].transform.model_matrix)
                 elif t == SceneChangeType.Object_Mesh_Changed:
                     self.ctx.update_object_mesh(ch.index, sc.objects[ch.index].mesh_index)
-                else:
-                    # Material/Object added or removed: the reference recompiles the whole table
-                    # (gpu_scene_recompile_materials / _objects, gpu_scene.odin:430-455)
-                    structural = True
-            if structural:
-                self.scene_info = self.ctx.build_scene(sc)
+                elif t == SceneChangeType.Material_Added:
+                    self.ctx.add_material(sc.materials[ch.index])
+                elif t == SceneChangeType.Material_Removed:
+                    self.ctx.remove_material(ch.index)
+                elif t == SceneChangeType.Object_Added:
+                    o = sc.objects[ch.index]
+                    if o.mesh_index >= n_meshes:
+                        # the object instances a mesh added after the last build: meshes only travel with rt_build_scene
+                        # (the reference has no change event for meshes at all), so the whole scene is built again
+                        self.set_scene(sc)
+                        return
+                    self.ctx.add_object(o.mesh_index, o.material_index, o.transform.model_matrix)
+                elif t == SceneChangeType.Object_Removed:
+                    self.ctx.remove_object(ch.index)
             sc.changes.clear()
 
     def render_scene(self):

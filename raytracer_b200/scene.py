@@ -172,8 +172,28 @@ class Scene:
         tr = Transform(np.asarray(position, F32), np.asarray(rotation, F32), np.asarray(scale, F32))
         tr.model_matrix = model_matrix_from_trs(tr.position, tr.rotation, tr.scale)
         self.objects.append(Object(name, tr, int(mesh_index), int(material_index)))
-        self.changes.append(SceneChange(SceneChangeType.Object_Added))
+        self.changes.append(SceneChange(SceneChangeType.Object_Added, len(self.objects) - 1))
         return len(self.objects) - 1
+
+    def delete_material(self, material_index: int) -> None:
+        """scene_delete_material (scene.odin:104-116): unordered_remove (the last material takes the freed slot), objects that
+        used the removed material fall back to material 0; objects that used the moved one follow it (defined here: the
+        reference leaves their index dangling)."""
+        last = len(self.materials) - 1
+        self.materials[material_index] = self.materials[last]
+        self.materials.pop()
+        for i, o in enumerate(self.objects):
+            if o.material_index == material_index:
+                self.update_object_material(i, 0)
+            elif o.material_index == last:
+                o.material_index = material_index
+        self.changes.append(SceneChange(SceneChangeType.Material_Removed, material_index))
+
+    def delete_object(self, object_idx: int) -> None:
+        """Object_Removed (scene.odin:21; the reference declares the change but ships no procedure that raises it): ordered
+        removal, later objects move down one index."""
+        del self.objects[object_idx]
+        self.changes.append(SceneChange(SceneChangeType.Object_Removed, object_idx))
 
     # -- edits (each appends a Scene_Change, scene.odin:116-163) ------------------------------
     def update_material(self, material_idx: int, material: Material) -> None:

@@ -180,3 +180,75 @@ def test_update_object_mesh_matches_rebuild_and_oracle():
             c.update_object_mesh(victim, 10 ** 6)
     finally:
         c.close()
+
+
+def test_transform_update_is_a_refit_and_matches_rebuild_and_oracle():
+    """rt_update_object_transform refits the boxes over the existing topology (TLAS update of the reference,
+    acceleration_structure.odin:91, gpu_scene.odin:457-483): refit + trace == rebuild + trace == oracle, for a drag of
+    several steps on the 262 k-triangle benchmark scene and on an instanced scene; a move that blows the tree up rebuilds."""
+    from raytracer_b200 import proxy_scenes
+
+    W, H = 160, 90
+    scene = proxy_scenes.sponza_proxy()
+    cam = rb.Camera(aspect=W / H, **proxy_scenes.SPONZA_CAMERA)
+    c = librt.Context(device=0, max_depth=4)
+    try:
+        info = c.build_scene(scene)
+        c.resize(W, H)
+        n_nodes = info.n_nodes
+        for step in range(3):   # drag two objects
+            for obj in (5, 40):
+                mm = np.asarray(scene.objects[obj].transform.model_matrix, np.float32).copy()
+                mm[12] += 0.15
+                mm[13] += 0.05 * (step + 1)
+                scene.objects[obj].transform.model_matrix = mm
+                c.update_object_transform(obj, mm)
+            c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+            info = c.scene_info()
+            assert info.refits == step + 1 and info.n_nodes == n_nodes     # no rebuild happened
+        got = c.readback().copy()
+        ref = _oracle_replay_depth(OracleScene(scene).build_bvh(), cam, W, H, range(2), 4)
+        assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+        # traversal hooks see the refitted tree: closest hits == brute force over the moved triangles
+        from conftest import random_rays
+        rays = random_rays(4000, 3, lo=(-14, 0, -8), hi=(14, 10, 8), target_lo=(-14, 0, -8), target_hi=(14, 10, 8))
+        tuv, ids = c.trace_rays_closest(rays)
+        o_tuv, o_ids = OracleScene(scene).build_bvh().trace_rays(rays, mode="bvh")
+        assert np.array_equal(ids, o_ids) and np.array_equal(tuv.view(np.uint32), o_tuv.view(np.uint32))
+        c.build_scene(scene)    # from scratch
+        c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+        assert np.array_equal(c.readback().view(np.uint32), got.view(np.uint32))
+        assert c.scene_info().refits == 0
+        # far away: the root box grows a hundredfold -> the refit reports a degraded tree and the flush rebuilds
+        mm = np.asarray(scene.objects[5].transform.model_matrix, np.float32).copy()
+        mm[12] += 500.0
+        scene.objects[5].transform.model_matrix = mm
+        c.update_object_transform(5, mm)
+        c.trace_frames(cam.ubo(), CLEAR, 0, 2)
+        assert c.scene_info().refits == 0
+        ref = _oracle_replay_depth(OracleScene(scene).build_bvh(), cam, W, H, range(2), 4)
+        assert np.array_equal(c.readback().view(np.uint32), ref.view(np.uint32))
+    finally:
+        c.close()
+    # instanced meshes (scenes/cornell_box.json shares one plane and one sphere mesh): only the moved instance's triangles change
+    scene = fixture_scene("cornell_box")
+    cam = rb.Camera(aspect=1.0)
+    c = librt.Context(device=0)
+    try:
+        c.build_scene(scene)
+        c.resize(64, 64)
+        scene.update_object_position(7, (0.3, -0.2, 0.1))
+        c.update_object_transform(7, scene.objects[7].transform.model_matrix)
+        c.trace_frames(cam.ubo(), CLEAR, 0, 3)
+        assert c.scene_info().refits == 1
+        ref = _oracle_replay(OracleScene(scene).build_bvh(), cam, 64, 64, range(3))
+        assert np.array_equal(c.readback().view(np.uint32), ref.view(np.uint32))
+    finally:
+        c.close()
+
+
+def _oracle_replay_depth(orc, cam, W, H, frames, depth):
+    img = None
+    for f in frames:
+        img = orc.render(cam.ubo(), CLEAR, f, W, H, image=img, max_depth=depth)
+    return img
