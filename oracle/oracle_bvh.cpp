@@ -271,7 +271,69 @@ void build_bvh8(Scene& s) {
     BinTree bt;
     bt.n = n;
     bt.box.resize(n == 1 ? 1 : 2 * n - 1);
-    if (n == 1) {
+    if (n > 1 && getenv("ORC_SAH_EXPERIMENT")) {
+        // EXPERIMENT (not the twin of anything on the GPU): top-down binned SAH over the same leaves, to measure what a
+        // SAH-quality binary tree would buy the collapsed BVH8 before building it on the device
+        std::vector<uint32_t> perm(s.sorted_ids);
+        bt.left.assign(n - 1, 0); bt.right.assign(n - 1, 0); bt.first.assign(n - 1, 0); bt.count.assign(n - 1, 0);
+        uint32_t next_internal = 0;
+        struct Job { uint32_t lo, hi, node; };
+        std::vector<Job> stack;
+        auto alloc = [&](uint32_t lo, uint32_t hi) -> uint32_t {  // node id of the range
+            if (hi - lo == 1) return n - 1 + lo;
+            const uint32_t id = next_internal++;
+            stack.push_back({lo, hi, id});
+            return id;
+        };
+        alloc(0, n);
+        const int NB = 32;
+        while (!stack.empty()) {
+            Job j = stack.back(); stack.pop_back();
+            Box cb{v3s(INFINITY), v3s(-INFINITY)};
+            for (uint32_t k = j.lo; k < j.hi; k++) { V3 c = (tb[perm[k]].lo + tb[perm[k]].hi) * 0.5f; cb.lo = v3(fminf(cb.lo.x, c.x), fminf(cb.lo.y, c.y), fminf(cb.lo.z, c.z)); cb.hi = v3(fmaxf(cb.hi.x, c.x), fmaxf(cb.hi.y, c.y), fmaxf(cb.hi.z, c.z)); }
+            float best = INFINITY; int best_axis = -1, best_bin = -1;
+            for (int ax = 0; ax < 3; ax++) {
+                const float lo = comp(cb.lo, ax), hi = comp(cb.hi, ax);
+                if (!(hi > lo)) continue;
+                Box bb[NB]; uint32_t bc[NB];
+                for (int b = 0; b < NB; b++) { bb[b] = Box{v3s(INFINITY), v3s(-INFINITY)}; bc[b] = 0; }
+                const float sc2 = NB / (hi - lo);
+                for (uint32_t k = j.lo; k < j.hi; k++) {
+                    const Box& t = tb[perm[k]];
+                    int b = (int)((comp((t.lo + t.hi) * 0.5f, ax) - lo) * sc2); if (b >= NB) b = NB - 1; if (b < 0) b = 0;
+                    bb[b] = box_union(bb[b], t); bc[b]++;
+                }
+                Box acc{v3s(INFINITY), v3s(-INFINITY)}; float la[NB]; uint32_t lc[NB]; uint32_t c = 0;
+                for (int b = 0; b < NB - 1; b++) { acc = box_union(acc, bb[b]); c += bc[b]; la[b] = c ? half_area(acc) : 0.0f; lc[b] = c; }
+                acc = Box{v3s(INFINITY), v3s(-INFINITY)}; c = 0;
+                for (int b = NB - 1; b > 0; b--) {
+                    acc = box_union(acc, bb[b]); c += bc[b];
+                    if (c == 0 || lc[b - 1] == 0) continue;
+                    const float cost = la[b - 1] * lc[b - 1] + half_area(acc) * c;
+                    if (cost < best) { best = cost; best_axis = ax; best_bin = b; }
+                }
+            }
+            uint32_t mid;
+            if (best_axis < 0) mid = (j.lo + j.hi) / 2;
+            else {
+                const float lo = comp(cb.lo, best_axis), sc2 = NB / (comp(cb.hi, best_axis) - lo);
+                auto it = std::stable_partition(perm.begin() + j.lo, perm.begin() + j.hi, [&](uint32_t id) {
+                    int b = (int)((comp((tb[id].lo + tb[id].hi) * 0.5f, best_axis) - lo) * sc2); if (b >= NB) b = NB - 1; if (b < 0) b = 0;
+                    return b < best_bin; });
+                mid = (uint32_t)(it - perm.begin());
+                if (mid == j.lo || mid == j.hi) mid = (j.lo + j.hi) / 2;
+            }
+            bt.first[j.node] = j.lo; bt.count[j.node] = j.hi - j.lo;
+            const uint32_t l = alloc(j.lo, mid), r = alloc(mid, j.hi);
+            bt.left[j.node] = l; bt.right[j.node] = r;
+        }
+        s.sorted_ids = perm;
+        for (uint32_t k = 0; k < n; k++) bt.box[n - 1 + k] = tb[s.sorted_ids[k]];
+        std::vector<uint32_t> order; std::vector<uint32_t> st{0};
+        while (!st.empty()) { uint32_t nd = st.back(); st.pop_back(); order.push_back(nd);
+            if (!bt.is_leaf(bt.left[nd])) st.push_back(bt.left[nd]); if (!bt.is_leaf(bt.right[nd])) st.push_back(bt.right[nd]); }
+        for (size_t q = order.size(); q-- > 0;) bt.box[order[q]] = box_union(bt.box[bt.left[order[q]]], bt.box[bt.right[order[q]]]);
+    } else if (n == 1) {
         bt.box[0] = tb[s.sorted_ids[0]];
     } else {
         bt.left.resize(n - 1); bt.right.resize(n - 1); bt.first.resize(n - 1); bt.count.resize(n - 1);

@@ -705,6 +705,36 @@ static int balance_strips(rt_ctx* ctx, const float* camera_ubo, const float* cle
     return install_owners(ctx, owner.data(), n_strips);
 }
 
+#ifndef RT_TWO_STREAM_MIN_LANES
+#define RT_TWO_STREAM_MIN_LANES 8
+#endif
+#ifndef RT_STATE_CAP_GIB
+#define RT_STATE_CAP_GIB 56  /* of the B200's 180 GB: 128 frames in flight at 1080p; 41 -> 128 frames: 0.540 -> 0.525 ms/frame */
+#endif
+// (Re)allocates the wavefront path state for up to `frames` frames in flight (~200 B per slot; all lanes together stay under
+// RT_STATE_CAP_GIB and 2^31 slots).  From RT_TWO_STREAM_MIN_LANES frames on, the state is split into equal shares for
+// RT_N_STREAMS streams.
+static int alloc_path_state(rt_ctx* ctx, uint32_t frames) {
+    if (ctx->wf) { wavefront_free(ctx->wf); ctx->wf = nullptr; }
+    for (rt::WavefrontBuffers*& w : ctx->wfx) if (w) { wavefront_free(w); w = nullptr; }
+    ctx->lanes = 1;
+    ctx->lanes_for = frames;
+    if (ctx->cfg.pipeline != RT_PIPELINE_WAVEFRONT) return RT_OK;
+    const size_t n = (size_t)ctx->local_rows * ctx->width;
+    std::string err;
+    uint64_t lanes = std::max<uint32_t>(frames, 1u);
+    const uint64_t per_lane = std::max<uint64_t>(n, 1) * 200ull;
+    lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, ((uint64_t)RT_STATE_CAP_GIB << 30) / per_lane));
+    lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, 0x7FFFFFFFull / std::max<uint64_t>(n, 1)));
+    const bool split = lanes >= RT_TWO_STREAM_MIN_LANES;
+    if (split) lanes = (lanes + RT_N_STREAMS - 1) / RT_N_STREAMS;
+    ctx->lanes = (uint32_t)lanes;
+    int rc = wavefront_alloc(&ctx->wf, (uint32_t)(n * lanes), err);
+    for (int k = 0; k < RT_N_STREAMS - 1 && rc == RT_OK && split; k++) rc = wavefront_alloc(&ctx->wfx[k], (uint32_t)(n * lanes), err);
+    if (rc != RT_OK) { set_error(err); return rc; }
+    return RT_OK;
+}
+
 extern "C" {
 
 // raytracing_renderer_on_resize (raytracing_renderer.odin:108-126): new output image, accumulation restarts
@@ -732,30 +762,9 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     ctx->has_gbuffer = false;
     ctx->rs_history = false;
     ctx->rs_surf.release(); ctx->rs_cur.release(); ctx->rs_hist[0].release(); ctx->rs_hist[1].release();
-    if (ctx->wf) { wavefront_free(ctx->wf); ctx->wf = nullptr; }
-    for (rt::WavefrontBuffers*& w : ctx->wfx) if (w) { wavefront_free(w); w = nullptr; }
-    if (ctx->cfg.pipeline == RT_PIPELINE_WAVEFRONT) {
-        std::string err;
-#ifndef RT_TWO_STREAM_MIN_LANES
-#define RT_TWO_STREAM_MIN_LANES 8
-#endif
-        // path state is ~200 B per slot; keep all lanes together under RT_STATE_CAP_GIB and 2^31 slots
-#ifndef RT_STATE_CAP_GIB
-#define RT_STATE_CAP_GIB 56  /* of the B200's 180 GB: 128 frames in flight at 1080p; 41 -> 128 frames: 0.540 -> 0.525 ms/frame */
-#endif
-        uint64_t lanes = ctx->cfg.frames_in_flight;
-        const uint64_t per_lane = std::max<uint64_t>(n, 1) * 200ull;
-        lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, ((uint64_t)RT_STATE_CAP_GIB << 30) / per_lane));
-        lanes = std::min<uint64_t>(lanes, std::max<uint64_t>(1, 0x7FFFFFFFull / std::max<uint64_t>(n, 1)));
-        // from RT_TWO_STREAM_MIN_LANES frames in flight on, the path state is split into equal shares for RT_N_STREAMS streams
-        const bool split = lanes >= RT_TWO_STREAM_MIN_LANES;
-        if (split) lanes = (lanes + RT_N_STREAMS - 1) / RT_N_STREAMS;
-        ctx->lanes = (uint32_t)lanes;
-        int rc = wavefront_alloc(&ctx->wf, (uint32_t)(n * lanes), err);
-        for (int k = 0; k < RT_N_STREAMS - 1 && rc == RT_OK && split; k++) rc = wavefront_alloc(&ctx->wfx[k], (uint32_t)(n * lanes), err);
-        if (rc != RT_OK) { set_error(err); return rc; }
-    }
-    return RT_OK;
+    // path state for ONE frame in flight: what rt_trace_frame (the reference's application loop, application.odin:109-115) needs.
+    // The first rt_trace_frames call with n > 1 grows it to cfg.frames_in_flight (alloc_path_state).
+    return alloc_path_state(ctx, 1u);
 }
 
 // Frames first_frame + k * frame_stride (k < n_frames) folded into the image as samples first_sample + k.
@@ -772,6 +781,13 @@ static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const floa
     // an accumulation restarts: the strips may change hands (the image is overwritten by frame 0 anyway)
     if (ctx->balance_pending && first_sample == 0u) {
         rc = balance_strips(ctx, camera_ubo, clear_color, first_frame);
+        if (rc != RT_OK) return rc;
+    }
+    if (n_frames > 1u && ctx->lanes_for < ctx->cfg.frames_in_flight && ctx->cfg.pipeline == RT_PIPELINE_WAVEFRONT) {
+        // first batched call: the path state grows from one frame in flight to the configured number
+        RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        for (cudaStream_t st2 : ctx->streamx) if (st2) RT_CUDA_TRY(cudaStreamSynchronize(st2));
+        rc = alloc_path_state(ctx, ctx->cfg.frames_in_flight);
         if (rc != RT_OK) return rc;
     }
     const SceneView sc = rt_scene_view(ctx);

@@ -225,6 +225,7 @@ struct rt_ctx {
     // target
     uint32_t width = 0, height = 0, local_rows = 0;
     uint32_t lanes = 1;  // frames traced together by the wavefront pipeline (<= cfg.frames_in_flight)
+    uint32_t lanes_for = 0;  // the frames in flight the path state was last sized for (1 after rt_resize, cfg.frames_in_flight after the first batch)
     rt::DevBuf<float4> image;
     rt::DevBuf<uchar4> srgb;
     rt::DevBuf<rt::DevCounters> counters;

@@ -12,7 +12,7 @@ try:
 except Exception as e: print("no json", sys.argv[1], e)
 PY
 }
-timeout 300 python -m pytest tests/test_gpu_multi.py -m gpu -q -p no:cacheprovider 2>&1 | tail -5
+timeout 600 python -m pytest tests/test_gpu_multi.py tests/test_gpu_host.py -m gpu -q -p no:cacheprovider 2>&1 | tail -8
 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 16 --warmup 3 > gpurun_out/${TAG}_bench_n$N.json 2> gpurun_out/${TAG}_bench_n$N.err; echo "torchrun bench rc=$?"
 tail -c 600 gpurun_out/${TAG}_bench_n$N.err
 show gpurun_out/${TAG}_bench_n$N.json
