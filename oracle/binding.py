@@ -2,7 +2,9 @@
 
 May be imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
 legs ONLY.  The product package (raytracer_b200/) never imports this module.
-Parity status: UNPINNED (the reference has no CPU path, tests or golden vectors).
+Parity status: the shader code is pinned to the reference's SHIPPED SPIR-V binaries executed by tools/spirv_interp.py
+(tests/golden/spirv_frames.npz, tests/test_oracle.py); what Vulkan leaves to the driver — built-in precision, BVH traversal,
+the hit a terminate-on-first-hit ray query commits — is defined by the arithmetic contract and stays unpinned.
 """
 from __future__ import annotations
 

@@ -1,4 +1,4 @@
-// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: UNPINNED.
+// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: pinned to the shipped SPIR-V (tests/golden/spirv_frames.npz); driver-defined parts unpinned.
 // C entry points for ctypes (tests/, bench.py cpu_baseline / --impl reference, smoke()).
 #include <cstdio>
 #include <cstdlib>

@@ -1,4 +1,4 @@
-// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: UNPINNED.
+// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: pinned to the shipped SPIR-V (tests/golden/spirv_frames.npz); driver-defined parts unpinned.
 //
 // Stand-in for what the reference delegates to the Vulkan driver: acceleration-structure build
 // (src/raytracer/acceleration_structure.odin:65-199, gpu_scene.odin:120-150) and the traversal

@@ -2,11 +2,17 @@
 // (raytracer_b200/csrc).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 // --impl reference legs may load it.
 //
-// Parity status: UNPINNED.  The reference (ARTurleite6/RayTracer) has no CPU implementation,
-// no tests and no golden vectors for this path, and its GLSL cannot be run here (no graphics
-// stack).  This file restates the GLSL built-ins the shaders rely on as plain IEEE-754 binary32
-// arithmetic with a fixed evaluation order ("the arithmetic contract"), so that a
-// second, independently written implementation (the CUDA kernels) can be compared bit for bit.
+// Parity status: PINNED TO THE SHIPPED SHADER BINARIES for the shader code; driver-defined parts unpinned.
+// The reference (ARTurleite6/RayTracer) has no CPU implementation, no tests and no golden vectors for this path,
+// and its Vulkan pipeline cannot be run here (no graphics stack).  What CAN be run is the SPIR-V the reference ships and
+// loads (shaders/rgen.spv, rchit.spv, rmiss.spv, restir_*.spv): tools/spirv_interp.py executes those binaries instruction
+// by instruction, tools/spirv_golden.py commits the frames, G-buffers and function vectors they compute
+// (tests/golden/spirv_frames.npz), and tests/test_oracle.py requires this oracle to reproduce them bit for bit — which pins
+// evaluation order, association, branch structure and the order of the random draws.  Not pinned by anything the reference
+// holds: the precision of the GLSL built-ins Vulkan leaves to the driver (normalize, dot, sin, cos, pow ...), the BVH
+// and its traversal (inside the driver), and which hit a terminate-on-first-hit ray query commits.  For those this file
+// states plain IEEE-754 binary32 arithmetic with a fixed evaluation order ("the arithmetic contract"), so that
+// a second, independently written implementation (the CUDA kernels) can be compared bit for bit.
 //
 // Build: g++ -O2 -ffp-contract=off -mfma (no -ffast-math).  fmaf() appears only where the
 // contract says "fused".

@@ -1,4 +1,4 @@
-// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: UNPINNED.
+// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: pinned to the shipped SPIR-V (tests/golden/spirv_frames.npz); driver-defined parts unpinned.
 //
 // CPU restatement of the live shader path of ARTurleite6/RayTracer, one function per shader
 // function, each citing the file:line it follows:

@@ -1,4 +1,4 @@
-// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: UNPINNED.
+// ORACLE — test infrastructure only (see oracle_math.h header).  Parity status: pinned to the shipped SPIR-V (tests/golden/spirv_frames.npz); driver-defined parts unpinned.
 //
 // Scene tables as the reference's shaders see them, derived from the host arrays exactly like
 // src/raytracer/gpu_scene.odin does, plus the flattened world-space triangle list that stands in

@@ -88,3 +88,19 @@ def test_product_package_never_imports_the_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", "Makefile")):
                 assert not pat.search(open(os.path.join(dirpath, f), errors="ignore").read()), f
+
+
+def _build_c_host(tmp_path):
+    exe = str(tmp_path / "host_three_calls")
+    csrc = os.path.join(ROOT, "raytracer_b200", "csrc")
+    subprocess.run(["gcc", "-std=c99", "-O2", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(ROOT, "examples", "host_three_calls.c"), "-L", csrc, "-lrt", f"-Wl,-rpath,{csrc}", "-o", exe], check=True)
+    return exe
+
+
+def test_a_plain_c_host_compiles_and_links_against_the_abi(lib, tmp_path):
+    """examples/host_three_calls.c: the reference renderer's three calls from C, GPUs listed in rt_config — no Python, no torch.
+    Here it must compile with -Wall -Werror against include/rt_api.h and link against librt.so; tests/test_gpu_multi.py runs it."""
+    exe = _build_c_host(tmp_path)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stderr

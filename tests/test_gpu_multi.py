@@ -306,3 +306,37 @@ def test_restir_image_does_not_depend_on_the_partition(mode):
         assert np.isfinite(c.readback()).all()
     finally:
         c.close()
+
+
+def test_a_plain_c_host_drives_the_gpus_through_the_abi(tmp_path):
+    """examples/host_three_calls.c (gcc, no Python in the process): build / trace / consume with the GPUs listed in
+    rt_config.device_ids.  Its image file must equal the ctypes single-context image bit for bit."""
+    import subprocess
+
+    from test_abi import _build_c_host
+
+    scene = fixture_scene("cornell_pbr")
+    W, H, n, depth = 96, 52, 3, 3
+    cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=W / H, target=(0.0, 1.0, 0.0))
+    want, _, _ = _single(scene, cam, W, H, n, depth)
+    blob = tmp_path / "scene.bin"
+    with open(blob, "wb") as f:
+        f.write(np.asarray([len(scene.meshes), len(scene.objects), len(scene.materials), W, H, n, depth], np.uint32).tobytes())
+        for m in scene.meshes:
+            f.write(np.asarray([len(m.vertices), len(m.indices)], np.uint32).tobytes())
+            f.write(np.ascontiguousarray(m.vertices).tobytes())
+            f.write(np.ascontiguousarray(m.indices, np.uint32).tobytes())
+        mesh, mat, model = scene.packed_objects()
+        for i in range(len(scene.objects)):
+            f.write(np.asarray([mesh[i], mat[i]], np.uint32).tobytes() + np.ascontiguousarray(model[i], np.float32).tobytes())
+        f.write(scene.packed_materials().tobytes())
+        f.write(np.ascontiguousarray(cam.ubo(), np.float32).tobytes() + np.asarray(CLEAR, np.float32).tobytes())
+    exe = _build_c_host(tmp_path)
+    devices = ["0", "1"] if _n_gpus() >= 2 else ["0", "0"]
+    for devs in (["0"], devices, ["0", "0", "0"]):
+        out = tmp_path / "out.rgba32f"
+        r = subprocess.run([exe, str(blob), str(out)] + devs, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        got = np.fromfile(out, np.float32).reshape(H, W, 4)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), devs
+        assert f"{max(len(devs), 1)} devices" in r.stdout
