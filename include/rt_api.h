@@ -271,6 +271,13 @@ RT_API int rt_trace_gbuffer(rt_ctx* ctx, const float camera_ubo[64]);
 RT_API int rt_readback_gbuffer(rt_ctx* ctx, uint8_t* albedo, uint16_t* normal_rough, float* position_metal,
                         uint16_t* emission, uint8_t* output);
 
+/* ---- rasterised G-buffer variant: shaders/restir/gbuffer.vert:22-37 + gbuffer.frag:26-39 (no host code of the reference draws
+ * with them; the fixed-function state is stated in rt_raster.cu).  Five float4 attachments, full-size W*H images, any pointer
+ * may be NULL: albedo|1, normalize(normal)|metallic, world position|roughness, emission_power*emission_color|isEmissive,
+ * roughness|metallic|isEmissive|0.  Note gbuffer.vert mirrors position and normal in y before the model matrix. */
+RT_API int rt_raster_gbuffer(rt_ctx* ctx, const float camera_ubo[64]);
+RT_API int rt_readback_raster_gbuffer(rt_ctx* ctx, float* albedo, float* normal_metal, float* position_rough, float* emission, float* props);
+
 /* ---- ReSTIR DI on the G-buffer (layout: shaders/restir/restir_structs.glsl; algorithm: the
  * reference has none — shaders/restir/restir_di.rgen:17-22 is a stub; parity unpinned) -------- */
 RT_API void rt_default_restir_params(rt_restir_params* p);

@@ -760,6 +760,9 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
     RT_CUDA_TRY(cudaMemsetAsync(ctx->image.p, 0, std::max<size_t>(n, 1) * sizeof(float4), ctx->stream));
     ctx->srgb.release();
     ctx->has_gbuffer = false;
+    ctx->has_raster = false;
+    ctx->ras_vis.release();
+    for (auto& b : ctx->ras_img) b.release();
     ctx->rs_history = false;
     ctx->rs_surf.release(); ctx->rs_cur.release(); ctx->rs_hist[0].release(); ctx->rs_hist[1].release();
     // path state for ONE frame in flight: what rt_trace_frame (the reference's application loop, application.odin:109-115) needs.

@@ -240,6 +240,11 @@ struct rt_ctx {
     rt::DevBuf<ushort4> g_normal, g_emission;
     rt::DevBuf<float4> g_position;
     bool has_gbuffer = false;
+    // rasterised G-buffer variant (rt_raster.cu): visibility keys, camera copy, five float4 attachments, full frame
+    rt::DevBuf<unsigned long long> ras_vis;
+    rt::DevBuf<float> ras_cam;
+    rt::DevBuf<float4> ras_img[5];
+    bool has_raster = false;
     // ReSTIR DI (rt_restir.cu): primary surfaces, this frame's reservoirs, the history
     rt::DevBuf<float4> rs_surf;
     rt::DevBuf<rt_reservoir> rs_cur, rs_hist[2];

@@ -31,7 +31,7 @@ EXPORTS = (
     "rt_create", "rt_destroy", "rt_default_config", "rt_last_error", "rt_version", "rt_build_scene",
     "rt_scene_info_get", "rt_update_material", "rt_update_object_transform", "rt_update_object_material",
     "rt_update_object_mesh", "rt_add_material", "rt_remove_material", "rt_add_object", "rt_remove_object", "rt_resize", "rt_trace_frame", "rt_trace_frames", "rt_trace_frames_sliced", "rt_synchronize", "rt_readback",
-    "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_get_strip_owners", "rt_rebalance", "rt_measure_row_costs", "rt_set_strip_owners", "rt_trace_gbuffer", "rt_readback_gbuffer",
+    "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_get_strip_owners", "rt_rebalance", "rt_measure_row_costs", "rt_set_strip_owners", "rt_trace_gbuffer", "rt_readback_gbuffer", "rt_raster_gbuffer", "rt_readback_raster_gbuffer",
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
     "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_event_elapsed_per_device", "rt_set_profiling", "rt_get_kernel_profile",
     "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh",
@@ -139,6 +139,8 @@ def load() -> C.CDLL:
     L.rt_set_strip_owners.argtypes = [vp, vp, u32]
     L.rt_trace_gbuffer.argtypes = [vp, f32p]
     L.rt_readback_gbuffer.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.rt_raster_gbuffer.argtypes = [vp, f32p]
+    L.rt_readback_raster_gbuffer.argtypes = [vp, vp, vp, vp, vp, vp]
     L.rt_default_restir_params.argtypes = [C.POINTER(RtRestirParams)]
     L.rt_default_restir_params.restype = None
     L.rt_restir_frame.argtypes = [vp, f32p, f32p, u32, C.POINTER(RtRestirParams)]
@@ -352,6 +354,15 @@ class Context:
                    output=np.zeros((H, W, 4), np.uint8))
         self._check(self.L.rt_readback_gbuffer(self.h, _p(out["albedo"]), _p(out["normal_rough"]),
                                                _p(out["position_metal"]), _p(out["emission"]), _p(out["output"])))
+        return out
+
+    def raster_gbuffer(self, camera_ubo) -> dict:
+        """The rasterised G-buffer variant (gbuffer.vert / gbuffer.frag): five (H, W, 4) float32 attachments."""
+        cam = np.ascontiguousarray(camera_ubo, np.float32).reshape(64)
+        self._check(self.L.rt_raster_gbuffer(self.h, _p(cam)))
+        names = ("albedo", "normal_metal", "position_rough", "emission", "props")
+        out = {k: np.zeros((self.height, self.width, 4), np.float32) for k in names}
+        self._check(self.L.rt_readback_raster_gbuffer(self.h, *[_p(out[k]) for k in names]))
         return out
 
     def restir_frame(self, camera_ubo, clear_color, frame_number, params: RtRestirParams = None):

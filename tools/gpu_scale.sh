@@ -1,0 +1,14 @@
+#!/bin/bash
+# one point of the scaling table: torchrun bench at N GPUs (as the driver launches it), plus the reference arm
+cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
+mkdir -p gpurun_out
+N=${1:-2}
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/r2s_bench_n$N.json 2> gpurun_out/r2s_bench_n$N.err; echo "bench rc=$?"
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29519 bench.py --impl reference --gpus $N --steps 4 --warmup 1 > gpurun_out/r2s_ref_n$N.json 2> gpurun_out/r2s_ref_n$N.err; echo "ref rc=$?"
+python - "$N" <<'PY'
+import json,sys
+n=sys.argv[1]
+j=json.loads(open(f"gpurun_out/r2s_bench_n{n}.json").read().strip().splitlines()[-1])
+print({k:j[k] for k in ("value","ms_per_step","n_gpus")}, "e2e", round(j["e2e"]["value"],1), j.get("ranks"), j.get("verify"))
+r=json.loads(open(f"gpurun_out/r2s_ref_n{n}.json").read().strip().splitlines()[-1]); print("reference arm:", r["value"], r["cpu_baseline"]["cores"])
+PY
