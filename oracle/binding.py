@@ -55,6 +55,8 @@ def lib():
         L.orc_direct_reference.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p]
         L.orc_direct_reference_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                                 C.c_int, C.c_int, C.c_void_p]
+        L.orc_raster_gbuffer.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 5
+        L.orc_unit_raster_vertex.argtypes = [C.c_void_p] * 5
         L.orc_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
         L.orc_tea.argtypes = [C.c_uint32, C.c_uint32]
@@ -163,6 +165,14 @@ class OracleScene:
                    output=np.zeros((H, W, 4), np.uint8))
         self.L.orc_gbuffer(self.h, _ptr(cam), W, H, 0, H, int(use_bvh), _ptr(out["albedo"]), _ptr(out["normal_rough"]),
                            _ptr(out["position_metal"]), _ptr(out["emission"]), _ptr(out["output"]))
+        return out
+
+    def raster_gbuffer(self, cam_ubo, W, H):
+        """CPU twin of rt_raster_gbuffer (gbuffer.vert / gbuffer.frag + the stated fixed-function rules)."""
+        cam = np.ascontiguousarray(cam_ubo, np.float32)
+        names = ("albedo", "normal_metal", "position_rough", "emission", "props")
+        out = {k: np.zeros((H, W, 4), np.float32) for k in names}
+        self.L.orc_raster_gbuffer(self.h, _ptr(cam), W, H, *[_ptr(out[k]) for k in names])
         return out
 
     def direct_reference(self, cam_ubo, clear, W, H, samples_per_axis=4, use_bvh=True, y0=0, y1=None):

@@ -17,6 +17,9 @@ void direct_reference_rows(const Scene& s, int use_bvh, const float* cam, const 
 void gbuffer_rows(const Scene& s, int use_bvh, const float* cam, uint32_t W, uint32_t H, uint32_t y0, uint32_t y1,
                   uint8_t* albedo_rgba8, uint16_t* normal_rough_f16, float* position_metal_f32, uint16_t* emission_f16,
                   uint8_t* output_rgba8);
+void raster_gbuffer(const Scene& s, const float* cam, uint32_t W, uint32_t H, float* albedo, float* normal_metal, float* position_rough,
+                    float* emission, float* props);
+void unit_raster_vertex(const float* model16, const float* pos3, const float* normal3, const float* cam, float out[10]);
 void unit_sample_brdf(const Material& m, V3 wo, float rx, float ry, uint32_t* seed, float out[8]);
 void unit_eval_brdf(const Material& m, V3 wo, V3 wi, float out[4]);
 }  // namespace orc
@@ -104,6 +107,15 @@ int orc_direct_reference(void* h, const float* cam64, const float* clear3, uint3
     if (use_bvh && !s->has_bvh) build_bvh8(*s);
     direct_reference_rows(*s, use_bvh, cam64, clear3, W, H, 0, H, spt, image_rgba);
     return 0;
+}
+
+int orc_raster_gbuffer(void* h, const float* cam64, uint32_t W, uint32_t H, float* albedo, float* normal_metal, float* position_rough,
+                       float* emission, float* props) {
+    raster_gbuffer(*(Scene*)h, cam64, W, H, albedo, normal_metal, position_rough, emission, props);
+    return 0;
+}
+void orc_unit_raster_vertex(const float* model16, const float* pos3, const float* normal3, const float* cam64, float* out10) {
+    unit_raster_vertex(model16, pos3, normal3, cam64, out10);
 }
 
 // the same on the rows y0 .. y1-1 only (full-size image; the other rows are left alone): full-resolution checks of a band

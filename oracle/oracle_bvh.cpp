@@ -331,7 +331,8 @@ void build_bvh8(Scene& s) {
         for (uint32_t k = 0; k < n; k++) bt.box[n - 1 + k] = tb[s.sorted_ids[k]];
         std::vector<uint32_t> order; std::vector<uint32_t> st{0};
         while (!st.empty()) { uint32_t nd = st.back(); st.pop_back(); order.push_back(nd);
-            if (!bt.is_leaf(bt.left[nd])) st.push_back(bt.left[nd]); if (!bt.is_leaf(bt.right[nd])) st.push_back(bt.right[nd]); }
+            if (!bt.is_leaf(bt.left[nd])) st.push_back(bt.left[nd]);
+            if (!bt.is_leaf(bt.right[nd])) st.push_back(bt.right[nd]); }
         for (size_t q = order.size(); q-- > 0;) bt.box[order[q]] = box_union(bt.box[bt.left[order[q]]], bt.box[bt.right[order[q]]]);
     } else if (n == 1) {
         bt.box[0] = tb[s.sorted_ids[0]];

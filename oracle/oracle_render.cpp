@@ -612,6 +612,143 @@ void gbuffer_rows(const Scene& s, int use_bvh, const float* cam, uint32_t W, uin
     }
 }
 
+// --------------------------------------------------------------------------------------------
+// Rasterised G-buffer variant: shaders/restir/gbuffer.vert:22-37 and gbuffer.frag:26-39 with the fixed-function rules this
+// repo states for them (no host code of the reference draws with these shaders): homogeneous edge functions over clip-space
+// (x, y, w) sampled at pixel centres, no culling, perspective-correct barycentrics lambda_i = E_i / (E_0 + E_1 + E_2), samples
+// with w <= 0 or depth z / w outside [0, 1] dropped, depth test LESS with ties to the lowest flat triangle id.  CPU twin of
+// raytracer_b200/csrc/rt_raster.cu: the same arithmetic in the same order, written independently.
+// --------------------------------------------------------------------------------------------
+struct RVert { V3 wp, wn; float cx, cy, cz, cw; };
+
+static void projView(const float* P, const float* V, float* PV) {  // (projection * view): GLSL multiplies left to right
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 4; r++)
+            PV[c * 4 + r] = ((P[0 * 4 + r] * V[c * 4 + 0] + P[1 * 4 + r] * V[c * 4 + 1]) + P[2 * 4 + r] * V[c * 4 + 2]) + P[3 * 4 + r] * V[c * 4 + 3];
+}
+
+// gbuffer.vert:22-37
+static RVert rasterVertex(const Object& o, const Vertex& v, const float* PV) {
+    RVert r;
+    V3 flippedPos = v3(v.pos[0], -v.pos[1], v.pos[2]);
+    V3 flippedNormal = v3(v.normal[0], -v.normal[1], v.normal[2]);
+    r.wp = xform_point(o.model, flippedPos);
+    r.wn = normalize(mul_nm(o.nrm, flippedNormal));
+    r.cx = ((PV[0] * r.wp.x + PV[4] * r.wp.y) + PV[8] * r.wp.z) + PV[12];
+    r.cy = ((PV[1] * r.wp.x + PV[5] * r.wp.y) + PV[9] * r.wp.z) + PV[13];
+    r.cz = ((PV[2] * r.wp.x + PV[6] * r.wp.y) + PV[10] * r.wp.z) + PV[14];
+    r.cw = ((PV[3] * r.wp.x + PV[7] * r.wp.y) + PV[11] * r.wp.z) + PV[15];
+    return r;
+}
+
+static bool rasterSample(const float a[3], const float b[3], const float c[3], const RVert v[3], uint32_t px, uint32_t py, uint32_t W,
+                         uint32_t H, float lambda[3], float* depth) {
+    const float X = (((float)px + 0.5f) / (float)W) * 2.0f - 1.0f;
+    const float Y = (((float)py + 0.5f) / (float)H) * 2.0f - 1.0f;
+    const float E0 = (a[0] * X + b[0] * Y) + c[0], E1 = (a[1] * X + b[1] * Y) + c[1], E2 = (a[2] * X + b[2] * Y) + c[2];
+    if (!((E0 >= 0.0f && E1 >= 0.0f && E2 >= 0.0f) || (E0 <= 0.0f && E1 <= 0.0f && E2 <= 0.0f))) return false;
+    const float S = (E0 + E1) + E2;
+    if (!(S != 0.0f)) return false;
+    lambda[0] = E0 / S; lambda[1] = E1 / S; lambda[2] = E2 / S;
+    const float w = (lambda[0] * v[0].cw + lambda[1] * v[1].cw) + lambda[2] * v[2].cw;
+    if (!(w > 0.0f)) return false;
+    const float z = (lambda[0] * v[0].cz + lambda[1] * v[1].cz) + lambda[2] * v[2].cz;
+    const float d = z / w;
+    if (!(d >= 0.0f && d <= 1.0f)) return false;
+    *depth = d;
+    return true;
+}
+
+static void rasterTriangle(const Scene& s, uint32_t flat, const float* PV, RVert v[3], float a[3], float b[3], float c[3]) {
+    const FlatTri& ft = s.tris[flat];
+    const Object& o = s.objects[ft.inst];
+    const Mesh& mesh = s.meshes[o.mesh_index];
+    for (int k = 0; k < 3; k++) v[k] = rasterVertex(o, mesh.v[mesh.idx[3 * ft.prim + k]], PV);
+    for (int i = 0; i < 3; i++) {
+        const RVert& p = v[(i + 1) % 3];
+        const RVert& q = v[(i + 2) % 3];
+        a[i] = p.cy * q.cw - p.cw * q.cy;
+        b[i] = p.cw * q.cx - p.cx * q.cw;
+        c[i] = p.cx * q.cy - p.cy * q.cx;
+    }
+}
+
+// out: five W*H*4 float images (albedo|1, normal|metallic, position|roughness, emission|isEmissive, roughness|metallic|isEmissive|0)
+void raster_gbuffer(const Scene& s, const float* cam, uint32_t W, uint32_t H, float* albedo, float* normal_metal, float* position_rough,
+                    float* emission, float* props) {
+    float PV[16];
+    projView(cam, cam + 16, PV);
+    std::vector<uint64_t> vis((size_t)W * H, ~0ull);
+    for (uint32_t flat = 0; flat < (uint32_t)s.tris.size(); flat++) {
+        RVert v[3];
+        float a[3], b[3], c[3];
+        rasterTriangle(s, flat, PV, v, a, b, c);
+        int x0 = 0, y0 = 0, x1 = (int)W - 1, y1 = (int)H - 1;  // conservative box: projected vertices when all lie in front
+        if (v[0].cw > 1e-6f && v[1].cw > 1e-6f && v[2].cw > 1e-6f) {
+            float lx = INFINITY, hx = -INFINITY, ly = INFINITY, hy = -INFINITY;
+            for (int k = 0; k < 3; k++) {
+                const float sx = (v[k].cx / v[k].cw * 0.5f + 0.5f) * (float)W, sy = (v[k].cy / v[k].cw * 0.5f + 0.5f) * (float)H;
+                lx = fminf(lx, sx); hx = fmaxf(hx, sx); ly = fminf(ly, sy); hy = fmaxf(hy, sy);
+            }
+            if (lx == lx && hx == hx && ly == ly && hy == hy) {
+                x0 = std::max(x0, (int)fmaxf(fminf(floorf(lx) - 2.0f, 1e9f), -1e9f)); y0 = std::max(y0, (int)fmaxf(fminf(floorf(ly) - 2.0f, 1e9f), -1e9f));
+                x1 = std::min(x1, (int)fmaxf(fminf(ceilf(hx) + 2.0f, 1e9f), -1e9f)); y1 = std::min(y1, (int)fmaxf(fminf(ceilf(hy) + 2.0f, 1e9f), -1e9f));
+            }
+        } else if (!(v[0].cw > 0.0f) && !(v[1].cw > 0.0f) && !(v[2].cw > 0.0f)) {
+            continue;  // entirely behind the eye: the interpolated w is never positive
+        }
+        for (int py = y0; py <= y1; py++)
+            for (int px = x0; px <= x1; px++) {
+                float l[3], depth;
+                if (!rasterSample(a, b, c, v, (uint32_t)px, (uint32_t)py, W, H, l, &depth)) continue;
+                const uint64_t key = ((uint64_t)f2u(depth) << 32) | flat;
+                uint64_t& dst = vis[(size_t)py * W + px];
+                if (key < dst) dst = key;
+            }
+    }
+    for (uint32_t py = 0; py < H; py++)
+        for (uint32_t px = 0; px < W; px++) {
+            const size_t i = (size_t)py * W + px;
+            float o[5][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}};
+            if (vis[i] != ~0ull) {
+                const uint32_t flat = (uint32_t)(vis[i] & 0xFFFFFFFFull);
+                RVert v[3];
+                float a[3], b[3], c[3], l[3] = {0.0f, 0.0f, 0.0f}, depth;
+                rasterTriangle(s, flat, PV, v, a, b, c);
+                rasterSample(a, b, c, v, px, py, W, H, l, &depth);
+                V3 inPos = (v[0].wp * l[0] + v[1].wp * l[1]) + v[2].wp * l[2];
+                V3 inNormal = (v[0].wn * l[0] + v[1].wn * l[1]) + v[2].wn * l[2];
+                const Material& m = s.materials[s.objects[s.tris[flat].inst].material_index];
+                // gbuffer.frag:26-39
+                V3 n = normalize(inNormal);
+                const float isEmissive = m.emission_power > 0.0f ? 1.0f : 0.0f;
+                o[0][0] = m.albedo[0]; o[0][1] = m.albedo[1]; o[0][2] = m.albedo[2]; o[0][3] = 1.0f;
+                o[1][0] = n.x; o[1][1] = n.y; o[1][2] = n.z; o[1][3] = m.metallic;
+                o[2][0] = inPos.x; o[2][1] = inPos.y; o[2][2] = inPos.z; o[2][3] = m.roughness;
+                o[3][0] = m.emission_power * m.emission_color[0]; o[3][1] = m.emission_power * m.emission_color[1];
+                o[3][2] = m.emission_power * m.emission_color[2]; o[3][3] = isEmissive;
+                o[4][0] = m.roughness; o[4][1] = m.metallic; o[4][2] = isEmissive; o[4][3] = 0.0f;
+            }
+            float* dst[5] = {albedo, normal_metal, position_rough, emission, props};
+            for (int k = 0; k < 5; k++)
+                if (dst[k]) memcpy(dst[k] + 4 * i, o[k], 16);
+        }
+}
+
+// the two programmable stages on their own, for the comparison with gbuffer_vert.spv / gbuffer_frag.spv (tools/spirv_golden.py)
+void unit_raster_vertex(const float* model16, const float* pos3, const float* normal3, const float* cam, float out[10]) {
+    Object o;
+    memcpy(o.model, model16, 64);
+    normal_matrix(o.model, o.nrm);
+    Vertex v;
+    memcpy(v.pos, pos3, 12); memcpy(v.normal, normal3, 12);
+    float PV[16];
+    projView(cam, cam + 16, PV);
+    RVert r = rasterVertex(o, v, PV);
+    out[0] = r.wp.x; out[1] = r.wp.y; out[2] = r.wp.z; out[3] = r.wn.x; out[4] = r.wn.y; out[5] = r.wn.z;
+    out[6] = r.cx; out[7] = r.cy; out[8] = r.cz; out[9] = r.cw;
+}
+
 // exported for unit tests of the BSDF pieces
 // --------------------------------------------------------------------------------------------
 // Ground truth for the ReSTIR DI path (the reference has no resampling algorithm to restate):

@@ -295,3 +295,53 @@ def test_the_fixture_is_what_the_binaries_compute(oracle_lib):
     a, b = z["conference/frames"], z["conference/frames_closest_commit"]
     d = (a.view(np.uint32) != b.view(np.uint32)).any(axis=3)
     assert 0 < d.sum() < 0.1 * d.size and (b[d][:, :3].sum(axis=1) >= a[d][:, :3].sum(axis=1) - 1e-6).mean() > 0.9
+
+
+def test_raster_gbuffer_stages_match_gbuffer_vert_and_frag_spv(oracle_lib):
+    """The two programmable stages of the rasterised G-buffer variant against the shipped gbuffer_vert.spv / gbuffer_frag.spv
+    (vectors in tests/golden/spirv_frames.npz): the oracle's vertex stage bit for bit — incl. (projection * view) as a matrix
+    product FIRST (OpMatrixTimesMatrix in the binary) and the y mirror of gbuffer.vert:24-25 — and the fragment outputs."""
+    z = _spirv_fixture()
+    L = oracle_lib.lib()
+    cam = np.ascontiguousarray(z["raster/camera"])
+    for k in range(len(z["raster/pos"])):
+        m, p, nrm = (np.ascontiguousarray(z[q][k]) for q in ("raster/models", "raster/pos", "raster/normal"))
+        out = np.zeros(10, np.float32)
+        L.orc_unit_raster_vertex(m.ctypes.data, p.ctypes.data, nrm.ctypes.data, cam.ctypes.data, out.ctypes.data)
+        assert np.array_equal(out.view(np.uint32), z["raster/vertex_out"][k].view(np.uint32)), k
+    mats, fo = z["raster/materials"], z["raster/fragment_out"]
+    v = z["raster/in_normal"]
+    inv = np.float32(1.0) / np.sqrt((v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1]) + v[:, 2] * v[:, 2])   # normalize of the contract
+    emissive = (mats[:, 6] > 0).astype(np.float32)
+    want = np.zeros_like(fo)
+    want[:, 0, :3], want[:, 0, 3] = mats[:, 0:3], 1.0
+    want[:, 1, :3], want[:, 1, 3] = v * inv[:, None], mats[:, 8]
+    want[:, 2, :3], want[:, 2, 3] = z["raster/in_pos"], mats[:, 7]
+    want[:, 3, :3], want[:, 3, 3] = mats[:, 6:7] * mats[:, 3:6], emissive
+    want[:, 4, 0], want[:, 4, 1], want[:, 4, 2] = mats[:, 7], mats[:, 8], emissive
+    assert np.array_equal(want.view(np.uint32), fo.view(np.uint32))
+    assert 0.2 < emissive.mean() < 0.8
+
+
+def test_raster_gbuffer_twin_agrees_with_the_ray_traced_gbuffer_on_a_mirrored_scene(oracle_lib):
+    """Sanity of the fixed-function rules this repo states for the raster variant: gbuffer.vert mirrors the geometry in y, so
+    rasterising a scene must show what the ray-traced G-buffer shows of the y-mirrored scene.  restir.rgen shoots through pixel
+    CORNERS; at twice the resolution the corners of the odd pixels are the centres the rasteriser samples, so the two passes
+    look at the same points: same coverage, same surface positions to float accuracy."""
+    scene = fixture_scene("cornell_pbr")
+    W = H = 96
+    cam = rb.Camera(position=(0.0, -1.0, 4.5), aspect=1.0, target=(0.0, -1.0, 0.0))
+    ras = oracle_lib.OracleScene(scene).raster_gbuffer(cam.ubo(), W, H)
+    mirrored = fixture_scene("cornell_pbr")
+    for m in mirrored.meshes:
+        m.vertices["pos"][:, 1] *= -1
+        m.vertices["normal"][:, 1] *= -1
+    # mirroring object space == mirroring the world only for objects whose model matrix commutes with the y flip; cornell_pbr's do
+    rt_img = {k: v[1::2, 1::2] for k, v in oracle_lib.OracleScene(mirrored).build_bvh().gbuffer(cam.ubo(), 2 * W, 2 * H).items()}
+    cov_r = ras["albedo"][..., 3] > 0
+    cov_t = rt_img["position_metal"][..., :3].any(axis=2)
+    assert (cov_r == cov_t).mean() > 0.995 and cov_r.mean() > 0.3
+    both = cov_r & cov_t
+    d = np.linalg.norm(ras["position_rough"][..., :3] - rt_img["position_metal"][..., :3], axis=2)[both]
+    assert np.percentile(d, 99) < 1e-3 and np.median(d) < 1e-5, (np.median(d), np.percentile(d, 99))
+    assert np.abs(ras["albedo"][..., :3][both] - rt_img["albedo"][..., :3][both] / 255.0).max(axis=1).mean() < 0.01

@@ -226,6 +226,55 @@ def unit_vectors(ref_dir, sincos, n=256, seed=7):
             "units/sampleBRDF": sample_out, "units/seed_out": seed_out, "units/evaluateFullBRDF": eval_out}
 
 
+def raster_stage_vectors(ref_dir, sincos, n=128, seed=11):
+    """gbuffer_vert.spv and gbuffer_frag.spv (shaders/restir/gbuffer.vert:22-37, gbuffer.frag:26-39) run on random inputs: the two
+    programmable stages of the rasterised G-buffer variant.  Inputs and what the binaries compute, as arrays."""
+    sh = os.path.join(ref_dir, "shaders", "restir")
+    vs = si.Machine(si.Module(os.path.join(sh, "gbuffer_vert.spv")), sincos)
+    fs = si.Machine(si.Module(os.path.join(sh, "gbuffer_frag.spv")), sincos)
+    import raytracer_b200 as rb
+
+    rng = np.random.default_rng(seed)
+    cam = rb.Camera(position=(0.3, 1.2, 4.0), target=(0.0, 0.8, 0.0), aspect=16 / 9).ubo()
+    camt = np.asarray(cam, np.float32).reshape(4, 16)
+    vs.vars["camera"].store([_mat4(camt[k]) for k in range(4)])
+    models = np.zeros((n, 16), np.float32)
+    pos = (rng.standard_normal((n, 3)) * 2).astype(np.float32)
+    nrm = rng.standard_normal((n, 3)).astype(np.float32)
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    vout = np.zeros((n, 10), np.float32)
+    for k in range(n):
+        m = rb.model_matrix_from_trs(rng.standard_normal(3), rng.uniform(-180, 180, 3), rng.uniform(0.3, 2.0, 3))
+        models[k] = m
+        cols = _mat4(m)
+        nm = si.inverse3([c[:3] for c in cols[:3]])                    # inverse(mat3(model)) ...
+        nm = [[nm[c][r] for c in range(3)] for r in range(3)]           # ... transposed: columns of the normal matrix
+        nm4 = [nm[0] + [F32(0)], nm[1] + [F32(0)], nm[2] + [F32(0)], [F32(0), F32(0), F32(0), F32(1)]]
+        vs.vars["push"].store([cols, nm4, 0])
+        vs.vars["aPos"].store(_vec(pos[k]))
+        vs.vars["aNormal"].store(_vec(nrm[k]))
+        vs.run()
+        vout[k] = list(vs.vars["outPos"].load()) + list(vs.vars["outNormal"].load()) + list(vs.vars[""].load()[0])
+    mats = np.zeros((n, 11), np.float32)
+    mats[:, 0:6] = rng.random((n, 6))
+    mats[:, 6] = np.where(rng.random(n) < 0.5, 0.0, rng.random(n) * 10)
+    mats[:, 7:9] = rng.random((n, 2))
+    in_pos = (rng.standard_normal((n, 3)) * 3).astype(np.float32)
+    in_nrm = (rng.standard_normal((n, 3))).astype(np.float32)
+    fout = np.zeros((n, 5, 4), np.float32)
+    fs.vars[""].store([[[_vec(m[0:3]), _vec(m[3:6]), F32(m[6]), F32(m[7]), F32(m[8]), F32(m[9]), F32(m[10])] for m in mats]])
+    for k in range(n):
+        fs.vars["push"].store([_mat4(np.eye(4, dtype=np.float32).reshape(16)), _mat4(np.eye(4, dtype=np.float32).reshape(16)), k])
+        fs.vars["inPos"].store(_vec(in_pos[k]))
+        fs.vars["inNormal"].store(_vec(in_nrm[k]))
+        fs.run()
+        for j, name in enumerate(("outAlbedo", "outNormal", "outPos", "outEmission", "outMaterialProps")):
+            o = list(fs.vars[name].load())
+            fout[k, j, :len(o)] = o
+    return {"raster/camera": np.asarray(cam, np.float32), "raster/models": models, "raster/pos": pos, "raster/normal": nrm, "raster/vertex_out": vout,
+            "raster/materials": mats, "raster/in_pos": in_pos, "raster/in_normal": in_nrm, "raster/fragment_out": fout}
+
+
 def make_sincos():
     from oracle import binding
 
@@ -294,11 +343,12 @@ def main():
             out[f"{name}/gbuffer/{k}"] = v
     t0 = time.time()
     out.update(unit_vectors(a.ref, sincos))
+    out.update(raster_stage_vectors(a.ref, sincos))
     print(f"function vectors: {len(out['units/wo'])} x (sampleBRDF, evaluateFullBRDF), {time.time() - t0:.1f} s", flush=True)
     out["clear"] = np.asarray(CLEAR, np.float32)
     if a.only_units:   # keep the frames of the existing fixture
         old = dict(np.load(a.out))
-        old.update({k: v for k, v in out.items() if k.startswith("units/")})
+        old.update({k: v for k, v in out.items() if k.startswith(("units/", "raster/"))})
         out = old
     np.savez_compressed(a.out, **out)
     print("wrote", a.out)

@@ -346,6 +346,18 @@ class Machine:
                             acc = acc + mtx[c][r] * vec[c]
                         out.append(acc)
                     v[a[1]] = out
+                elif op == 146:   # MatrixTimesMatrix: column c of the result = M1 x (column c of M2), summed left to right
+                    m1, m2 = val(a[2]), val(a[3])
+                    res = []
+                    for col in m2:
+                        out = []
+                        for r in range(len(m1[0])):
+                            acc = m1[0][r] * col[0] + m1[1][r] * col[1]
+                            for k in range(2, len(m1)):
+                                acc = acc + m1[k][r] * col[k]
+                            out.append(acc)
+                        res.append(out)
+                    v[a[1]] = res
                 elif op == 148:
                     v[a[1]] = dot(val(a[2]), val(a[3]))
                 elif op == 81:    # CompositeExtract
