@@ -1,22 +1,27 @@
 #!/usr/bin/env python
 """bench.py — Mrays/s and ms/frame of the path-tracing hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--inproc] [--balance cost|round_robin]
 
-Workload (config.workload): BASELINE.json configs[2] — Sponza 1920x1080, depth 8 (roulette from depth 3),
-one step = `--spp-per-step` accumulated frames (default 256 = the config's whole 256-spp image, traced as
-batches of as many frames in flight as the path-state arrays hold in 56 GiB: two batches of 128 at N = 1, all 256 at N >= 2).  The Sponza geometry blob is absent from the reference mount, so the scene is the
-deterministic "sponza-proxy" (raytracer_b200/proxy_scenes.py: same object/triangle/material counts).
-N > 1: screen tiles (8-row strips, rank r owns strip s when s % N == r), scene replicated, no
-collective on the data path; the strips are gathered over NCCL only for the end-to-end number.
+Workload (config.workload): BASELINE.json configs[2] — Sponza 1920x1080, depth 8 (roulette from depth 3), one step =
+`--spp-per-step` accumulated frames (default 256 = the config's whole 256-spp image, traced as batches of as many frames in
+flight as the path-state arrays hold in 56 GiB: four batches of 64 over two streams at N = 1, all 256 at once at N >= 2).
+The Sponza geometry blob is absent from the reference mount, so the scene is the deterministic "sponza-proxy"
+(raytracer_b200/proxy_scenes.py: same object/triangle/material counts).
+N > 1 (torchrun, one process per GPU): screen tiles — 8-row strips, dealt to the ranks by measured cost (the library's
+calibration pass, then measured-time feedback before the warm-up) — scene replicated, NO collective on the data path; for the
+end-to-end number every rank writes its strips into one pinned host frame the ranks share.  `--inproc`: the same N GPUs driven
+by ONE process through one multi-GPU rt_ctx (rt_config.device_ids), no torchrun.
 
-  value        Mrays/s (extend + visibility rays actually traced, from device counters of an identical untimed
-               pass) over K steps timed with CUDA events on the library's stream, inputs resident in HBM
-  e2e          the same through the C ABI with HOST buffers: camera UBO from host memory each step and the
-               RGBA32F image read back to (pinned) host memory each step
-  roofline     dominant kernel (wf_extend_coop_kernel: per-ray traversal of bounces >= 1): algorithmic bytes / its
-               CUDA-event time; roofline_packet: the same for the first-bounce packet kernel
-  cpu_baseline the CPU oracle (a port: the reference has no CPU path) on a bounded sample, rank 0, N = 1
+  value        Mrays/s (extend + visibility rays actually traced, from device counters of an identical untimed pass) over K
+               steps timed with CUDA events on the library's stream(s), inputs resident in HBM, max over ranks
+  e2e          the same through the C ABI with HOST buffers: camera UBO from host memory each step and the RGBA32F image
+               into pinned host memory each step
+  roofline     dominant kernel (wf_extend_coop_kernel: per-ray traversal of bounces >= 1): thread-loads of its BVH gather /
+               its CUDA-event time against the measured divergent-gather peak (profiles/gather_peaks.json); the byte model of
+               SURVEY §8d as roofline.hbm_bookkeeping; roofline_packet: the first-bounce packet kernel
+  verify       SHA-256 of a 16-frame image; at N > 1 also of the same image rendered on one GPU (must be equal)
+  cpu_baseline the CPU oracle (a port: the reference has no CPU path) on whole frames of the workload, rank 0, N = 1
   --impl reference   times that CPU port with all host threads (the reference's Vulkan path cannot run here)
 """
 from __future__ import annotations
