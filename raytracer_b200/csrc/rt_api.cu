@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "rt_internal.h"
@@ -16,17 +17,9 @@ using namespace rt;
 static thread_local std::string g_create_error;
 
 // Every entry point makes the context's device current (and leaves it current: documented in rt_api.h).
-#define CTX_CHECK_NOJOIN(ctx)                    \
+#define CTX_CHECK(ctx)                          \
     if (!(ctx)) return RT_ERR_INVALID_ARGUMENT; \
     if ((ctx)->children.empty()) cudaSetDevice((ctx)->device);
-// ... and, except for rt_trace_frames itself, first lets the context's stream catch up with the batch streams that earlier
-// rt_trace_frames calls may have left running (rt_join_streams)
-#define CTX_CHECK(ctx)                                                 \
-    CTX_CHECK_NOJOIN(ctx)                                              \
-    if ((ctx)->forked) {                                               \
-        const int _jrc = rt_join_streams(ctx);                         \
-        if (_jrc != RT_OK) return _jrc;                                \
-    }
 #define set_error ctx->set_error
 // Multi-GPU contexts (rt_config.n_devices >= 2) own one child per device; an entry point that simply applies to every
 // device runs `call` (an expression in `c`) on each child from the calling thread — all of them are stream-ordered, so
@@ -39,23 +32,6 @@ static thread_local std::string g_create_error;
         }                                                                   \
         return RT_OK;                                                       \
     }
-
-// Batches of consecutive rt_trace_frames calls keep alternating over the batch streams WITHOUT meeting on the context's stream in
-// between: a 256-frame step on an eighth of the image is two short batches, and draining the pipeline at the end of every call
-// cost ~3 % of the step at N = 8.  Whatever else touches the context joins first.
-int rt_join_streams(rt_ctx* ctx) {
-    if (!ctx->forked) return RT_OK;
-    ctx->forked = false;
-    ctx->batch_seq = 0;
-    for (int k = 0; k < RT_N_STREAMS - 1; k++) {
-        if (!ctx->streamx[k]) continue;
-        cudaError_t e = cudaEventRecord(ctx->ev_join[k], ctx->streamx[k]);
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ctx->ev_join[k], 0);
-        if (e != cudaSuccess) { ctx->error = std::string("rt_join_streams: ") + cudaGetErrorString(e); return RT_ERR_CUDA; }
-    }
-    if (ctx->timing_pending) cudaEventRecord(ctx->ev1, ctx->stream);  // the timed call ends when its last batch does
-    return RT_OK;
-}
 
 static bool create_side_streams(rt_ctx* ctx) {
     for (int k = 0; k < RT_N_STREAMS; k++)
@@ -798,15 +774,25 @@ int rt_resize(rt_ctx* ctx, uint32_t width, uint32_t height) {
 // Frames first_frame + k * frame_stride (k < n_frames) folded into the image as samples first_sample + k.
 static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const float clear_color[3], uint32_t first_frame,
                              uint32_t n_frames, uint32_t frame_stride, uint32_t first_sample) {
-    CTX_CHECK_NOJOIN(ctx);
-    FANOUT(ctx, trace_frames_impl(c, camera_ubo, clear_color, first_frame, n_frames, frame_stride, first_sample));
-    // anything that puts work on the context's own stream before the batches (table uploads, a rebuild or refit, the strip
-    // calibration, a reallocation) must see the batch streams finished first
-    if (ctx->forked && (ctx->tables_dirty || ctx->geometry_dirty || !ctx->refit_objects.empty() || (ctx->balance_pending && first_sample == 0u) ||
-                        (n_frames > 1u && ctx->lanes_for < ctx->cfg.frames_in_flight))) {
-        const int jrc = rt_join_streams(ctx);
-        if (jrc != RT_OK) return jrc;
+    CTX_CHECK(ctx);
+    if (ctx->children.size() > 1) {
+        // A frame is ~60 launches per device and batch; one thread queueing them device after device makes the last device start
+        // a few hundred microseconds after the first, which an end-to-end step (trace, then read back) pays in full.  One short-lived
+        // launcher thread per device queues them side by side; the caller still sees one synchronous call.
+        const size_t n = ctx->children.size();
+        std::vector<int> rcs(n, RT_OK);
+        std::vector<std::thread> launchers;
+        launchers.reserve(n);
+        for (size_t k = 0; k < n; k++)
+            launchers.emplace_back([&, k] {
+                rcs[k] = trace_frames_impl(ctx->children[k], camera_ubo, clear_color, first_frame, n_frames, frame_stride, first_sample);
+            });
+        for (std::thread& t : launchers) t.join();
+        for (size_t k = 0; k < n; k++)
+            if (rcs[k] != RT_OK) { ctx->error = ctx->children[k]->error; return rcs[k]; }
+        return RT_OK;
     }
+    FANOUT(ctx, trace_frames_impl(c, camera_ubo, clear_color, first_frame, n_frames, frame_stride, first_sample));
     if (!camera_ubo || !clear_color) { set_error("rt_trace_frame: null argument"); return RT_ERR_INVALID_ARGUMENT; }
     if (frame_stride == 0) { set_error("rt_trace_frames_sliced: frame_stride must be >= 1"); return RT_ERR_INVALID_ARGUMENT; }
     int rc = rt_flush_scene(ctx);
@@ -849,19 +835,13 @@ static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const floa
         set_error(std::string("rt_trace_frames: ") + cudaGetErrorString(e));
         return true;
     };
-    if (!multi && ctx->forked) {  // this call runs on the context's stream alone: after everything the batch streams hold
-        rc = rt_join_streams(ctx);
-        if (rc != RT_OK) return rc;
-    }
-    if (multi && !ctx->forked) {
+    if (multi) {
         if (cuda_fail(cudaEventRecord(ctx->ev_fork, ctx->stream))) return RT_ERR_CUDA;
         for (uint32_t k = 1; k < n_str; k++)
             if (cuda_fail(cudaStreamWaitEvent(ctx->streamx[k - 1], ctx->ev_fork, 0))) return RT_ERR_CUDA;
-        ctx->forked = true;
-        ctx->batch_seq = 0;
     }
-    for (uint32_t f = 0; f < n_frames;) {
-        const uint32_t b = multi ? ctx->batch_seq++ : 0u;  // the batch sequence runs on across calls while the streams stay forked
+    uint32_t b = 0;
+    for (uint32_t f = 0; f < n_frames; b++) {
         FrameParams fp;
         rt_fill_frame_params(ctx, camera_ubo, clear_color, first_frame + f * frame_stride, &fp);
         fp.frame_stride = frame_stride;
@@ -876,7 +856,12 @@ static int trace_frames_impl(rt_ctx* ctx, const float camera_ubo[64], const floa
         if (rc != RT_OK) { set_error(err); return rc; }
         f += fp.n_lanes;
     }
-    // no join here: the next rt_trace_frames call keeps feeding the batch streams; any other entry point joins (CTX_CHECK)
+    if (multi) {  // the context's stream continues once every side stream has finished its batches
+        for (uint32_t k = 1; k < n_str; k++)
+            if (cuda_fail(cudaEventRecord(ctx->ev_join[k - 1], ctx->streamx[k - 1])) ||
+                cuda_fail(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[k - 1], 0)))
+                return RT_ERR_CUDA;
+    }
     ctx->frames_traced += n_frames;
     rt_end_timing(ctx);
     return RT_OK;

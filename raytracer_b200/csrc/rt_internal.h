@@ -234,8 +234,6 @@ struct rt_ctx {
     // state, so that the tail of one batch's kernels (few blocks left, SMs idle) is filled by the next batch's
     rt::WavefrontBuffers* wfx[RT_N_STREAMS - 1] = {};    // path state of streams 1 .. RT_N_STREAMS - 1 (stream 0 uses wf)
     cudaStream_t streamx[RT_N_STREAMS - 1] = {};
-    bool forked = false;     // batch streams hold work the context's stream has not waited for yet (rt_join_streams)
-    uint32_t batch_seq = 0;  // index of the next batch in the alternation over the streams, running across rt_trace_frames calls
     cudaEvent_t ev_fork = nullptr, ev_join[RT_N_STREAMS - 1] = {}, ev_acc[RT_N_STREAMS] = {};
     // g-buffer images (allocated on first use)
     rt::DevBuf<uchar4> g_albedo, g_output;
@@ -269,7 +267,6 @@ struct rt_ctx {
 };
 
 // shared by the translation units behind the C ABI (rt_api.cu)
-int rt_join_streams(rt_ctx* ctx);
 int rt_flush_scene(rt_ctx* ctx);
 int rt_require_target(rt_ctx* ctx);
 rt::SceneView rt_scene_view(const rt_ctx* ctx);

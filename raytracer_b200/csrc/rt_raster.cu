@@ -219,7 +219,6 @@ int rt_raster_gbuffer(rt_ctx* ctx, const float camera_ubo[64]) {
         return rc0;
     }
     cudaSetDevice(ctx->device);
-    if (ctx->forked && rt_join_streams(ctx) != RT_OK) return RT_ERR_CUDA;
     if (!camera_ubo) { set_error("rt_raster_gbuffer: null camera"); return RT_ERR_INVALID_ARGUMENT; }
     int rc = rt_flush_scene(ctx);
     if (rc != RT_OK) return rc;
@@ -257,7 +256,6 @@ int rt_readback_raster_gbuffer(rt_ctx* ctx, float* albedo, float* normal_metal, 
         return rc0;
     }
     cudaSetDevice(ctx->device);
-    if (ctx->forked && rt_join_streams(ctx) != RT_OK) return RT_ERR_CUDA;
     if (!ctx->has_raster) { set_error("rt_readback_raster_gbuffer: nothing rasterised"); return RT_ERR_NO_TARGET; }
     const size_t bytes = (size_t)ctx->width * ctx->height * sizeof(float4);
     float* dst[5] = {albedo, normal_metal, position_rough, emission, props};

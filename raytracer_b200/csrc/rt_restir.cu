@@ -419,7 +419,6 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     }
     if (!ctx->children.empty()) return RT_OK;
     cudaSetDevice(ctx->device);
-    if (ctx->forked && rt_join_streams(ctx) != RT_OK) return RT_ERR_CUDA;
     if (!camera_ubo || !clear_color) { set_error("rt_restir_frame: null argument"); return RT_ERR_INVALID_ARGUMENT; }
     rt_restir_params prm;
     if (params) prm = *params; else rt_default_restir_params(&prm);
@@ -505,7 +504,6 @@ int rt_readback_reservoirs(rt_ctx* ctx, rt_reservoir* dst, size_t bytes) {
     }
     if (!ctx->children.empty()) return RT_OK;
     cudaSetDevice(ctx->device);
-    if (ctx->forked && rt_join_streams(ctx) != RT_OK) return RT_ERR_CUDA;
     if (!ctx->rs_history) { set_error("rt_readback_reservoirs: no ReSTIR frame traced"); return RT_ERR_NO_TARGET; }
     const size_t row = (size_t)ctx->width * sizeof(rt_reservoir);
     if (!dst || bytes < row * ctx->height) { set_error("rt_readback_reservoirs: destination too small"); return RT_ERR_INVALID_ARGUMENT; }
