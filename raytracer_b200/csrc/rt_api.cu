@@ -238,6 +238,9 @@ static int upload_tables(rt_ctx* ctx) {
     offs[no] = off;
     ctx->n_tris = off;
     ctx->n_lights = (uint32_t)lights.size();
+    ctx->light_tris.clear();
+    for (const DevLight& l : lights) ctx->light_tris.push_back(l.num_triangles);
+    ctx->tables_epoch++;
     RT_CUDA_TRY(ctx->d_objects.ensure(no));
     RT_CUDA_TRY(ctx->d_tri_offsets.ensure(no + 1));
     RT_CUDA_TRY(ctx->d_lights.ensure(lights.size()));

@@ -248,6 +248,12 @@ struct rt_ctx {
     // ReSTIR DI (rt_restir.cu): primary surfaces, this frame's reservoirs, the history
     rt::DevBuf<float4> rs_surf;
     rt::DevBuf<rt_reservoir> rs_cur, rs_hist[2];
+    // world-space light triangles for light_point (rt_restir.cu: LightTable), rebuilt when the scene tables change
+    rt::DevBuf<float4> rs_light_tris;
+    rt::DevBuf<uint4> rs_light_aux;
+    rt::DevBuf<uint32_t> rs_light_base;
+    uint32_t rs_light_epoch = 0, tables_epoch = 0;
+    std::vector<uint32_t> light_tris;  // triangle count of every light, in light order (host copy)
     rt::DevBuf<uint32_t> rs_rows;   // global rows passes 1 and 2 cover: own rows + halo (strip partitions only)
     uint32_t rs_n_rows = 0, rs_rows_halo = 0, rs_rows_epoch = 0;
     uint32_t band_epoch = 1;        // bumped whenever the strip table or the target changes

@@ -112,30 +112,63 @@ struct LightPoint {
     uint32_t object;
 };
 
-// (light, triangle, barycentrics) -> point; the reservoir stores exactly this triple
-__device__ __forceinline__ LightPoint light_point(const SceneView& sc, uint32_t light_idx, uint32_t tri, float bu, float bv) {
-    const DevLight* light = sc.lights + light_idx;
-    const uint32_t lobj = __ldg(&light->object_index);
+// World-space light triangles, flattened once per scene flush (light_table_kernel): a reservoir names a light point as
+// (light, triangle, barycentrics), and rebuilding it from the scene tables is a chain of five dependent loads (light -> object ->
+// indices -> vertices -> material) that the resolve kernel — which waits on memory, ncu r2f — walks up to five times per pixel.
+// Here it is two: aux[light] (32 B: first triangle, triangle count, object, Le) -> the triangle's record (64 B, two LDG.256:
+// three world-space vertices, unit normal, area).
+struct LightTable {
+    const float4* tris;  // 4 x float4 per light triangle: w0.xyz area | w1.xyz n.x | w2.xyz n.y | n.z - - -
+    const uint4* aux;    // 2 x uint4 per light: tri_base n_tris object - | Le.xyz -
+};
+
+__global__ void light_table_kernel(SceneView sc, const uint32_t* tri_base, float4* tris, uint4* aux) {
+    const uint32_t li = blockIdx.x;
+    const DevLight* light = sc.lights + li;
+    const uint32_t lobj = light->object_index, ntri = light->num_triangles;
     const DevObject* lo = sc.objects + lobj;
-    const uint32_t* ip = sc.indices + __ldg(&lo->index_base) + 3u * tri;
-    const rt_vertex* vb = sc.vertices + __ldg(&lo->vertex_base);
-    const vec3 p0 = vertex_pos(vb + __ldg(ip)), p1 = vertex_pos(vb + __ldg(ip + 1)), p2 = vertex_pos(vb + __ldg(ip + 2));
+    if (threadIdx.x == 0) {
+        const rt_material* lm = sc.materials + lo->material_index;
+        aux[2 * li] = make_uint4(tri_base[li], ntri, lobj, 0u);
+        aux[2 * li + 1] = make_uint4(__float_as_uint(lm->emission_color[0] * lm->emission_power), __float_as_uint(lm->emission_color[1] * lm->emission_power),
+                                     __float_as_uint(lm->emission_color[2] * lm->emission_power), 0u);
+    }
     float tr[12];
-#pragma unroll
-    for (int k = 0; k < 12; k++) tr[k] = __ldg(&light->transform[k]);
-    const vec3 w0 = xf_point(tr, p0), w1 = xf_point(tr, p1), w2 = xf_point(tr, p2);
+    for (int k = 0; k < 12; k++) tr[k] = light->transform[k];
+    for (uint32_t t = threadIdx.x; t < ntri; t += blockDim.x) {
+        const uint32_t* ip = sc.indices + lo->index_base + 3u * t;
+        const rt_vertex* vb = sc.vertices + lo->vertex_base;
+        const vec3 w0 = xf_point(tr, vertex_pos(vb + ip[0])), w1 = xf_point(tr, vertex_pos(vb + ip[1])), w2 = xf_point(tr, vertex_pos(vb + ip[2]));
+        const vec3 cr = cross3(sub3(w1, w0), sub3(w2, w0));
+        const vec3 n = normalize3(cr);
+        float4* dst = tris + 4 * (size_t)(tri_base[li] + t);
+        dst[0] = make_float4(w0.x, w0.y, w0.z, 0.5f * length3(cr));
+        dst[1] = make_float4(w1.x, w1.y, w1.z, n.x);
+        dst[2] = make_float4(w2.x, w2.y, w2.z, n.y);
+        dst[3] = make_float4(n.z, 0.0f, 0.0f, 0.0f);
+    }
+}
+
+// (light, triangle, barycentrics) -> point; the reservoir stores exactly this triple
+__device__ __forceinline__ LightPoint light_point(const LightTable& lt, uint32_t light_idx, uint32_t tri, float bu, float bv) {
+    const uint4 a0 = __ldg(lt.aux + 2 * light_idx), a1 = __ldg(lt.aux + 2 * light_idx + 1);
+    const uint4* tp = reinterpret_cast<const uint4*>(lt.tris + 4 * (size_t)(a0.x + tri));
+    uint4 q0, q1, q2, q3;
+    ldg256(tp, q0, q1);
+    ldg256(tp + 2, q2, q3);
+    const vec3 w0 = mk3(__uint_as_float(q0.x), __uint_as_float(q0.y), __uint_as_float(q0.z));
+    const vec3 w1 = mk3(__uint_as_float(q1.x), __uint_as_float(q1.y), __uint_as_float(q1.z));
+    const vec3 w2 = mk3(__uint_as_float(q2.x), __uint_as_float(q2.y), __uint_as_float(q2.z));
     const float bw = (1.0f - bu) - bv;
     LightPoint lp;
     lp.y = add3(add3(scale3(w0, bu), scale3(w1, bv)), scale3(w2, bw));
-    const vec3 cr = cross3(sub3(w1, w0), sub3(w2, w0));
-    lp.area = 0.5f * length3(cr);
-    lp.n = normalize3(cr);
-    const rt_material* lm = sc.materials + __ldg(&lo->material_index);
-    lp.Le = scale3(mk3(__ldg(&lm->emission_color[0]), __ldg(&lm->emission_color[1]), __ldg(&lm->emission_color[2])),
-                   __ldg(&lm->emission_power));
-    lp.object = lobj;
+    lp.area = __uint_as_float(q0.w);
+    lp.n = mk3(__uint_as_float(q1.w), __uint_as_float(q2.w), __uint_as_float(q3.x));
+    lp.Le = mk3(__uint_as_float(a1.x), __uint_as_float(a1.y), __uint_as_float(a1.z));
+    lp.object = a0.z;
     return lp;
 }
+__device__ __forceinline__ uint32_t light_num_triangles(const LightTable& lt, uint32_t light_idx) { return __ldg(lt.aux + 2 * light_idx).y; }
 
 // unshadowed contribution f Le cos_x cos_y / d^2 of a light point at a surface; zero when either side faces away
 __device__ __forceinline__ vec3 unshadowed(const SceneView& sc, const RSurf& s, const Basis& basis, const vec3 wo_l, const Mat& mat,
@@ -175,9 +208,9 @@ __device__ __forceinline__ SurfShade prepare_surface(const SceneView& sc, const 
     }
     return ss;
 }
-__device__ __forceinline__ bool reservoir_sample_valid(const SceneView& sc, const rt_reservoir& r) {
+__device__ __forceinline__ bool reservoir_sample_valid(const SceneView& sc, const LightTable& lt, const rt_reservoir& r) {
     if (r.light_index >= sc.n_lights) return false;
-    return __float_as_uint(r.distance) < __ldg(&sc.lights[r.light_index].num_triangles);
+    return __float_as_uint(r.distance) < light_num_triangles(lt, r.light_index);
 }
 // target function of a light point that has already been reconstructed (the same sample judged at several surfaces)
 __device__ __forceinline__ float target_of_point(const SceneView& sc, const SurfShade& ss, const LightPoint& lp) {
@@ -185,13 +218,25 @@ __device__ __forceinline__ float target_of_point(const SceneView& sc, const Surf
     const float p = luminance(unshadowed(sc, ss.s, ss.basis, ss.wo_l, ss.mat, lp));
     return (p > 0.0f && p == p && !is_inf1(p)) ? p : 0.0f;
 }
-__device__ __forceinline__ float target_of(const SceneView& sc, const SurfShade& ss, const rt_reservoir& r) {
-    if (!reservoir_sample_valid(sc, r)) return 0.0f;
-    return target_of_point(sc, ss, light_point(sc, r.light_index, __float_as_uint(r.distance), r.uv[0], r.uv[1]));
+// Is the target function of `lp` positive at surface `s`?  Same conditions as unshadowed() / target_of_point() — not the light
+// itself, a proper distance and area, the point above the surface's horizon (wi.z > 1e-4: the basis' z axis is N) and the
+// surface on an emitting side of the light — without evaluating the BSDF: f > 0 whenever both cosines are (the GGX term never
+// vanishes for alpha >= 0.02 and N faces the viewer by construction).  The 1/Z normalisation only needs the sign.
+__device__ __forceinline__ bool target_positive(const RSurf& s, const LightPoint& lp) {
+    if (lp.object == s.inst) return false;
+    const vec3 to = sub3(lp.y, s.pos);
+    const float d2 = dot3(to, to);
+    if (!(d2 > 1e-12f) || !(lp.area > 0.0f)) return false;
+    const vec3 wi_w = div3(to, sqrtf(d2));
+    return dot3(s.N, wi_w) > 1e-4f && fabsf(dot3(lp.n, wi_w)) > 1e-6f;
+}
+__device__ __forceinline__ float target_of(const SceneView& sc, const LightTable& lt, const SurfShade& ss, const rt_reservoir& r) {
+    if (!reservoir_sample_valid(sc, lt, r)) return 0.0f;
+    return target_of_point(sc, ss, light_point(lt, r.light_index, __float_as_uint(r.distance), r.uv[0], r.uv[1]));
 }
 
 // ---- pass 2: initial candidates (RIS) + temporal reuse ---------------------------------------------------
-__global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, FrameParams fp, rt_restir_params prm,
+__global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, LightTable lt, FrameParams fp, rt_restir_params prm,
                                                                 const uint32_t* rows, uint32_t n_rows, const float4* surf,
                                                                 const rt_reservoir* prev, rt_reservoir* out, DevCounters* counters) {
     const uint32_t n_px = n_rows * fp.width;
@@ -224,13 +269,13 @@ __global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, Fr
                 }
                 const float ut = rnd01(seed), q1 = rnd01(seed), q2 = rnd01(seed), uu = rnd01(seed);
                 if (sel == 0xFFFFFFFFu) continue;
-                const uint32_t ntri = __ldg(&sc.lights[sel].num_triangles);
+                const uint32_t ntri = light_num_triangles(lt, sel);
                 if (ntri == 0u) continue;  // a light whose mesh is empty has no point to sample
                 uint32_t tri = (uint32_t)(ut * (float)ntri);
                 if (tri > ntri - 1u) tri = ntri - 1u;
                 const float sq = sqrtf(q1);
                 const float bu = 1.0f - sq, bv = sq * (1.0f - q2);  // uniform point, simple.rchit:262-270
-                const LightPoint lp = light_point(sc, sel, tri, bu, bv);
+                const LightPoint lp = light_point(lt, sel, tri, bu, bv);
                 c_nee++;
                 if (!(lp.area > 0.0f)) continue;
                 const float src_pdf = ((wsel / total) / (float)ntri) / lp.area;  // area measure
@@ -251,7 +296,7 @@ __global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, Fr
             if (rp.M > 0u) {
                 const uint32_t cap = prm.history_cap * (M ? M : 1u);
                 const uint32_t Mp = rp.M < cap ? rp.M : cap;
-                const float pp = target_of(sc, ss, rp);
+                const float pp = target_of(sc, lt, ss, rp);
                 const float w = pp * rp.W * (float)Mp;
                 const float uu = rnd01(seed);
                 if (w > 0.0f && !is_inf1(w)) {
@@ -286,7 +331,7 @@ __global__ void __launch_bounds__(128) restir_candidates_kernel(SceneView sc, Fr
 #ifndef RT_RESOLVE_MIN_BLOCKS
 #define RT_RESOLVE_MIN_BLOCKS 4  /* 128 registers, no spills: 2.015 -> 1.886 ms/frame (3 blocks x 152 registers before) */
 #endif
-__global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_kernel(SceneView sc, FrameParams fp, rt_restir_params prm, const float4* surf,
+__global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_kernel(SceneView sc, LightTable lt, FrameParams fp, rt_restir_params prm, const float4* surf,
                                                              const rt_reservoir* in, rt_reservoir* out, float4* image,
                                                              DevCounters* counters) {
     const uint32_t n_px = fp.local_rows * fp.width;
@@ -332,7 +377,7 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
                     if (rq.M == 0u) continue;
                     nb[n_nb++] = qpx;
                     M += rq.M;
-                    const float pq = target_of(sc, ss, rq);  // the neighbour's sample, judged at THIS surface
+                    const float pq = target_of(sc, lt, ss, rq);  // the neighbour's sample, judged at THIS surface
                     const float w = pq * rq.W * (float)rq.M;
                     if (w > 0.0f && !is_inf1(w)) {
                         wsum += w;
@@ -344,13 +389,11 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
                 }
                 // 1/Z: count the sources that could have produced the winner (their own target function is > 0 there)
                 float Z = (sel_p > 0.0f) ? (float)res.M : 0.0f;
-                if (sel_p > 0.0f && reservoir_sample_valid(sc, res)) {  // one light point for all sources (an invalid sample has target 0 everywhere)
-                    lpw = light_point(sc, res.light_index, __float_as_uint(res.distance), res.uv[0], res.uv[1]);
+                if (sel_p > 0.0f && reservoir_sample_valid(sc, lt, res)) {  // one light point for all sources (an invalid sample has target 0 everywhere)
+                    lpw = light_point(lt, res.light_index, __float_as_uint(res.distance), res.uv[0], res.uv[1]);
                     have_lpw = true;
-                    for (uint32_t k = 0; k < n_nb; k++) {
-                        const SurfShade qs = prepare_surface(sc, surf, nb[k]);
-                        if (target_of_point(sc, qs, lpw) > 0.0f) Z += (float)in[nb[k]].M;
-                    }
+                    for (uint32_t k = 0; k < n_nb; k++)
+                        if (target_positive(load_surf(surf, nb[k]), lpw)) Z += (float)in[nb[k]].M;
                 }
                 res.M = M;
                 res.weight_sum = wsum;
@@ -359,8 +402,8 @@ __global__ void __launch_bounds__(128, RT_RESOLVE_MIN_BLOCKS) restir_resolve_ker
                 if (!(res.W == res.W) || is_inf1(res.W)) res.W = 0.0f;
             }
             // shading: f Le G V W for the surviving sample, one visibility ray (isVisibleRQ, simple.rchit:350-385)
-            if (res.W > 0.0f && reservoir_sample_valid(sc, res)) {
-                const LightPoint lp = have_lpw ? lpw : light_point(sc, res.light_index, __float_as_uint(res.distance), res.uv[0], res.uv[1]);
+            if (res.W > 0.0f && reservoir_sample_valid(sc, lt, res)) {
+                const LightPoint lp = have_lpw ? lpw : light_point(lt, res.light_index, __float_as_uint(res.distance), res.uv[0], res.uv[1]);
                 const vec3 c = scale3(unshadowed(sc, ss.s, ss.basis, ss.wo_l, ss.mat, lp), res.W);
                 const vec3 tl = normalize3(sub3(lp.y, ss.s.pos));
                 const vec3 from = add3(ss.s.pos, scale3(scale3(ss.s.N, 0.001f), sign1(dot3(ss.s.N, tl))));
@@ -471,6 +514,21 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     rt_fill_frame_params(ctx, camera_ubo, clear_color, frame_number, &fp);
     const rt::SceneView sc = rt_scene_view(ctx);
     rt::DevCounters* cnt = (ctx->cfg.flags & RT_FLAG_COUNTERS) ? ctx->counters.p : nullptr;
+    if (ctx->rs_light_epoch != ctx->tables_epoch) {  // the light tables changed (build, material / object / transform edit): flatten again
+        const uint32_t L = ctx->n_lights;
+        std::vector<uint32_t> base(L + 1, 0u);
+        for (uint32_t i = 0; i < L; i++) base[i + 1] = base[i] + ctx->light_tris[i];
+        RT_CUDA_TRY(ctx->rs_light_base.ensure(L + 1));
+        RT_CUDA_TRY(ctx->rs_light_tris.ensure((size_t)base[L] * 4));
+        RT_CUDA_TRY(ctx->rs_light_aux.ensure((size_t)L * 2));
+        RT_CUDA_TRY(cudaMemcpyAsync(ctx->rs_light_base.p, base.data(), (L + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+        if (L) rt::light_table_kernel<<<L, 128, 0, ctx->stream>>>(sc, ctx->rs_light_base.p, ctx->rs_light_tris.p, ctx->rs_light_aux.p);
+        RT_CUDA_TRY(cudaGetLastError());
+        RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));  // `base` is on this stack frame
+        ctx->rs_light_epoch = ctx->tables_epoch;
+        ctx->launches++;
+    }
+    const rt::LightTable lt{ctx->rs_light_tris.p, ctx->rs_light_aux.p};
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
     const uint32_t grid = (uint32_t)std::min<size_t>(((size_t)n_rows * ctx->width + 127) / 128, (size_t)sms * 32);
@@ -483,8 +541,8 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     rt_reservoir* temporal = ctx->rs_hist[ctx->rs_flip ^ 1].p;
     rt_begin_timing(ctx);
     rt::restir_surface_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, d_rows, n_rows, ctx->rs_surf.p, cnt);
-    rt::restir_candidates_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, prm, d_rows, n_rows, ctx->rs_surf.p, prev, temporal, cnt);
-    rt::restir_resolve_kernel<<<grid3, 128, 0, ctx->stream>>>(sc, fp, prm, ctx->rs_surf.p, temporal, ctx->rs_cur.p, ctx->image.p, cnt);
+    rt::restir_candidates_kernel<<<grid, 128, 0, ctx->stream>>>(sc, lt, fp, prm, d_rows, n_rows, ctx->rs_surf.p, prev, temporal, cnt);
+    rt::restir_resolve_kernel<<<grid3, 128, 0, ctx->stream>>>(sc, lt, fp, prm, ctx->rs_surf.p, temporal, ctx->rs_cur.p, ctx->image.p, cnt);
     rt_end_timing(ctx);
     RT_CUDA_TRY(cudaGetLastError());
     ctx->launches += 3;
