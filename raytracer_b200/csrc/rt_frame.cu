@@ -1193,6 +1193,87 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     return RT_OK;
 }
 
+// ---- primary visibility through pixel CORNERS (restir.rgen:47-57) with the packet kernel ---------------------------------------
+// The ReSTIR surface pass shoots one un-jittered ray per pixel: as coherent as the path tracer's first bounce, so it goes through
+// the same 128-ray packets (hand-backs through the cooperative kernel) instead of one BVH walk per ray.  Slot i = (index in the row
+// list) * width + x; hit records land in the wavefront state's hit array.
+__global__ void __launch_bounds__(256) corner_raygen_kernel(FrameParams fp, const uint32_t* rows, uint32_t n_rows, WfView wf) {
+    const uint32_t n = n_rows * fp.width;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t r = i / fp.width, x = i - r * fp.width;
+        const uint32_t y = rows ? __ldg(rows + r) : r;
+        vec3 o, d;
+        camera_ray(fp, (float)x, (float)y, false, &o, &d);  // pixel corner, direction not re-normalised
+        wf.ray_o[i] = make_float4(o.x, o.y, o.z, 0.0f);
+        wf.ray_d[i] = make_float4(d.x, d.y, d.z, 0.0f);
+    }
+}
+
+// the same rays one per thread (a strip context whose halo covers more rows than its wavefront state has slots for, and
+// RT_FLAG_PER_RAY_PRIMARY): the same traversal code under the same arithmetic contract, hence the same hit records bit for bit
+template <bool COUNT>
+__global__ void __launch_bounds__(128) corner_hits_per_ray_kernel(SceneView sc, FrameParams fp, const uint32_t* rows, uint32_t n_rows, uint4* hits,
+                                                                  DevCounters* counters) {
+    const uint32_t n = n_rows * fp.width;
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t r = i / fp.width, x = i - r * fp.width;
+        const uint32_t y = rows ? __ldg(rows + r) : r;
+        vec3 o, d;
+        camera_ray(fp, (float)x, (float)y, false, &o, &d);
+        c_rays++;
+        const Hit h = traverse<false, COUNT>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, c_nodes, c_tris);
+        hits[i] = make_uint4(__float_as_uint(h.u), __float_as_uint(h.v), h.id == 0xFFFFFFFFu ? 0xFFFFFFFFu : h.inst, h.prim);
+    }
+    if (COUNT) {
+        warp_add(&counters->extend_rays, c_rays);
+        warp_add(&counters->nodes, c_nodes);
+        warp_add(&counters->tris, c_tris);
+    }
+}
+
+template <bool COUNT>
+static int corner_hits_t(const SceneView& sc, const FrameParams& fp, FrameResources& res, const uint32_t* d_rows, uint32_t n_rows,
+                         uint4* own_hits, cudaStream_t stream, std::string& err, const uint4** hits) {
+    WavefrontBuffers* w = res.wf;
+    const uint32_t n = n_rows * fp.width;
+    if (n == 0) { *hits = own_hits; return RT_OK; }
+    if (!w || w->n_slots < n || (fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
+        if (!own_hits) { err = "corner pass: no hit buffer"; return RT_ERR_NO_TARGET; }
+        int sms = res.dims && res.dims->num_sms ? res.dims->num_sms : query_num_sms();
+        corner_hits_per_ray_kernel<COUNT><<<std::min<uint32_t>((n + 127) / 128, (uint32_t)sms * 32), 128, 0, stream>>>(sc, fp, d_rows, n_rows, own_hits,
+                                                                                                                  res.counters);
+        FRAME_TRY(cudaGetLastError());
+        if (res.launches) *res.launches += 1;
+        *hits = own_hits;
+        return RT_OK;
+    }
+    WfView v;
+    v.ray_o = w->ray_o.p; v.ray_d = w->ray_d.p; v.thr = w->thr.p; v.col = w->col.p;
+    v.seeds = w->seeds.p; v.hit = w->hit.p; v.sh_o = w->sh_o.p; v.sh_d = w->sh_d.p; v.sh_c = w->sh_c.p; v.sh_e = w->sh_e.p; v.sh_n = w->sh_n.p;
+    v.ctrl = w->ctrl.p;
+    LaunchDims local_dims;
+    LaunchDims& dims = res.dims ? *res.dims : local_dims;
+    if (!dims.num_sms) dims.num_sms = query_num_sms();
+    const int g_pkt = persistent_grid(wf_extend_packet_kernel<COUNT>, 128, dims.num_sms), g_coop = persistent_grid(wf_extend_coop_kernel<COUNT>, 128, dims.num_sms);
+    const int need = (int)((n + 127) / 128);
+    corner_raygen_kernel<<<std::min<uint32_t>((n + 255) / 256, (uint32_t)dims.num_sms * 16), 256, 0, stream>>>(fp, d_rows, n_rows, v);
+    wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, 0u, n);
+    wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, fp, v, w->queue[0].p, fp.width, n, res.counters);
+    wf_extend_coop_kernel<COUNT><<<std::min(g_coop, need), 128, 0, stream>>>(sc, v, w->queue[0].p, CT_FB, fp.width, n, res.counters);
+    FRAME_TRY(cudaGetLastError());
+    if (res.launches) *res.launches += 4;
+    *hits = w->hit.p;
+    return RT_OK;
+}
+
+int launch_corner_hits(const SceneView& sc, const FrameParams& fp, FrameResources& res, const uint32_t* d_rows, uint32_t n_rows,
+                       uint4* own_hits, cudaStream_t stream, std::string& err, const uint4** hits) {
+    return (fp.flags & RT_FLAG_COUNTERS) ? corner_hits_t<true>(sc, fp, res, d_rows, n_rows, own_hits, stream, err, hits)
+                                         : corner_hits_t<false>(sc, fp, res, d_rows, n_rows, own_hits, stream, err, hits);
+}
+uint32_t wavefront_slots(const WavefrontBuffers* w) { return w ? w->n_slots : 0u; }
+
 int launch_frame_wavefront(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
                            std::string& err) {
     return (fp.flags & RT_FLAG_COUNTERS) ? frame_wavefront_t<true>(sc, fp, res, stream, err)

@@ -160,6 +160,12 @@ int wavefront_alloc(WavefrontBuffers** wf, uint32_t n_pixels, std::string& err);
 void wavefront_free(WavefrontBuffers* wf);
 int launch_frame_wavefront(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
                            std::string& err);
+// closest hits of one un-jittered ray per pixel CORNER of the listed rows (restir.rgen:47-57): through the packet kernel into the
+// wavefront state's hit array when that has a slot per ray, else one ray per thread into own_hits.  *hits = where they are,
+// slot = row-list index * width + x: {u bits, v bits, instance (0xFFFFFFFF = miss), primitive}.  Same records either way.
+int launch_corner_hits(const SceneView& sc, const FrameParams& fp, FrameResources& res, const uint32_t* d_rows, uint32_t n_rows,
+                       uint4* own_hits, cudaStream_t stream, std::string& err, const uint4** hits);
+uint32_t wavefront_slots(const WavefrontBuffers* w);
 int launch_frame_megakernel(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
                             std::string& err);
 // strip-cost calibration (RT_BALANCE_COST): one path per pixel of the FULL frame `fp` describes (strip_count must be 1 in
@@ -254,6 +260,7 @@ struct rt_ctx {
     rt::DevBuf<uint32_t> rs_light_base;
     uint32_t rs_light_epoch = 0, tables_epoch = 0;
     std::vector<uint32_t> light_tris;  // triangle count of every light, in light order (host copy)
+    rt::DevBuf<uint4> rs_hits;      // primary hits of the surface pass when the wavefront state cannot hold them
     rt::DevBuf<uint32_t> rs_rows;   // global rows passes 1 and 2 cover: own rows + halo (strip partitions only)
     uint32_t rs_n_rows = 0, rs_rows_halo = 0, rs_rows_epoch = 0;
     uint32_t band_epoch = 1;        // bumped whenever the strip table or the target changes

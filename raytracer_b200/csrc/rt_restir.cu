@@ -53,8 +53,9 @@ __device__ __forceinline__ float luminance(vec3 c) { return dot3(c, mk3(0.2126f,
 // from the rank that owns it ("recompute G-buffer + candidates for the halo rows locally (no comms)").  Every value
 // of a pixel depends on its GLOBAL coordinates only, so two ranks that both process a row get the same bits, and the image
 // does not depend on how many ranks share the frame.  All per-pixel arrays of this file are indexed by global pixel.
+// the closest hits come from rt_frame.cu (launch_corner_hits: the contract's traversal); this kernel only shades them
 __global__ void __launch_bounds__(128) restir_surface_kernel(SceneView sc, FrameParams fp, const uint32_t* rows, uint32_t n_rows,
-                                                             float4* surf, DevCounters* counters) {
+                                                             const uint4* hits, float4* surf, DevCounters* counters) {
     const uint32_t n_px = n_rows * fp.width;
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_px; i += gridDim.x * blockDim.x) {
@@ -63,8 +64,12 @@ __global__ void __launch_bounds__(128) restir_surface_kernel(SceneView sc, Frame
         const uint32_t px = y * fp.width + x;
         vec3 o, d;
         camera_ray(fp, (float)x, (float)y, false, &o, &d);  // pixel corner, direction not re-normalised
-        c_rays++;
-        const Hit h = traverse<false, true>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, c_nodes, c_tris);
+        Hit h;
+        {
+            const uint4 hr = hits[i];
+            h.t = 0.0f; h.u = __uint_as_float(hr.x); h.v = __uint_as_float(hr.y); h.inst = hr.z; h.prim = hr.w;
+            h.id = hr.z == 0xFFFFFFFFu ? 0xFFFFFFFFu : 0u;
+        }
         float4 a = make_float4(0.f, 0.f, 0.f, __uint_as_float(0xFFFFFFFFu)), b = make_float4(0.f, 0.f, 0.f, 0.f),
                c = make_float4(0.f, 0.f, 0.f, 0.f);
         if (h.id != 0xFFFFFFFFu) {
@@ -540,7 +545,22 @@ int rt_restir_frame(rt_ctx* ctx, const float camera_ubo[64], const float clear_c
     const rt_reservoir* prev = ctx->rs_history ? ctx->rs_hist[ctx->rs_flip].p : nullptr;
     rt_reservoir* temporal = ctx->rs_hist[ctx->rs_flip ^ 1].p;
     rt_begin_timing(ctx);
-    rt::restir_surface_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, d_rows, n_rows, ctx->rs_surf.p, cnt);
+    // primary visibility: rt_frame.cu finds the hits (packets when the wavefront state has a slot per covered pixel — always with
+    // one context per frame — else one ray per thread); both under the arithmetic contract, so every context gets the same records
+    const uint4* hits = nullptr;
+    {
+        const bool packets = ctx->wf && rt::wavefront_slots(ctx->wf) >= (size_t)n_rows * ctx->width && !(ctx->cfg.flags & RT_FLAG_PER_RAY_PRIMARY);
+        if (!packets) RT_CUDA_TRY(ctx->rs_hits.ensure((size_t)n_rows * ctx->width));
+        rt::FrameResources fr;
+        fr.dims = &ctx->dims;
+        fr.counters = ctx->counters.p;
+        fr.wf = ctx->wf;
+        fr.launches = &ctx->launches;
+        std::string err;
+        rc = rt::launch_corner_hits(sc, fp, fr, d_rows, n_rows, packets ? nullptr : ctx->rs_hits.p, ctx->stream, err, &hits);
+        if (rc != RT_OK) { set_error(err); return rc; }
+    }
+    rt::restir_surface_kernel<<<grid, 128, 0, ctx->stream>>>(sc, fp, d_rows, n_rows, hits, ctx->rs_surf.p, cnt);
     rt::restir_candidates_kernel<<<grid, 128, 0, ctx->stream>>>(sc, lt, fp, prm, d_rows, n_rows, ctx->rs_surf.p, prev, temporal, cnt);
     rt::restir_resolve_kernel<<<grid3, 128, 0, ctx->stream>>>(sc, lt, fp, prm, ctx->rs_surf.p, temporal, ctx->rs_cur.p, ctx->image.p, cnt);
     rt_end_timing(ctx);
