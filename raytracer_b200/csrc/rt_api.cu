@@ -1347,6 +1347,19 @@ int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t 
     if (morton && ctx->n_tris) RT_CUDA_TRY(cudaMemcpyAsync(morton, ctx->bvh.morton.p, (size_t)ctx->n_tris * 8, cudaMemcpyDeviceToHost, ctx->stream));
     if (sorted_ids && ctx->n_tris) RT_CUDA_TRY(cudaMemcpyAsync(sorted_ids, ctx->bvh.sorted_ids.p, (size_t)ctx->n_tris * 4, cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    if (nodes) {  // device nodes keep their 32-byte chunks rotated by the node index (rt_types.cuh); callers get struct Node8
+        Node8* hn = static_cast<Node8*>(nodes);
+        for (uint32_t k = 0; k < ctx->bvh.n_nodes; k++) {
+            Node8 raw = hn[k];
+            const uint4* src = reinterpret_cast<const uint4*>(&raw);
+            uint4* dst = reinterpret_cast<uint4*>(&hn[k]);
+            for (uint32_t c = 0; c < 4u; c++) {
+                const uint32_t at = node_chunk(k, c);
+                dst[2u * c] = src[at];
+                dst[2u * c + 1u] = src[at + 1u];
+            }
+        }
+    }
     return RT_OK;
 }
 

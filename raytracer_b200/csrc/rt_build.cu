@@ -441,6 +441,28 @@ __device__ __forceinline__ void quantize_axis(float lo, float hi, int* e_out, fl
     *p_out = lo - scale;
 }
 
+// A node in memory: its four 32-byte chunks rotated by the node index (rt_types.cuh: node_chunk).
+__device__ __forceinline__ void store_node(Node8* nodes, uint32_t idx, const Node8& nd) {
+    const uint4* src = reinterpret_cast<const uint4*>(&nd);
+    uint4* dst = reinterpret_cast<uint4*>(nodes + idx);
+#pragma unroll
+    for (uint32_t c = 0; c < 4u; c++) {
+        const uint32_t at = node_chunk(idx, c);
+        dst[at] = src[2u * c];
+        dst[at + 1u] = src[2u * c + 1u];
+    }
+}
+__device__ __forceinline__ void fetch_node(const Node8* nodes, uint32_t idx, Node8& nd) {
+    const uint4* src = reinterpret_cast<const uint4*>(nodes + idx);
+    uint4* dst = reinterpret_cast<uint4*>(&nd);
+#pragma unroll
+    for (uint32_t c = 0; c < 4u; c++) {
+        const uint32_t at = node_chunk(idx, c);
+        dst[2u * c] = src[at];
+        dst[2u * c + 1u] = src[at + 1u];
+    }
+}
+
 // 6b. emit the level's nodes, its leaf triangles and the next level's node list.
 // n_int / n_tri hold exclusive prefix sums over the level.
 __global__ void emit_kernel(TreeView bt, const uint32_t* level, uint32_t n_level, const uint32_t* child_slots,
@@ -504,10 +526,7 @@ __global__ void emit_kernel(TreeView bt, const uint32_t* level, uint32_t n_level
             tri_off += cn;
         }
     }
-    const uint4* src = reinterpret_cast<const uint4*>(&nd);
-    uint4* dst = reinterpret_cast<uint4*>(nodes + level_first + w);
-#pragma unroll
-    for (int k = 0; k < (int)RT_NODE_WORDS; k++) dst[k] = src[k];
+    store_node(nodes, level_first + w, nd);
     if (w == n_level - 1) {  // level totals for the host loop
         scratch->level_int = int_prefix[w] + n_int;
         scratch->level_tris = tri_prefix[w] + tri_off;
@@ -687,7 +706,8 @@ __global__ void refit_level_kernel(Node8* nodes, const float4* btris, float4* no
                                    double* sa_sum) {
     const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= n_level) return;
-    Node8 nd = nodes[first + w];
+    Node8 nd;
+    fetch_node(nodes, first + w, nd);
     float clo[8][3], chi[8][3];
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     uint32_t n_int = 0;
@@ -733,10 +753,7 @@ __global__ void refit_level_kernel(Node8* nodes, const float4* btris, float4* no
             nd.q[a][1][sl] = half_of_int(min(max(qh, 0), RT_QMAX));
         }
     }
-    const uint4* src = reinterpret_cast<const uint4*>(&nd);
-    uint4* dst = reinterpret_cast<uint4*>(nodes + first + w);
-#pragma unroll
-    for (int k = 0; k < (int)RT_NODE_WORDS; k++) dst[k] = src[k];
+    store_node(nodes, first + w, nd);
 }
 
 int refit_bvh8(const BuildInput& in, BuildOutput& out, const uint8_t* d_dirty, double* sa_now, cudaStream_t stream, std::string& err) {

@@ -665,13 +665,16 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
             const uint32_t node = ng.x + __popc(ng.y & 0xFFu & ((1u << sl) - 1u));
             if (ng.y & 0xFF000000u) stk[sp++] = ng;
             const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
-            const uint4 w0 = __ldg(np);
-            const uint2 w1 = __ldg(reinterpret_cast<const uint2*>(np + 1));  // child_base, tri_base
-            const uint32_t meta = __ldg(reinterpret_cast<const unsigned char*>(np) + 24 + c);
-            const unsigned short* qp = reinterpret_cast<const unsigned short*>(np + 2) + c;  // q[axis][lo/hi][slot]
-            const float qxl = __half2float(__ushort_as_half(__ldg(qp))), qxh = __half2float(__ushort_as_half(__ldg(qp + 8)));
-            const float qyl = __half2float(__ushort_as_half(__ldg(qp + 16))), qyh = __half2float(__ushort_as_half(__ldg(qp + 24)));
-            const float qzl = __half2float(__ushort_as_half(__ldg(qp + 32))), qzh = __half2float(__ushort_as_half(__ldg(qp + 40)));
+            const uint4* hp = np + node_chunk(node, 0u);  // the node's chunks are stored rotated (rt_types.cuh)
+            const uint4 w0 = __ldg(hp);
+            const uint2 w1 = __ldg(reinterpret_cast<const uint2*>(hp + 1));  // child_base, tri_base
+            const uint32_t meta = __ldg(reinterpret_cast<const unsigned char*>(hp) + 24 + c);
+            const unsigned short* qx = reinterpret_cast<const unsigned short*>(np + node_chunk(node, 1u)) + c;  // q[axis][lo/hi][slot]
+            const unsigned short* qy = reinterpret_cast<const unsigned short*>(np + node_chunk(node, 2u)) + c;
+            const unsigned short* qz = reinterpret_cast<const unsigned short*>(np + node_chunk(node, 3u)) + c;
+            const float qxl = __half2float(__ushort_as_half(__ldg(qx))), qxh = __half2float(__ushort_as_half(__ldg(qx + 8)));
+            const float qyl = __half2float(__ushort_as_half(__ldg(qy))), qyh = __half2float(__ushort_as_half(__ldg(qy + 8)));
+            const float qzl = __half2float(__ushort_as_half(__ldg(qz))), qzh = __half2float(__ushort_as_half(__ldg(qz + 8)));
             if (COUNT && lane == 0) c_nodes++;
             const uint32_t ew = w0.w;
             const float scx = __uint_as_float((ew & 0xFFu) << 23), scy = __uint_as_float(((ew >> 8) & 0xFFu) << 23),

@@ -169,25 +169,29 @@ __device__ __forceinline__ uint4 sel4(bool c, uint4 a, uint4 b) {
 }
 
 // One node = one 128-byte line: header words w0, w1 and, per axis, the near and far plane vectors for this ray's
-// direction signs (near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one).
-__device__ __forceinline__ void load_node(const uint4* np, uint32_t sx, uint32_t sy, uint32_t sz, uint4& w0, uint4& w1, uint4& nx,
-                                          uint4& fx, uint4& ny, uint4& fy, uint4& nz, uint4& fz) {
+// direction signs (near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one).  The four chunks are
+// stored rotated by the node index (rt_types.cuh: node_chunk).
+__device__ __forceinline__ void load_node(const uint4* nodes, uint32_t node, uint32_t sx, uint32_t sy, uint32_t sz, uint4& w0, uint4& w1,
+                                          uint4& nx, uint4& fx, uint4& ny, uint4& fy, uint4& nz, uint4& fz) {
+    const uint4* np = nodes + (size_t)node * RT_NODE_WORDS;
 #if RT_NODE_LDG256
     // four 256-bit loads per node (sm_100 LDG.256) instead of eight 128-bit ones: fewer L1 requests when the lanes
     // of a warp sit in different nodes; the near / far planes are then picked by register selects
     uint4 lx, hx, ly, hy, lz, hz;
-    ldg256(np, w0, w1);
-    ldg256(np + 2, lx, hx);
-    ldg256(np + 4, ly, hy);
-    ldg256(np + 6, lz, hz);
+    ldg256(np + node_chunk(node, 0u), w0, w1);
+    ldg256(np + node_chunk(node, 1u), lx, hx);
+    ldg256(np + node_chunk(node, 2u), ly, hy);
+    ldg256(np + node_chunk(node, 3u), lz, hz);
     nx = sel4(sx != 0u, hx, lx); fx = sel4(sx != 0u, lx, hx);
     ny = sel4(sy != 0u, hy, ly); fy = sel4(sy != 0u, ly, hy);
     nz = sel4(sz != 0u, hz, lz); fz = sel4(sz != 0u, lz, hz);
 #else
-    w0 = __ldg(np); w1 = __ldg(np + 1);
-    nx = __ldg(np + 2 + sx); fx = __ldg(np + 3 - sx);
-    ny = __ldg(np + 4 + sy); fy = __ldg(np + 5 - sy);
-    nz = __ldg(np + 6 + sz); fz = __ldg(np + 7 - sz);
+    const uint4 *c0 = np + node_chunk(node, 0u), *cx = np + node_chunk(node, 1u), *cy = np + node_chunk(node, 2u),
+                *cz = np + node_chunk(node, 3u);
+    w0 = __ldg(c0); w1 = __ldg(c0 + 1);
+    nx = __ldg(cx + sx); fx = __ldg(cx + 1 - sx);
+    ny = __ldg(cy + sy); fy = __ldg(cy + 1 - sy);
+    nz = __ldg(cz + sz); fz = __ldg(cz + 1 - sz);
 #endif
 }
 
@@ -228,11 +232,10 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
     const uint32_t rel = __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
     const uint32_t node = ng.x + rel;
     if (ng.y & 0xFF000000u) stk.e[st.sp++] = ng;
-    const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
     // near plane of axis a: word 2 + 2a + sign(d_a), far plane: the other one
     const uint32_t sx = r.rbits & 1u, sy = (r.rbits >> 1) & 1u, sz = (r.rbits >> 2) & 1u;
     uint4 w0, w1, nx, fx, ny, fy, nz, fz;
-    load_node(np, sx, sy, sz, w0, w1, nx, fx, ny, fy, nz, fz);
+    load_node(sc.nodes, node, sx, sy, sz, w0, w1, nx, fx, ny, fy, nz, fz);
     if (COUNT) n_nodes++;
     const uint32_t hm = node_hits(w0, w1, nx, fx, ny, fy, nz, fz, r, st.tmin, st.best.t);
     ng = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));
@@ -240,8 +243,8 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
     while (tmask) {
         const int tb = __ffs(tmask) - 1;
         tmask &= tmask - 1u;
-        const float4* tp = sc.tris + (size_t)(w1.y + (uint32_t)tb) * 3u;
-        const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+        float4 q0, q1, q2;
+        ldg_tri(sc.tris, w1.y + (uint32_t)tb, q0, q1, q2);
         if (COUNT) n_tris++;
         const uint32_t inst = __float_as_uint(q1.w);
         if (ANY && inst == st.ignore_inst) continue;
@@ -315,8 +318,8 @@ __device__ __forceinline__ void coop_init_ray(CoopWarp& cw, uint32_t lane, const
 template <bool ANY>
 __device__ __forceinline__ unsigned long long coop_test(const SceneView& sc, CoopWarp& cw, uint32_t owner, uint32_t ti, float tmin,
                                                         float* uu, float* vv) {
-    const float4* tp = sc.tris + (size_t)ti * 3u;
-    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+    float4 q0, q1, q2;
+    ldg_tri(sc.tris, ti, q0, q1, q2);
     if (ANY && __float_as_uint(q1.w) == cw.ignore[owner]) return 0ull;
     const float4 a = cw.ra[owner], b = cw.rb[owner];
     Shear sh;
@@ -403,10 +406,9 @@ __device__ __forceinline__ uint32_t coop_node(const SceneView& sc, const NodeRay
     const uint32_t slot = ((uint32_t)bit - 24u) ^ nr.oct;
     const uint32_t node = ng.x + __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
     if (ng.y & 0xFF000000u) stk.e[sp++] = ng;
-    const uint4* np = sc.nodes + (size_t)node * RT_NODE_WORDS;
     const uint32_t sx = nr.oct & 1u, sy = (nr.oct >> 1) & 1u, sz = (nr.oct >> 2) & 1u;
     uint4 w0, w1, nx, fx, ny, fy, nz, fz;
-    load_node(np, sx, sy, sz, w0, w1, nx, fx, ny, fy, nz, fz);
+    load_node(sc.nodes, node, sx, sy, sz, w0, w1, nx, fx, ny, fy, nz, fz);
     if (COUNT) n_nodes++;
     const uint32_t hm = node_hits(w0, w1, nx, fx, ny, fy, nz, fz, r, tmin, tmax);
     ng_io = make_uint2(w1.x, (hm & 0xFF000000u) | (w0.w >> 24));

@@ -42,8 +42,24 @@ struct __align__(16) Node8 {
 };
 static_assert(sizeof(Node8) == 128, "Node8 is 128 bytes");
 #define RT_NODE_WORDS 8u
+// In memory the four 32-byte chunks of a node (header, x planes, y planes, z planes) are rotated by the node's
+// index: chunk c of node n sits at chunk position (c + n) & 3.  Incoherent rays fetch chunk c of 32 DIFFERENT
+// nodes with one LDG.256; unrotated, all 32 accesses fall on the same eight L1 banks and are served one thread
+// per cycle, rotated they spread over the four bank groups (tools/mb/gather2.cu: 128.8 -> 70.1 cycles per warp
+// and node, L1-resident).  Struct Node8 above is the UNROTATED form (builder registers, rt_get_bvh, oracle).
+#ifndef RT_NODE_ROTATE
+#define RT_NODE_ROTATE 1
+#endif
+__host__ __device__ __forceinline__ uint32_t node_chunk(uint32_t node, uint32_t c) {  // in uint4 units
+#if RT_NODE_ROTATE
+    return ((c + node) & 3u) * 2u;
+#else
+    (void)node;
+    return c * 2u;
+#endif
+}
 
-// 48-byte triangle: three float4 (world-space vertices + ids), fetched with three LDG.128.
+// 48-byte triangle: three float4 (world-space vertices + ids), fetched as LDG.256 + LDG.128 (ldg_tri below).
 struct __align__(16) BvhTri {
     float p0[3]; uint32_t id;    // flat triangle id = object.tri_offset + primitive
     float p1[3]; uint32_t inst;  // object index (instanceCustomIndex, gpu_scene.odin:135)
@@ -142,6 +158,27 @@ __device__ __forceinline__ void ldg256(const uint4* p, uint4& a, uint4& b) {
     asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
                  : "l"(p));
+}
+__device__ __forceinline__ void ldg256f(const float4* p, float4& a, float4& b) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+// One 48-byte triangle as a 256-bit and a 128-bit load (which of the two comes first depends on the parity of the
+// index: only even triangles start on a 32-byte boundary) instead of three 128-bit ones: two L1 requests per thread
+// instead of three when the lanes of a warp fetch different triangles (tools/mb/gather2.cu: 62.7 -> 33.2 cycles per
+// warp, L1-resident; 90.1 -> 63.7 from L2).  `tris` must be 32-byte aligned (every device allocation is).
+#ifndef RT_TRI_LDG256
+#define RT_TRI_LDG256 1
+#endif
+__device__ __forceinline__ void ldg_tri(const float4* tris, uint32_t ti, float4& q0, float4& q1, float4& q2) {
+    const float4* tp = tris + (size_t)ti * 3u;
+#if RT_TRI_LDG256
+    if (ti & 1u) { q0 = __ldg(tp); ldg256f(tp + 1, q1, q2); }
+    else { ldg256f(tp, q0, q1); q2 = __ldg(tp + 2); }
+#else
+    q0 = __ldg(tp); q1 = __ldg(tp + 1); q2 = __ldg(tp + 2);
+#endif
 }
 #endif
 
