@@ -443,7 +443,7 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel
     NodeRay nr;
     nr.ox = nr.oy = nr.oz = nr.idx = nr.idy = nr.idz = 0.0f; nr.oct = 0u;
     TravStack stk;
-    uint2 ng = make_uint2(0u, 0u);
+    uint2 ng = make_uint2(0u, 0u), top = make_uint2(0u, 0u);
     int sp = 0;
     float best_t = 0.0f;
     bool has_ray = false;
@@ -458,6 +458,7 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel
             nr.ox = r.ox; nr.oy = r.oy; nr.oz = r.oz; nr.idx = r.idx; nr.idy = r.idy; nr.idz = r.idz; nr.oct = r.rbits & 7u;
             ng = make_uint2(0u, 0x80000000u);
             sp = 0;
+            top.y = 0u;
             best_t = 10000.0f;
             has_ray = true;
             c_rays++;
@@ -468,12 +469,12 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel
         const uint32_t max_idle = wfetch.drained ? 31u : (RT_REFILL_IDLE - 1u);
         for (;;) {
             uint32_t tmask = 0u, tbase = 0u;
-            if (has_ray) tmask = coop_node<COUNT>(sc, nr, ng, sp, stk, 0.001f, best_t, &tbase, c_nodes);
+            if (has_ray) tmask = coop_node<COUNT>(sc, nr, ng, sp, stk, top, 0.001f, best_t, &tbase, c_nodes);
             coop_triangles<false, COUNT>(sc, cw, lane, tmask, tbase, 0.001f, c_tris);
             if (has_ray) {
                 best_t = __uint_as_float((uint32_t)(cw.key[lane] >> 32));
-                if (!(ng.y & 0xFF000000u)) {
-                    if (sp == 0) {  // traversal complete
+                if (!(ng.y & 0xFF000000u) && !stk_pop(stk, sp, top, ng)) {
+                    {  // traversal complete
                         const uint32_t ti = cw.tri[lane];
                         uint32_t inst = 0xFFFFFFFFu, prim = 0u;
                         float2 uv = make_float2(0.0f, 0.0f);
@@ -485,8 +486,6 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel
                         }
                         wf.hit[slot] = make_uint4(__float_as_uint(uv.x), __float_as_uint(uv.y), inst, prim);
                         has_ray = false;
-                    } else {
-                        ng = stk.e[--sp];
                     }
                 }
             }
@@ -1004,7 +1003,7 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_shadow_coop_kernel
     NodeRay nr;
     nr.ox = nr.oy = nr.oz = nr.idx = nr.idy = nr.idz = 0.0f; nr.oct = 0u;
     TravStack stk;
-    uint2 ng = make_uint2(0u, 0u);
+    uint2 ng = make_uint2(0u, 0u), top = make_uint2(0u, 0u);
     int sp = 0;
     float tmax = 0.0f;
     bool has_ray = false;
@@ -1023,6 +1022,7 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_shadow_coop_kernel
                 nr.ox = r.ox; nr.oy = r.oy; nr.oz = r.oz; nr.idx = r.idx; nr.idy = r.idy; nr.idz = r.idz; nr.oct = r.rbits & 7u;
                 ng = make_uint2(0u, 0x80000000u);
                 sp = 0;
+                top.y = 0u;
                 has_ray = true;
                 c_rays++;
             }
@@ -1035,14 +1035,12 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_shadow_coop_kernel
         const uint32_t max_idle = wfetch.drained ? 31u : (RT_REFILL_IDLE - 1u);
         for (;;) {
             uint32_t tmask = 0u, tbase = 0u;
-            if (has_ray) tmask = coop_node<COUNT>(sc, nr, ng, sp, stk, 0.001f, tmax, &tbase, c_nodes);
+            if (has_ray) tmask = coop_node<COUNT>(sc, nr, ng, sp, stk, top, 0.001f, tmax, &tbase, c_nodes);
             coop_triangles<true, COUNT>(sc, cw, lane, tmask, tbase, 0.001f, c_tris);
             if (has_ray) {
                 const bool occluded = cw.tri[lane] == 0u;
                 bool done = occluded;
-                if (!done && !(ng.y & 0xFF000000u)) {
-                    if (sp == 0) done = true; else ng = stk.e[--sp];
-                }
+                if (!done && !(ng.y & 0xFF000000u)) done = !stk_pop(stk, sp, top, ng);
                 if (done) {
                     shadow_entry_finish(fp, wf, entry, !occluded);
                     has_ray = false;

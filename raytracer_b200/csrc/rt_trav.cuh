@@ -210,6 +210,32 @@ struct TravState {
 };
 // the group stack lives beside the state (a dynamically indexed member would drag the whole struct into local memory)
 struct TravStack { uint2 e[RT_STACK_SIZE]; };
+// The cooperative kernels keep the newest stack entry in registers (`top`, valid while top.y != 0: a pushed group
+// always has hit bits left): an entry that is popped right after it was pushed never touches local memory.  ncu on
+// the Sponza proxy: the stack was 20 % of the kernel's L1 sectors and 13 % of its L1 misses (node traffic evicts it).
+#ifndef RT_STACK_TOP
+#define RT_STACK_TOP 0 /* measured: 2073.7 -> 2049.2 Mrays/s on bounces >= 1 (the extra selects cost more issue slots than the L1 relief returns) */
+#endif
+__device__ __forceinline__ void stk_push(TravStack& stk, int& sp, uint2& top, uint2 x) {
+#if RT_STACK_TOP
+    if (top.y) stk.e[sp++] = top;
+    top = x;
+#else
+    (void)top;
+    stk.e[sp++] = x;
+#endif
+}
+// false: the stack is empty
+__device__ __forceinline__ bool stk_pop(TravStack& stk, int& sp, uint2& top, uint2& out) {
+#if RT_STACK_TOP
+    if (top.y) { out = top; top.y = 0u; return true; }
+#else
+    (void)top;
+#endif
+    if (sp == 0) return false;
+    out = stk.e[--sp];
+    return true;
+}
 
 __device__ __forceinline__ void trav_init(TravState& st, vec3 o, vec3 d, float tmin, float tmax, uint32_t ignore_inst) {
     st.r = trav_setup(o, d);
@@ -280,9 +306,6 @@ __device__ __forceinline__ bool trav_step(const SceneView& sc, TravState& st, Tr
 // owns it.  The owner's closest hit lives in shared memory as one 64-bit key (t bits << 32 | flat id): an
 // unsigned atomicMin on it IS the (t, id)-lexicographic rule of the per-lane loop (t > 0, so the bit patterns
 // order like the floats), hence the same hit record bit for bit.
-#ifndef RT_COOP_ITEMS
-#define RT_COOP_ITEMS 256  /* pairs pooled per node step and warp; more than that (never seen) falls back to per-lane tests */
-#endif
 struct CoopWarp {
     unsigned long long key[32];  // t bits << 32 | flat triangle id of the closest accepted hit; (tmax bits << 32) = none yet
     float4 ra[32];               // shear px.x px.y py.x py.y
@@ -291,7 +314,7 @@ struct CoopWarp {
     float2 uv[32];               // barycentrics of the hit in `key`
     uint32_t tri[32];            // its index in the BVH triangle array, 0xFFFFFFFF = miss; any-hit: 0 = occluded
     uint32_t ignore[32];         // any-hit: triangles of this instance do not occlude (simple.rchit:378-382)
-    uint32_t items[RT_COOP_ITEMS];  // triangle index | owner lane << 27
+    uint4 ent[32];               // one per lane with triangles this step: triangle base, bits, first pool slot, lane
 };
 
 // slim per-lane state of the cooperative kernel: everything the node test needs, nothing of the triangle test
@@ -341,62 +364,60 @@ __device__ __forceinline__ unsigned long long coop_test(const SceneView& sc, Coo
 
 // All 32 lanes call this after a node step; tmask / tbase: the lane's triangle bits and triangle base (0 when the
 // lane has no ray).  On return every owner's closest hit (key, tri, uv) includes the pooled triangles.
+//
+// Dealing the pairs out: the lanes that reached triangles each leave ONE entry (triangle base, bits, first pool slot,
+// lane) in shared memory, in lane order, hence sorted by first slot; the lane that tests pool slot w finds its entry
+// by counting the entries that start at or before w (a REDUX.OR of the start slots + POPC) and clears w - start low
+// bits of the entry's mask.  (Before: every owner wrote one item per pair in a loop that ran max-pairs-per-lane times
+// with 2.7 lanes active, 9 % of the kernel's issue slots; the counts were scanned with five dependent SHFL.UP.)
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ void coop_triangles(const SceneView& sc, CoopWarp& cw, uint32_t lane, uint32_t tmask, uint32_t tbase,
                                                float tmin, uint32_t& n_tris) {
-    const uint32_t cnt = __popc(tmask);
-    uint32_t pre = cnt;  // inclusive scan of the counts
+    const uint32_t cnt = __popc(tmask);  // 0..24
+    // inclusive scan of the counts by bit planes: five independent ballots instead of a five-step shuffle chain
+    const uint32_t le = 0xFFFFFFFFu >> (31u - lane);
+    uint32_t pre = 0u, total = 0u, owners = 0u;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, pre, o);
-        if (lane >= (uint32_t)o) pre += v;
+    for (int b = 0; b < 5; b++) {
+        const uint32_t plane = __ballot_sync(0xFFFFFFFFu, ((cnt >> b) & 1u) != 0u);
+        pre += (uint32_t)__popc(plane & le) << b;
+        total += (uint32_t)__popc(plane) << b;
+        owners |= plane;
     }
-    const uint32_t total = __shfl_sync(0xFFFFFFFFu, pre, 31);
     if (total == 0u) return;
-    if (total <= RT_COOP_ITEMS) {
-        uint32_t pos = pre - cnt;
-        while (tmask) {
-            const uint32_t tb = __ffs(tmask) - 1;
-            tmask &= tmask - 1u;
-            cw.items[pos++] = (tbase + tb) | (lane << 27);
-        }
-        __syncwarp();
-        for (uint32_t base = 0; base < total; base += 32u) {
-            const uint32_t w = base + lane;
-            unsigned long long key = 0ull;
-            uint32_t owner = 0, ti = 0;
-            float uu = 0.0f, vv = 0.0f;
-            if (w < total) {
-                const uint32_t item = cw.items[w];
-                owner = item >> 27;
-                ti = item & 0x07FFFFFFu;
-                if (COUNT) n_tris++;
-                key = coop_test<ANY>(sc, cw, owner, ti, tmin, &uu, &vv);
-            }
-            __syncwarp();
-            if (!ANY) {
-                // of the lanes that lowered an owner's key this round, the one whose key stayed publishes the rest
-                if (key != 0ull && cw.key[owner] == key) { cw.tri[owner] = ti; cw.uv[owner] = make_float2(uu, vv); }
-                __syncwarp();
-            }
-        }
-    } else {  // more pairs than the pool holds: every lane tests its own triangles
-        while (tmask) {
-            const uint32_t tb = __ffs(tmask) - 1;
-            tmask &= tmask - 1u;
-            float uu, vv;
+    const uint32_t start = pre - cnt;
+    if (cnt) cw.ent[__popc(owners & (le >> 1))] = make_uint4(tbase, tmask, start, lane);
+    __syncwarp();
+    for (uint32_t base = 0; base < total; base += 32u) {
+        const uint32_t rel = start - base;  // wraps for entries that start before this round
+        const uint32_t heads = __reduce_or_sync(0xFFFFFFFFu, (cnt != 0u && rel < 32u) ? (1u << rel) : 0u);
+        const uint32_t before = base ? (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, cnt != 0u && start < base)) : 0u;
+        const uint32_t w = base + lane;
+        unsigned long long key = 0ull;
+        uint32_t owner = 0, ti = 0;
+        float uu = 0.0f, vv = 0.0f;
+        if (w < total) {
+            const uint4 e = cw.ent[before + (uint32_t)__popc(heads & le) - 1u];
+            uint32_t m = e.y;
+            for (uint32_t k = w - e.z; k; k--) m &= m - 1u;
+            ti = e.x + (uint32_t)__ffs(m) - 1u;
+            owner = e.w;
             if (COUNT) n_tris++;
-            const unsigned long long key = coop_test<ANY>(sc, cw, lane, tbase + tb, tmin, &uu, &vv);
-            if (!ANY && key != 0ull) { cw.tri[lane] = tbase + tb; cw.uv[lane] = make_float2(uu, vv); }
+            key = coop_test<ANY>(sc, cw, owner, ti, tmin, &uu, &vv);
         }
         __syncwarp();
+        if (!ANY) {
+            // of the lanes that lowered an owner's key this round, the one whose key stayed publishes the rest
+            if (key != 0ull && cw.key[owner] == key) { cw.tri[owner] = ti; cw.uv[owner] = make_float2(uu, vv); }
+            __syncwarp();
+        }
     }
 }
 
 // node part of a traversal step for the cooperative kernel: pop the next child, slab-test its eight boxes.
 // ng / sp / stk as in TravState; returns the triangle bits, *tbase the node's triangle base.
 template <bool COUNT>
-__device__ __forceinline__ uint32_t coop_node(const SceneView& sc, const NodeRay& nr, uint2& ng_io, int& sp, TravStack& stk,
+__device__ __forceinline__ uint32_t coop_node(const SceneView& sc, const NodeRay& nr, uint2& ng_io, int& sp, TravStack& stk, uint2& top,
                                               float tmin, float tmax, uint32_t* tbase, uint32_t& n_nodes) {
     TravRay r;  // node_hits reads only the members set here
     r.ox = nr.ox; r.oy = nr.oy; r.oz = nr.oz; r.idx = nr.idx; r.idy = nr.idy; r.idz = nr.idz; r.rbits = nr.oct;
@@ -405,7 +426,7 @@ __device__ __forceinline__ uint32_t coop_node(const SceneView& sc, const NodeRay
     ng.y &= ~(1u << bit);
     const uint32_t slot = ((uint32_t)bit - 24u) ^ nr.oct;
     const uint32_t node = ng.x + __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
-    if (ng.y & 0xFF000000u) stk.e[sp++] = ng;
+    if (ng.y & 0xFF000000u) stk_push(stk, sp, top, ng);
     const uint32_t sx = nr.oct & 1u, sy = (nr.oct >> 1) & 1u, sz = (nr.oct >> 2) & 1u;
     uint4 w0, w1, nx, fx, ny, fy, nz, fz;
     load_node(sc.nodes, node, sx, sy, sz, w0, w1, nx, fx, ny, fy, nz, fz);
