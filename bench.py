@@ -18,7 +18,7 @@ by ONE process through one multi-GPU rt_ctx (rt_config.device_ids), no torchrun.
   e2e          the same through the C ABI with HOST buffers: camera UBO from host memory each step and the RGBA32F image
                into pinned host memory each step
   roofline     dominant kernel (wf_extend_coop_kernel: per-ray traversal of bounces >= 1): thread-loads of its BVH gather /
-               its CUDA-event time against the measured divergent-gather peak (profiles/gather_peaks.json); the byte model of
+               its CUDA-event time against the measured divergent-gather peak (profiles/gather2_peaks.json); the byte model of
                SURVEY §8d as roofline.hbm_bookkeeping; roofline_packet: the first-bounce packet kernel
   verify       SHA-256 of a 16-frame image; at N > 1 also of the same image rendered on one GPU (must be equal)
   cpu_baseline the CPU oracle (a port: the reference has no CPU path) on whole frames of the workload, rank 0, N = 1
@@ -352,8 +352,8 @@ def run_ours(args):
         def alg(c):  # BVH8 nodes 128 B + triangles 48 B fetched by closest-hit rays, ray in 32 B, hit out 16 B
             return (c["nodes"] - c["shadow_nodes"]) * 128 + (c["tris"] - c["shadow_tris"]) * 48 + c["extend_rays"] * 48
 
-        def loads(c):  # (thread, load instruction) pairs of the gather: a node is 4 x LDG.256, a triangle 3 x LDG.128
-            return (c["nodes"] - c["shadow_nodes"]) * 4 + (c["tris"] - c["shadow_tris"]) * 3
+        def loads(c):  # (thread, load instruction) pairs of the gather: a node is 4 x LDG.256, a triangle LDG.256 + LDG.128
+            return (c["nodes"] - c["shadow_nodes"]) * 4 + (c["tris"] - c["shadow_tris"]) * 2
 
         sec_rays = cnt["extend_rays"] - cnt1["extend_rays"]
         alg_sec = alg(cnt) - alg(cnt1)
@@ -361,11 +361,18 @@ def run_ours(args):
         t_ext = ext["ms"] * 1e-3
         hbm_ratio = alg_sec / t_ext / 1e9 if t_ext > 0 else 0.0
         achieved = loads_sec / t_ext / 1e9 if t_ext > 0 else 0.0
-        # peak: one (thread, load) per clock per SM when every thread of a warp sits in another 128-byte line — measured
-        # by the microbenchmark with an L1-resident table; the L2-resident figure (the BVH is 18 MB) is reported beside it
-        g_l1 = gpeaks.get(("LDG.256", 65536))
-        g_l2 = gpeaks.get(("128 B = 4 x LDG.256", 16777216))
-        peak_l1 = g_l1["thread_loads_per_s"] / 1e9 if g_l1 else 290.8
+        # peak: the kernel's own node fetch (four LDG.256 per thread, every thread in another 128-byte line, chunks rotated by
+        # the line index so that the accesses spread over the L1 banks) on an L1-resident table — tools/mb/gather2.cu; the
+        # L2-resident figure (the BVH is 18 MB, the kernel's L1 hit rate 43 %) is reported beside it
+        g2 = {}
+        try:
+            j2 = json.load(open(os.path.join(ROOT, "profiles", "gather2_peaks.json")))
+            g2 = {(r["pattern"], r["table_bytes"]): 128.0 / r["cycles_per_warp_iteration"] * 148 * j2["sm_clock_hz"] / 1e9 for r in j2["rows"]}
+        except Exception:
+            pass
+        pat = "line = 4 x LDG.256 from chunk line&3"
+        g_l1, g_l2 = g2.get((pat, 32768)), g2.get((pat, 16777216))
+        peak_l1 = g_l1 if g_l1 else 531.0
         traffic, l1_stage, tsrc = None, None, None
         try:  # dram__bytes_read + write per launch and the L1 data-stage share of the last committed `ncu --set full`
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_coop_kernel"]
@@ -376,10 +383,10 @@ def run_ours(args):
         roof = {"bound": "l1_data_stage",
                 "kernel": "wf_extend_coop_kernel (one ray per lane, pooled triangle tests; bounces 1..%d)" % (args.max_depth - 1),
                 "achieved": achieved, "peak": peak_l1, "unit": "G thread-loads/s", "frac": achieved / peak_l1,
-                "peak_source": "profiles/gather_peaks.json (tools/mb/gather.cu on a B200 of this pool)" if g_l1 else "fallback 148 SMs x 1.965 GHz",
-                "peak_l2_resident": g_l2["thread_loads_per_s"] / 1e9 if g_l2 else None,
-                "definition": "thread-loads = 4 per BVH8 node (4 x LDG.256) + 3 per triangle (3 x LDG.128) fetched by the rays of bounces >= 1, "
-                              "counted on an identical untimed pass; a divergent load costs the SM's L1 data stage one cycle per thread whatever its width",
+                "peak_source": "profiles/gather2_peaks.json (tools/mb/gather2.cu on a B200 of this pool: the kernel's node fetch, L1-resident)" if g_l1 else "fallback",
+                "peak_l2_resident": g_l2, "frac_of_l2_resident": (achieved / g_l2) if g_l2 else None,
+                "definition": "thread-loads = 4 per BVH8 node (4 x LDG.256) + 2 per triangle (LDG.256 + LDG.128) fetched by the rays of bounces >= 1, "
+                              "counted on an identical untimed pass; each is one 32-byte-sector request of one thread to the SM's L1",
                 "traffic": traffic, "traffic_source": tsrc,
                 "launches": ext["launches"], "avg_launch_ms": ext["ms"] / max(ext["launches"], 1),
                 "thread_loads_per_launch": loads_sec / max(ext["launches"], 1),

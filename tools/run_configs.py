@@ -92,7 +92,7 @@ def run_config(tag, name, W, H, spp, depth, out_dir, restir=False, small=(96, 54
     # bytes_per_ray: the §8(d) byte model (bookkeeping: the BVH is cache-resident, so no fraction of the HBM peak is derived
     # from it any more); loads_per_ray: (thread, load instruction) pairs of the BVH gather, the quantity that binds traversal
     row.update(mrays_s=round(rays / ms / 1e3, 1), ms_per_frame=round(ms / spp, 4), rays_per_frame=rays // spp,
-               bytes_per_ray=round(alg / max(rays, 1), 1), loads_per_ray=round((4 * c["nodes"] + 3 * c["tris"]) / max(rays, 1), 1))
+               bytes_per_ray=round(alg / max(rays, 1), 1), loads_per_ray=round((4 * c["nodes"] + 2 * c["tris"]) / max(rays, 1), 1))
     # ---- the CPU port at THIS resolution: a centred band of rows of frame 1, sized for about a second, scaled to the frame
     if not restir:
         from oracle.binding import OracleScene as _O, lib as _lib
