@@ -314,6 +314,18 @@ RT_API int rt_get_kernel_profile(rt_ctx* ctx, rt_kernel_profile* out);
  * any: out_occluded n x u32 (1 = a triangle of an instance != ignore_inst[i] lies in range). */
 RT_API int rt_trace_rays_closest(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id);
 RT_API int rt_trace_rays_any(rt_ctx* ctx, const float* rays, uint32_t n, const uint32_t* ignore_inst, uint32_t* out_occluded);
+/* Closest hit without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, host pointers and bit-identical results as rt_trace_rays_closest, but the device staging of rays and
+ * results is a file-scope static __device__ array of RT_STATIC_MAX_RAYS x 48 B + 256 B (3 MiB, held by every GPU that loads
+ * the library until the process exits) instead of per-call cudaMalloc; the call makes no cudaMalloc / cudaFree and no
+ * allocating library call.  n > RT_STATIC_MAX_RAYS -> RT_ERR_INVALID_ARGUMENT (split the batch).  The scene must already
+ * be resident: pending edits (which need allocations to reach the device) -> RT_ERR_NO_SCENE; rt_scene_info_get or any
+ * trace call makes it resident.  Every call on a device shares the one array, which keeps the last call's contents (the
+ * work cursor is cleared per call): calls that overlap on one GPU race — one call at a time per device. */
+#define RT_STATIC_MAX_RAYS 65536u
+RT_API uint32_t rt_static_max_rays(void);
+RT_API int rt_trace_rays_closest_static(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id);
 /* BVH download for the bit-exact comparison with the deterministic CPU twin.
  * nodes: n_nodes x 128 B, tris: n_triangles x 48 B, morton/sorted ids: n_triangles each; NULL skips. */
 RT_API int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t tris_bytes, uint64_t* morton,

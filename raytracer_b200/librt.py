@@ -34,7 +34,7 @@ EXPORTS = (
     "rt_readback_srgb8", "rt_device_image", "rt_upload_accum", "rt_get_strip_owners", "rt_rebalance", "rt_measure_row_costs", "rt_set_strip_owners", "rt_trace_gbuffer", "rt_readback_gbuffer", "rt_raster_gbuffer", "rt_readback_raster_gbuffer",
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
     "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_event_elapsed_per_device", "rt_set_profiling", "rt_get_kernel_profile",
-    "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh",
+    "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh", "rt_static_max_rays", "rt_trace_rays_closest_static",
 )
 
 
@@ -155,6 +155,9 @@ def load() -> C.CDLL:
     L.rt_get_kernel_profile.argtypes = [vp, C.POINTER(RtKernelProfile)]
     L.rt_trace_rays_closest.argtypes = [vp, f32p, u32, vp, vp]
     L.rt_trace_rays_any.argtypes = [vp, f32p, u32, vp, vp]
+    L.rt_static_max_rays.argtypes = []
+    L.rt_static_max_rays.restype = u32
+    L.rt_trace_rays_closest_static.argtypes = [vp, f32p, u32, vp, vp]
     L.rt_get_bvh.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t, vp, vp]
     _lib = L
     return L
@@ -415,6 +418,14 @@ class Context:
         tuv = np.zeros((len(rays), 3), np.float32)
         ids = np.zeros(len(rays), np.uint32)
         self._check(self.L.rt_trace_rays_closest(self.h, _p(rays), len(rays), _p(tuv), _p(ids)))
+        return tuv, ids
+
+    def trace_rays_closest_static(self, rays):
+        """rt_trace_rays_closest_static: same results, no allocation (static device scratch, <= rt_static_max_rays rays)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        tuv = np.zeros((len(rays), 3), np.float32)
+        ids = np.zeros(len(rays), np.uint32)
+        self._check(self.L.rt_trace_rays_closest_static(self.h, _p(rays), len(rays), _p(tuv), _p(ids)))
         return tuv, ids
 
     def trace_rays_any(self, rays, ignore_inst=None):
