@@ -240,6 +240,11 @@ struct WavefrontBuffers {
     DevBuf<float4> sh_e;    // emissive term.xyz, flags (1 = emissive add, 2 = sky add)
     DevBuf<float4> sh_n;    // light sample waiting for wf_nee_kernel: its three draws, selection pdf
     DevBuf<uint32_t> ctrl;  // [0..1] queue counts, [2] shadow count, [3..5] work cursors (extend, shade, shadow)
+    // how many paths the last batch on this state still had at bounce RT_TAIL_DEPTH: written by the GPU into mapped host memory,
+    // read by the host WITHOUT synchronisation when it queues the next batch (a hint for the choice of kernels, never for results)
+    uint32_t* tail_hint_h = nullptr;
+    uint32_t* tail_hint_d = nullptr;
+    ~WavefrontBuffers() { if (tail_hint_h) cudaFreeHost(tail_hint_h); }
 };
 
 int wavefront_alloc(WavefrontBuffers** out, uint32_t n_slots, std::string& err) {
@@ -252,6 +257,11 @@ int wavefront_alloc(WavefrontBuffers** out, uint32_t n_slots, std::string& err) 
     A(w->queue[0].alloc(n_slots)); A(w->queue[1].alloc(n_slots));
     A(w->sh_o.alloc(n_slots)); A(w->sh_d.alloc(n_slots)); A(w->sh_c.alloc(n_slots)); A(w->sh_e.alloc(n_slots)); A(w->sh_n.alloc(n_slots));
     A(w->ctrl.alloc(8));
+    A(cudaHostAlloc(reinterpret_cast<void**>(&w->tail_hint_h), sizeof(uint32_t), cudaHostAllocMapped));
+    if (e == cudaSuccess) {
+        *w->tail_hint_h = 0xFFFFFFFFu;  // unknown
+        A(cudaHostGetDevicePointer(reinterpret_cast<void**>(&w->tail_hint_d), w->tail_hint_h, 0));
+    }
     if (e != cudaSuccess) {
         err = std::string("wavefront_alloc: ") + cudaGetErrorString(e);
         delete w;
@@ -280,13 +290,14 @@ struct WfView {
 #define CT_FB 6       /* rays the packet kernel handed back to the per-ray kernel */
 #define CT_CUR_PKT 7  /* packet cursor */
 
-__global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_count) {
+__global__ void wf_reset_kernel(uint32_t* ctrl, uint32_t q_in, uint32_t q_in_count, uint32_t* report = nullptr) {
     // before a bounce: the out queue, the shadow queue and the cursors are empty
     const uint32_t t = threadIdx.x;
     if (t == 0) {
         ctrl[q_in ^ 1u] = 0; ctrl[CT_SH] = 0; ctrl[CT_CUR_EXT] = 0; ctrl[CT_CUR_SHD] = 0; ctrl[CT_CUR_SHW] = 0;
         ctrl[CT_FB] = 0; ctrl[CT_CUR_PKT] = 0;
         if (q_in_count != 0xFFFFFFFFu) ctrl[q_in] = q_in_count;
+        if (report) *report = ctrl[q_in];  // the tail hint (mapped host memory)
     }
 }
 
@@ -896,6 +907,86 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
     }
 }
 
+// tail: the few paths that are still alive after RT_TAIL_DEPTH bounces are each run to their end by one thread, in ONE launch,
+// instead of three to five launches per remaining bounce.  With a handful of rays a launch lasts as long as its slowest ray
+// (60 - 100 us for a cooperative extend launch on the Sponza proxy, whatever the queue holds), so bounces 3..7 cost a
+// 64-frame batch 0.43 ms in 25 launches — 1.4 % of the batch on one GPU and 5 % of an eighth of it on eight.  The loop is the
+// megakernel's (simple.rgen:87-118 with the hit shader and the visibility query inline), entered with the state the shade
+// kernel of bounce RT_TAIL_DEPTH - 1 left behind: the same operations on the same values in the same order, hence the same
+// image bit for bit.  The host uses it only when the previous batch on this state reported a small queue (WavefrontBuffers::
+// tail_hint_h); with many live paths the wavefront kernels are faster.
+#ifndef RT_TAIL_DEPTH
+#define RT_TAIL_DEPTH 3
+#endif
+template <bool COUNT, bool LIGHTS>
+__global__ void __launch_bounds__(128) wf_tail_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in, uint32_t q_idx, int depth0,
+                                                      uint32_t* report, DevCounters* counters) {
+    constexpr bool PACKED = !LIGHTS && RT_PACK_SEEDS;
+    const uint32_t n = wf.ctrl[q_idx];
+    if (report && blockIdx.x == 0 && threadIdx.x == 0) *report = n;
+    uint32_t c_ext = 0, c_sh = 0, c_nodes = 0, c_tris = 0, c_hits = 0, c_nee = 0, c_snodes = 0, c_stris = 0;
+    const vec3 clearc = mk3(fp.clear[0], fp.clear[1], fp.clear[2]);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = q_in[i];
+        // the path's state as wf_shade_kernel<., false, LIGHTS> reads it
+        const float4 tv = wf.thr[slot], dv = wf.ray_d[slot], ov = wf.ray_o[slot];
+        PathState ps;
+        ps.throughput = mk3(tv.x, tv.y, tv.z);
+        ps.prev_brdf_pdf = tv.w;
+        ps.color = mk3(0.0f, 0.0f, 0.0f);
+        ps.p_sample_light = LIGHTS ? dv.w : 0.0f;
+        if (LIGHTS) {
+            const float4 c = wf.col[slot];
+            ps.color = mk3(c.x, c.y, c.z);
+        }
+        const uint32_t fl = LIGHTS ? __float_as_uint(ov.w) : PF_FIRST;
+        ps.prev_hit_pos = LIGHTS ? mk3(ov.x, ov.y, ov.z) : mk3(0.0f, 0.0f, 0.0f);
+        ps.first_bounce = (fl & PF_FIRST) != 0u;
+        ps.is_specular = (fl & PF_SPECULAR) != 0u;
+        ps.did_direct = (fl & PF_DID_DIRECT) != 0u;
+        const uint2 sd = PACKED ? make_uint2(__float_as_uint(dv.w), __float_as_uint(tv.w)) : wf.seeds[slot];
+        ps.seed = sd.x;
+        ps.rr_seed = sd.y;
+        vec3 o = mk3(ov.x, ov.y, ov.z), d = mk3(dv.x, dv.y, dv.z);
+        bool sky = false;
+        for (int depth = depth0;;) {
+            c_ext++;
+            const Hit h = traverse<false, COUNT>(sc, o, d, 0.001f, 10000.0f, 0xFFFFFFFFu, c_nodes, c_tris);
+            bool alive = false;
+            if (h.id != 0xFFFFFFFFu) {
+                c_hits++;
+                ShadowRequest sr;
+                const ShadeResult res = shade_hit<LIGHTS, false>(sc, ps, h, d, sr, c_nee);
+                if (LIGHTS && sr.pending) {
+                    c_sh++;
+                    const Hit sh = traverse<true, COUNT>(sc, sr.origin, sr.dir, 0.001f, sr.tmax, sr.light_object, c_snodes, c_stris);
+                    if (sh.id == 0xFFFFFFFFu) ps.color = add3(ps.color, sr.contrib);
+                }
+                if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
+                alive = res.alive;
+                o = res.next_origin;
+                d = res.next_dir;
+            }
+            if (!alive) {  // simple.rmiss / payload.hit = false: the sky term ends the path
+                ps.color = add3(ps.color, mul3(ps.throughput, clearc));
+                sky = true;
+                break;
+            }
+            if (throughput_dead(ps.throughput)) break;
+            if (++depth >= fp.max_depth) break;
+            if (!russian_roulette(ps, depth, fp.rr_start)) break;
+        }
+        // without lights a path's colour is zero (as the first shade launch stored it) until its sky term
+        if (LIGHTS || sky) wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, 0.0f);
+    }
+    if (COUNT) {
+        warp_add(&counters->extend_rays, c_ext); warp_add(&counters->shadow_rays, c_sh);
+        warp_add(&counters->nodes, c_nodes + c_snodes); warp_add(&counters->tris, c_tris + c_stris);
+        warp_add(&counters->shadow_nodes, c_snodes); warp_add(&counters->shadow_tris, c_stris);
+        warp_add(&counters->hits, c_hits); warp_add(&counters->nee, c_nee);
+    }
+}
+
 // nee: the second half of the light sample (sampleLight geometry, evaluateLightMIS, the isVisibleRQ ray) for every entry
 // of the shadow queue, one thread per sample.  Inside the hit shader this code ran with 6 of 32 lanes active (ncu r1p,
 // config 4b) and made the kernel 3 700 instructions long; here every lane has a sample.  An entry whose sample
@@ -1127,8 +1218,26 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     uint32_t q_in = 0;
     // no more blocks than the widest possible queue needs
     const int need = (int)((n_slots + 127) / 128);
+    // the tail kernel takes over at bounce RT_TAIL_DEPTH when at least two bounces remain and the last batch on this state had
+    // few paths left there (the hint is read unsynchronised: it steers the choice of kernels, not the result)
+    const uint32_t tail_hint = *reinterpret_cast<volatile uint32_t*>(w->tail_hint_h);
+    const char* tail_env = getenv("RT_TAIL");  // tests and A/B runs: "0" = never, "1" = whenever the depths allow it
+    const bool tail_small = tail_env ? tail_env[0] == '1' : tail_hint <= (uint32_t)dims.num_sms * 1024u;
+    const bool tail_ok = RT_TAIL_DEPTH > 0 && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY) && fp.max_depth - RT_TAIL_DEPTH >= 2 && tail_small;
     for (int depth = 0; depth < fp.max_depth; depth++) {
-        wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, q_in, depth == 0 ? n_slots : 0xFFFFFFFFu);
+        if (depth == RT_TAIL_DEPTH && tail_ok) {
+            const int g = std::min(dims.num_sms * 8, need);
+            pf.begin(RT_K_EXTEND, stream);
+            if (sc.n_lights != 0u)
+                wf_tail_kernel<COUNT, true><<<g, 128, 0, stream>>>(sc, fp, v, w->queue[q_in].p, q_in, depth, w->tail_hint_d, res.counters);
+            else
+                wf_tail_kernel<COUNT, false><<<g, 128, 0, stream>>>(sc, fp, v, w->queue[q_in].p, q_in, depth, w->tail_hint_d, res.counters);
+            pf.end(stream);
+            n_launch++;
+            break;
+        }
+        wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, q_in, depth == 0 ? n_slots : 0xFFFFFFFFu,
+                                             depth == RT_TAIL_DEPTH ? w->tail_hint_d : nullptr);
         const uint32_t* qi = depth == 0 ? nullptr : w->queue[q_in].p;
         if (depth == 0 && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY)) {
             // packets first; what they hand back (tiles across an axis plane) goes through the per-ray kernel

@@ -81,6 +81,48 @@ def test_config3_two_streams_many_frames_vs_oracle():
         c.close()
 
 
+@pytest.mark.parametrize("tail", ["1", "0", None], ids=["tail_forced", "tail_off", "tail_by_hint"])
+def test_config3_tail_kernel_vs_oracle(tail, monkeypatch):
+    """Bounces >= 3 run to their end in one launch (wf_tail_kernel) when few paths are left: forced on, forced off and
+    chosen by the previous batch's queue size (4 batches of 2 frames on one stream pair), all equal to the oracle."""
+    W, H, n = 256, 144, 8
+    scene, cam = _sponza(W, H)
+    ref, cnt = _oracle_frames(scene, cam, W, H, range(n), 8)
+    if tail is None:
+        monkeypatch.delenv("RT_TAIL", raising=False)
+    else:
+        monkeypatch.setenv("RT_TAIL", tail)
+    c = librt.Context(device=0, max_depth=8, rr_start_depth=3, frames_in_flight=4)
+    try:
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(cam.ubo(), CLEAR, 0, n)
+        _assert_bits(c.readback(), ref, f"sponza-proxy depth 8, RT_TAIL={tail}")
+        _assert_counters(c.counters(), cnt, False)
+    finally:
+        c.close()
+
+
+def test_tail_kernel_in_a_lit_scene_vs_oracle(monkeypatch):
+    """The tail kernel's variant with lights (inline light sample and visibility query, as the megakernel): Cornell PBR,
+    depth 6, roulette from depth 3, forced on."""
+    W = H = 192
+    scene = fixture_scene("cornell_pbr")
+    cam = rb.Camera(position=(0.0, 1.0, 4.5), aspect=1.0, target=(0.0, 1.0, 0.0))
+    ref, cnt = _oracle_frames(scene, cam, W, H, range(4), 6)
+    monkeypatch.setenv("RT_TAIL", "1")
+    c = librt.Context(device=0, max_depth=6, rr_start_depth=3, frames_in_flight=2)
+    try:
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(cam.ubo(), CLEAR, 0, 4)
+        _assert_bits(c.readback(), ref, "cornell_pbr depth 6 with the tail kernel")
+        _assert_counters(c.counters(), cnt, False)
+        assert int(cnt[1]) > 0
+    finally:
+        c.close()
+
+
 def test_config3_full_resolution_band_vs_oracle():
     """1920x1080, depth 8: the GPU traces the whole frame, the oracle the rows 500..563 of frames 0 and 1 (the band crosses
     the colonnade and the sky opening).  Seeds and camera rays depend on the full launch size, so this is the
