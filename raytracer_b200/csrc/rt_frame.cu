@@ -533,6 +533,9 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel
 #define RT_PKT_MIN_BLOCKS 8
 #endif
 #define RT_PKT_MARGIN 4e-6f
+#ifndef RT_PKT_GROUP_SLOT
+#define RT_PKT_GROUP_SLOT 1
+#endif
 
 // min / max over the warp of floats that all carry the sign `neg` (unsigned order of the bit patterns)
 __device__ __forceinline__ float warp_fmin_signed(float v, bool neg) {
@@ -557,6 +560,9 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
     const uint32_t lane = threadIdx.x & 31u, c = lane & 7u;
     uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     uint2 stk[RT_STACK_SIZE];
+#if RT_PKT_GROUP_SLOT
+    const bool grp_fast = n % (32u * R) == 0u && n_px % (32u * R) == 0u && (width * RT_TILE_H) % (32u * R) == 0u && width % RT_TILE_W == 0u;
+#endif
     for (;;) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&wf.ctrl[CT_CUR_PKT], 1u);
@@ -575,11 +581,31 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
         bool ok = true;
         {
             uint32_t sb0 = 0, ox0 = 0, oy0 = 0, oz0 = 0;
+#if RT_PKT_GROUP_SLOT
+            // primary_slot() for the whole group at once: when frames and 8-row bands are whole numbers of groups, the group's
+            // 32 R entries lie in one band of one frame, so the two run-time divisions are taken once per group instead of once per ray
+            // (they were 2 % of the kernel's instructions).  Same slots as primary_slot(): tile (b0 >> 5) + k, pixel `lane` of the tile.
+            uint32_t gs_base = 0u, gs_step = 0u;
+            if (grp_fast) {
+                const uint32_t i0 = g * (32u * R);
+                const uint32_t lane_f = i0 / n_px, r0 = i0 - lane_f * n_px;
+                const uint32_t band_px = width * RT_TILE_H;
+                const uint32_t band = r0 / band_px, b0 = r0 - band * band_px;
+                const bool tiled = (band + 1u) * band_px <= n_px;  // rows that do not fill a band keep the linear order
+                gs_base = lane_f * n_px + (tiled ? (band * RT_TILE_H + lane / RT_TILE_W) * width + (b0 >> 5) * RT_TILE_W + (lane % RT_TILE_W)
+                                                 : r0 + lane);
+                gs_step = tiled ? RT_TILE_W : 32u;
+            }
+#endif
 #pragma unroll
             for (int k = 0; k < R; k++) {
                 const uint32_t i = (g * R + (uint32_t)k) * 32u + lane;
                 if (i < n) valid |= 1u << k;
+#if RT_PKT_GROUP_SLOT
+                slot[k] = grp_fast ? gs_base + (uint32_t)k * gs_step : primary_slot(i < n ? i : n - 1u, width, n_px);
+#else
                 slot[k] = primary_slot(i < n ? i : n - 1u, width, n_px);
+#endif
 #if RT_FUSED_RAYGEN
                 // the ray-gen shader runs here (simple.rgen:70-85): no ray-gen launch, no primary ray read back.  The hit
                 // shader wants the direction and the seeds, the per-ray kernel (packets handed back) the origin as well.
