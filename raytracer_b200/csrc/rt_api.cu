@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cmath>
 #include <string>
 #include <thread>
 #include <vector>
@@ -186,6 +187,58 @@ void rt_destroy(rt_ctx* ctx) {
 }  // extern "C"
 
 // ---- scene tables ------------------------------------------------------------------------------
+// ---- first-hit filter: which objects qualify (DevObject::dead_diffuse) -----------------------------------------------------
+// A hit that draws the Lambert lobe on a material with metallic == 1 multiplies the throughput by exactly zero
+// (simple.rchit:416-422: albedo * (1 - metallic) * (1 - F) / pi), so the path ends without a colour term — PROVIDED every
+// intermediate of the hit shader is finite: a NaN normal turns `payload.hit` false and the ray-gen shader adds the sky term
+// instead (the object-without-normals rule).  The three checks below guarantee finiteness, conservatively.
+// True when every vertex normal is finite with length in [0.5, 2] and the three normals of every triangle have pairwise dot
+// products >= 0.1: any barycentric mix of them is then finite and at least 0.28 long.
+static bool mesh_normals_safe(const HostMesh& m) {
+    for (const rt_vertex& v : m.v) {
+        double l2 = 0.0;
+        for (int k = 0; k < 3; k++) {
+            if (!std::isfinite(v.normal[k])) return false;
+            l2 += (double)v.normal[k] * v.normal[k];
+        }
+        if (!(l2 >= 0.25 && l2 <= 4.0)) return false;
+    }
+    for (size_t t = 0; t + 2 < m.idx.size(); t += 3) {
+        const float* a = m.v[m.idx[t]].normal;
+        const float* b = m.v[m.idx[t + 1]].normal;
+        const float* c = m.v[m.idx[t + 2]].normal;
+        const double ab = (double)a[0] * b[0] + (double)a[1] * b[1] + (double)a[2] * b[2];
+        const double ac = (double)a[0] * c[0] + (double)a[1] * c[1] + (double)a[2] * c[2];
+        const double bc = (double)b[0] * c[0] + (double)b[1] * c[1] + (double)b[2] * c[2];
+        if (!(ab >= 0.1 && ac >= 0.1 && bc >= 0.1)) return false;
+    }
+    return true;
+}
+// True when mat3(model) is finite, of ordinary size (Frobenius norm in [1e-6, 1e6]) and well conditioned (norm x norm of the
+// inverse <= 1e4): the float normal matrix the device derives from it (cofactors / determinant) then maps a unit normal to a
+// finite vector whose squared length neither overflows nor underflows.
+static bool model_matrix_safe(const float* model16) {
+    double a[3][3], fro2 = 0.0;
+    for (int c = 0; c < 3; c++)
+        for (int r = 0; r < 3; r++) {
+            a[r][c] = model16[c * 4 + r];
+            if (!std::isfinite(a[r][c])) return false;
+            fro2 += a[r][c] * a[r][c];
+        }
+    const double c00 = a[1][1] * a[2][2] - a[1][2] * a[2][1], c01 = a[1][2] * a[2][0] - a[1][0] * a[2][2], c02 = a[1][0] * a[2][1] - a[1][1] * a[2][0];
+    const double c10 = a[0][2] * a[2][1] - a[0][1] * a[2][2], c11 = a[0][0] * a[2][2] - a[0][2] * a[2][0], c12 = a[0][1] * a[2][0] - a[0][0] * a[2][1];
+    const double c20 = a[0][1] * a[1][2] - a[0][2] * a[1][1], c21 = a[0][2] * a[1][0] - a[0][0] * a[1][2], c22 = a[0][0] * a[1][1] - a[0][1] * a[1][0];
+    const double det = a[0][0] * c00 + a[0][1] * c01 + a[0][2] * c02;
+    if (!std::isfinite(det) || det == 0.0) return false;
+    const double cof2 = c00 * c00 + c01 * c01 + c02 * c02 + c10 * c10 + c11 * c11 + c12 * c12 + c20 * c20 + c21 * c21 + c22 * c22;
+    const double fro = std::sqrt(fro2), inv_fro = std::sqrt(cof2) / std::fabs(det);
+    return fro >= 1e-6 && fro <= 1e6 && std::isfinite(inv_fro) && fro * inv_fro <= 1e4;
+}
+static bool material_dead_diffuse(const rt_material& m) {
+    return m.metallic == 1.0f && std::isfinite(m.albedo[0]) && std::isfinite(m.albedo[1]) && std::isfinite(m.albedo[2]) &&
+           std::isfinite(m.roughness);
+}
+
 static void make_dev_object(const rt_ctx* ctx, uint32_t i, uint32_t tri_offset, DevObject* o) {
     const rt_object& src = ctx->objects[i];
     const HostMesh& m = ctx->meshes[src.mesh_index];
@@ -199,6 +252,7 @@ static void make_dev_object(const rt_ctx* ctx, uint32_t i, uint32_t tri_offset, 
     o->tri_offset = tri_offset;
     o->n_tris = (uint32_t)(m.idx.size() / 3);
     o->mesh_index = src.mesh_index;
+    o->dead_diffuse = (m.normals_safe && model_matrix_safe(src.model) && material_dead_diffuse(ctx->materials[src.material_index])) ? 1u : 0u;
 }
 
 __global__ void normal_matrix_kernel(DevObject* objects, uint32_t n) {
@@ -219,10 +273,12 @@ static int upload_tables(rt_ctx* ctx) {
     std::vector<uint32_t> offs(no + 1);
     std::vector<DevLight> lights;
     uint32_t off = 0;
+    ctx->any_dead_diffuse = false;
     for (uint32_t i = 0; i < no; i++) {
         offs[i] = off;
         make_dev_object(ctx, i, off, &dobj[i]);
         off += dobj[i].n_tris;
+        if (dobj[i].dead_diffuse) ctx->any_dead_diffuse = true;
         // a light is any object whose material has emission_power > 0 (gpu_scene.odin:366-379)
         const rt_material& mat = ctx->materials[ctx->objects[i].material_index];
         if (mat.emission_power > 0.0f) {
@@ -255,6 +311,10 @@ static int upload_tables(rt_ctx* ctx) {
                                     cudaMemcpyHostToDevice, ctx->stream));
     if (no) normal_matrix_kernel<<<(no + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_objects.p, no);
     RT_CUDA_TRY(cudaGetLastError());
+    if (no && launch_object_spec_prob(ctx->d_objects.p, ctx->d_materials.p, no, ctx->stream) != RT_OK) {
+        set_error("upload_tables: object_spec_prob_kernel failed to launch");
+        return RT_ERR_CUDA;
+    }
     RT_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->tables_dirty = false;
     return RT_OK;
@@ -340,6 +400,7 @@ SceneView rt_scene_view(const rt_ctx* ctx) {
     sc.n_objects = (uint32_t)ctx->objects.size();
     sc.n_tris = ctx->n_tris;
     sc.n_nodes = ctx->bvh.n_nodes;
+    sc.any_dead_diffuse = (ctx->any_dead_diffuse && ctx->n_lights == 0u) ? 1u : 0u;
     return sc;
 }
 
@@ -367,6 +428,7 @@ int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const 
         hm[i].idx.assign(m.indices, m.indices + m.n_indices);
         hm[i].vertex_base = (uint32_t)nv;
         hm[i].index_base = (uint32_t)ni;
+        hm[i].normals_safe = mesh_normals_safe(hm[i]);
         nv += m.n_vertices;
         ni += m.n_indices;
     }

@@ -157,6 +157,8 @@ struct FrameResources {
     cudaEvent_t done_accumulate = nullptr;  // recorded after the accumulation of this batch
 };
 int wavefront_alloc(WavefrontBuffers** wf, uint32_t n_pixels, std::string& err);
+// fills DevObject::spec_prob of every object with the hit shader's own specularProbability of its material (first-hit filter)
+int launch_object_spec_prob(DevObject* objects, const rt_material* materials, uint32_t n, cudaStream_t stream);
 void wavefront_free(WavefrontBuffers* wf);
 int launch_frame_wavefront(const SceneView& sc, const FrameParams& fp, FrameResources& res, cudaStream_t stream,
                            std::string& err);
@@ -187,6 +189,7 @@ struct HostMesh {
     std::vector<rt_vertex> v;
     std::vector<uint32_t> idx;
     uint32_t vertex_base = 0, index_base = 0;
+    bool normals_safe = false;  // every interpolated normal on the mesh is finite and non-zero (mesh_normals_safe, rt_api.cu)
 };
 
 #ifndef RT_N_STREAMS
@@ -227,6 +230,7 @@ struct rt_ctx {
     rt::DevBuf<rt_material> d_materials;
     rt::BuildOutput bvh;
     uint32_t n_tris = 0, n_lights = 0;
+    bool any_dead_diffuse = false;  // upload_tables: some object qualifies for the first-hit filter (DevObject::dead_diffuse)
 
     // target
     uint32_t width = 0, height = 0, local_rows = 0;

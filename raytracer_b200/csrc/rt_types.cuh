@@ -77,12 +77,19 @@ struct __align__(16) DevObject {  // 128 B
     uint32_t tri_offset;  // first flat triangle id
     uint32_t n_tris;
     uint32_t mesh_index;
-    uint32_t pad[4];
+    // First-hit filter of the packet kernel (rt_frame.cu, "dead diffuse lobe"): 1 when a hit on this object that draws the Lambert
+    // lobe ends its path without a colour term whatever the geometry — metallic == 1 makes the lobe's value exactly zero, and the
+    // object's normals and matrix are checked (host side, rt_api.cu) to keep every intermediate finite.  spec_prob is
+    // specularProbability (simple.rchit:69-75) of the object's material, computed on the device by the shader's own function.
+    uint32_t dead_diffuse;
+    float spec_prob;
+    uint32_t pad[2];
 };
 static_assert(sizeof(DevObject) == 128, "DevObject is 128 bytes");
 static_assert(offsetof(DevObject, nrm) == 48 && offsetof(DevObject, material_index) == 84 && offsetof(DevObject, light_index) == 88 &&
                   offsetof(DevObject, vertex_base) == 92 && offsetof(DevObject, index_base) == 96,
               "shade_hit reads DevObject as six 16-byte words");
+static_assert(offsetof(DevObject, dead_diffuse) == 112 && offsetof(DevObject, spec_prob) == 116, "the filter reads (dead_diffuse, spec_prob) as one 64-bit word");
 
 struct __align__(16) DevLight {  // 64 B
     float transform[12];  // as DevObject.model
@@ -116,6 +123,7 @@ struct SceneView {
     uint32_t n_objects;
     uint32_t n_tris;
     uint32_t n_nodes;
+    uint32_t any_dead_diffuse;  // some object has DevObject::dead_diffuse set (and the scene no light): the first-hit filter is worth running
 };
 
 struct FrameParams {

@@ -123,6 +123,73 @@ def test_tail_kernel_in_a_lit_scene_vs_oracle(monkeypatch):
         c.close()
 
 
+# ---- first-hit filter (end of wf_extend_packet_kernel): paths whose end needs no hit shader ------------------------------
+@pytest.mark.parametrize("size", [(320, 180), (300, 170)], ids=["whole_groups", "ragged_groups"])
+@pytest.mark.parametrize("flt", ["0", None], ids=["filter_off", "filter_on"])
+def test_config3_first_hit_filter_vs_oracle(flt, size, monkeypatch):
+    """Light-less scene, all-metal materials (what the reference's loader makes of Sponza): a first hit that draws the Lambert
+    lobe multiplies the throughput by exactly zero, so the packet kernel ends such paths (and misses) itself and hands only the
+    rest to the hit shader.  On and off, at a width that is a whole number of 128-ray groups and at one that is not, the image
+    and the ray / hit counters equal the oracle's."""
+    W, H = size
+    n = 4
+    scene, cam = _sponza(W, H)
+    ref, cnt = _oracle_frames(scene, cam, W, H, range(n), 8)
+    if flt is None:
+        monkeypatch.delenv("RT_FILTER", raising=False)
+    else:
+        monkeypatch.setenv("RT_FILTER", flt)
+    c = librt.Context(device=0, max_depth=8, rr_start_depth=3, frames_in_flight=2)
+    try:
+        c.build_scene(scene)
+        c.resize(W, H)
+        c.trace_frames(cam.ubo(), CLEAR, 0, n)
+        _assert_bits(c.readback(), ref, f"sponza-proxy {W}x{H}, RT_FILTER={flt}")
+        _assert_counters(c.counters(), cnt, False)
+    finally:
+        c.close()
+
+
+def _metal_yard():
+    """Light-less scene whose metallic objects differ in whether the filter may end their paths early: a clean sphere (may), a
+    sphere without normals (NaN normal -> sky colour, simple.rgen:106-109), a sphere whose vertex normals alternate in sign
+    (finite, but the interpolated normal is not bounded away from zero), a sphere squashed by 1e-5 along y (ill-conditioned
+    normal matrix), and non-metallic surfaces (never filtered)."""
+    s = rb.Scene()
+    metal = s.add_material(rb.Material("metal", albedo=(0.9, 0.7, 0.4), roughness=0.6, metallic=1.0))
+    rough = s.add_material(rb.Material("rough_metal", albedo=(0.6, 0.6, 0.7), roughness=1.0, metallic=1.0))
+    half = s.add_material(rb.Material("half", albedo=(0.7, 0.3, 0.3), roughness=0.5, metallic=0.5))
+    plane = s.add_mesh(rb.create_plane())
+    sphere = s.add_mesh(rb.create_sphere())
+    bare = rb.create_sphere()
+    bare.vertices["normal"][:] = 0.0
+    bare = s.add_mesh(bare)
+    creased = rb.create_sphere()
+    creased.vertices["normal"][::2] *= -1.0
+    creased = s.add_mesh(creased)
+    s.add_object("floor", plane, rough, (0, -1, 0), (-90, 0, 0), (8, 8, 1))
+    s.add_object("back", plane, half, (0, 0.5, 2.0), (0, 180, 0), (8, 3, 1))
+    s.add_object("clean", sphere, metal, (-1.5, -0.5, 0.3), (0, 0, 0), (0.5, 0.5, 0.5))
+    s.add_object("bare", bare, metal, (-0.5, -0.5, 0.3), (0, 0, 0), (0.45, 0.45, 0.45))
+    s.add_object("creased", creased, metal, (0.5, -0.5, 0.3), (0, 0, 0), (0.45, 0.45, 0.45))
+    s.add_object("squashed", sphere, metal, (1.5, -0.3, 0.3), (60, 0, 0), (0.5, 1e-5, 0.5))
+    s.add_object("half", sphere, half, (0.0, 0.4, 1.0), (0, 0, 0), (0.4, 0.4, 0.4))
+    s.changes.clear()
+    return s
+
+
+def test_first_hit_filter_leaves_unsafe_objects_to_the_hit_shader():
+    """The filter's shortcut holds only while every intermediate of the hit shader is finite; objects for which the host cannot
+    guarantee that (no normals, normals that may cancel, an ill-conditioned matrix) and non-metals go through the hit shader.
+    Wavefront (filter on) and megakernel (no filter) both equal the oracle, and the normal-less sphere shows the sky colour."""
+    scene = _metal_yard()
+    W, H = 256, 144
+    cam = rb.Camera(position=(0.0, 0.2, -4.0), aspect=W / H, target=(0.0, -0.2, 0.0))
+    ref, cnt = _run_vs_oracle(scene, cam, W, H, 4, 5, "metal yard")
+    assert int(cnt[1]) == 0 and int(cnt[0]) > 4 * W * H  # no light, hence no visibility ray; there are continuation rays
+    assert np.isfinite(ref).all()
+
+
 def test_config3_full_resolution_band_vs_oracle():
     """1920x1080, depth 8: the GPU traces the whole frame, the oracle the rows 500..563 of frames 0 and 1 (the band crosses
     the colonnade and the sky opening).  Seeds and camera rays depend on the full launch size, so this is the
