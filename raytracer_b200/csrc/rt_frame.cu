@@ -545,7 +545,6 @@ __global__ void __launch_bounds__(128, RT_COOP_MIN_BLOCKS) wf_extend_coop_kernel
 #define RT_PKT_MIN_BLOCKS 8
 #endif
 #define RT_PKT_MARGIN 4e-6f
-#define RT_HIT_DONE 0xFFFFFFFEu /* instance word of a hit record whose path the first-hit filter has already ended */
 #ifndef RT_PKT_GROUP_SLOT
 #define RT_PKT_GROUP_SLOT 1
 #endif
@@ -565,15 +564,13 @@ __device__ __forceinline__ float warp_fmax_signed(float v, bool neg) {
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kernel(SceneView sc, FrameParams fp, WfView wf, uint32_t* fb_queue,
-                                                                                  uint32_t width, uint32_t n_px, uint32_t filter,
+                                                                                  uint32_t width, uint32_t n_px,
                                                                                   DevCounters* counters) {
-    // filter != 0: the first-hit filter (at the end of a packet, below) is on — paths whose end is known without the hit shader get
-    // their colour here and RT_HIT_DONE as the instance of their hit record; wf_shade_kernel<., true, false, true> skips those.
     constexpr int R = RT_PKT_RPL;
     const uint32_t n = wf.ctrl[CT_Q0];
     const uint32_t n_groups = (n + 32u * R - 1u) / (32u * R);
     const uint32_t lane = threadIdx.x & 31u, c = lane & 7u;
-    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0, c_hits = 0;
+    uint32_t c_nodes = 0, c_tris = 0, c_rays = 0;
     uint2 stk[RT_STACK_SIZE];
 #if RT_PKT_GROUP_SLOT
     const bool grp_fast = n % (32u * R) == 0u && n_px % (32u * R) == 0u && (width * RT_TILE_H) % (32u * R) == 0u && width % RT_TILE_W == 0u;
@@ -589,7 +586,6 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
         float ikz[R], bt[R], bu[R], bv[R];
         vec3 idl[R];  // 1/d of the lane's rays, until the hulls are built
         uint32_t bid[R], btri[R];
-        uint32_t sd[R];  // the path's seed (direction.w, as ray-gen left it): the filter at the end replays the hit shader's draws
         uint32_t kzs = 0u, valid = 0u;
         float ox, oy, oz;
         float ilx, ihx, ily, ihy, ilz, ihz;
@@ -653,7 +649,6 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                 ok = ok && sb == sb0 && __float_as_uint(o4.x) == ox0 && __float_as_uint(o4.y) == oy0 && __float_as_uint(o4.z) == oz0 &&
                      fabsf(d4.x) >= 1e-20f && fabsf(d4.y) >= 1e-20f && fabsf(d4.z) >= 1e-20f;  // the last three also reject NaN
                 const TravRay r = trav_setup(mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
-                sd[k] = __float_as_uint(d4.w);
                 sh[k] = r.sh;
                 const uint32_t kz = (r.rbits >> 3) & 3u;
                 kzs |= kz << (2 * k);
@@ -673,7 +668,6 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                 if (lane == 0) base = atomicAdd(&wf.ctrl[CT_FB], (uint32_t)__popc(bal));
                 base = __shfl_sync(0xFFFFFFFFu, base, 0);
                 if (v) fb_queue[base + __popc(bal & ((1u << lane) - 1u))] = slot[k];
-                if (v && filter) wf.col[slot[k]] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);  // as at the end of a traced packet
             }
 #if RT_FUSED_RAYGEN
             // origins are not compared lane by lane here (all equal inv_view's translation): the lane's own value is the ray's
@@ -808,38 +802,6 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
                     inst = __float_as_uint(__ldg(tq + 7));
                     prim = __float_as_uint(__ldg(tq + 11));
                 }
-                // ---- first-hit filter (light-less scenes): paths whose end is known without running the hit shader -------------
-                // (a) a miss: the sky term of simple.rgen:106-109 on the initial payload (colour 0, throughput 1).
-                // (b) a hit on an object with DevObject::dead_diffuse whose lobe draw picks the Lambert lobe with a direction above
-                // the surface (cosine direction: z = sqrt(ry) > 0 iff ry > 0): sample_brdf returns value = albedo * (1 - metallic) *
-                // (1 - F) / pi = 0 exactly with a finite positive pdf, shade_hit leaves payload.hit true and throughput 0, the ray-gen
-                // loop stops at simple.rgen:115-118 and the pixel keeps colour 0.  The draws are the hit shader's, in its order:
-                // light-sample decision (simple.rchit:622), rx, ry (:638), lobe (:408).  Everything else goes to wf_shade_kernel.
-                // The colour of EVERY ray of the packet is written here (zero: the slot's initial value, which the hit shader's
-                // first launch then only overwrites with a sky term): whole 64-byte tile rows instead of the filtered pixels' lone
-                // 16 bytes, which cost a sector fill each (ncu: +3 GB written, +1.1 GB read per launch when only those were written).
-                if (filter) {
-                    float4 c4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                    if (inst == 0xFFFFFFFFu) {
-                        const vec3 c = add3(mk3(0.0f, 0.0f, 0.0f), mul3(mk3(1.0f, 1.0f, 1.0f), mk3(fp.clear[0], fp.clear[1], fp.clear[2])));
-                        c4 = make_float4(c.x, c.y, c.z, 0.0f);
-                        inst = RT_HIT_DONE;
-                    } else {
-                        const uint2 dd = __ldg(reinterpret_cast<const uint2*>(&sc.objects[inst].dead_diffuse));
-                        if (dd.x != 0u) {
-                            uint32_t s = sd[k];
-                            rnd01(s);
-                            rnd01(s);
-                            const float ry = rnd01(s);
-                            const float lobe = rnd01(s);
-                            if (!(lobe < __uint_as_float(dd.y)) && ry > 0.0f) {
-                                inst = RT_HIT_DONE;
-                                if (COUNT) c_hits++;
-                            }
-                        }
-                    }
-                    wf.col[slot[k]] = c4;
-                }
                 wf.hit[slot[k]] = make_uint4(__float_as_uint(bu[k]), __float_as_uint(bv[k]), inst, prim);
             }
         }
@@ -848,7 +810,6 @@ __global__ void __launch_bounds__(128, RT_PKT_MIN_BLOCKS) wf_extend_packet_kerne
         warp_add(&counters->extend_rays, c_rays);
         warp_add(&counters->nodes, c_nodes);
         warp_add(&counters->tris, c_tris);
-        warp_add(&counters->hits, c_hits);
     }
 }
 
@@ -869,11 +830,19 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 #ifndef RT_PACK_SEEDS
 #define RT_PACK_SEEDS 1
 #endif
-// DENSE (first bounce after the first-hit filter, no queue): a warp takes 128 consecutive slots, keeps those whose hit record is not
-// marked RT_HIT_DONE and runs the hit shader on them 32 at a time — compaction inside the chunk, so the survivors (43 % on the
-// Sponza proxy) fill whole warps while staying in pixel order.  (A global survivor queue filled by the packet kernel was tried first:
-// its entries interleave the tiles of all packets in flight, the hit shader got only 11 % faster for 57 % fewer entries and the
-// bounce-1 kernels, which inherit the order, 32 % slower.)
+// DENSE = the first bounce of a light-less scene with the FIRST-HIT FILTER: a warp scans 128 consecutive slots at a time and ends,
+// without running the hit shader, the paths whose outcome it can tell from the hit record and the path's seed alone:
+// (a) a miss: the sky term of simple.rgen:106-109 on the initial payload (colour 0, throughput 1);
+// (b) a hit on an object with DevObject::dead_diffuse whose lobe draw picks the Lambert lobe with a direction above the surface
+//     (cosine direction: z = sqrt(ry) > 0 iff ry > 0): sample_brdf returns value = albedo * (1 - metallic) * (1 - F) / pi = 0 exactly
+//     with a finite positive pdf, shade_hit leaves payload.hit true and the throughput 0, the ray-gen loop stops at
+//     simple.rgen:115-118 and the pixel keeps colour 0.  The draws are the hit shader's own, in its order: light-sample decision
+//     (simple.rchit:622), rx, ry (:638), lobe (:408).  What makes (b) exact is checked per object on the host (rt_api.cu).
+// The scan writes every slot's initial colour (coalesced); the survivors (43 % on the Sponza proxy, where the reference's loader
+// leaves every material metallic) wait in a per-warp ring until 32 of them fill a warp, so the hit shader runs with all lanes and
+// in pixel order.  History (profiles/r2q_filter.md): a global survivor queue filled at the end of the packet kernel interleaved
+// the tiles of all packets in flight — hit shader 11 % faster for 57 % fewer entries, bounce-1 kernels 32 % slower; marking the
+// hit records there instead cost the packet kernel 8 % (scattered colour writes, a dependent table load per ray).
 template <bool COUNT, bool FIRST, bool LIGHTS, bool DENSE = false>
 __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
                                                        uint32_t q_idx, uint32_t* q_out, int depth, DevCounters* counters) {
@@ -956,7 +925,7 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
                 if (res.emissive_add) ps.color = add3(ps.color, res.emissive);
                 if (sky) ps.color = add3(ps.color, mul3(ps.throughput, clearc));
             }
-            // DENSE: the packet kernel has initialised the slot's colour (zero), only a sky term changes it
+            // DENSE: the scan has initialised the slot's colour (zero), only a sky term changes it
             if ((FIRST && !DENSE) || (LIGHTS ? col_term : sky)) wf.col[slot] = make_float4(ps.color.x, ps.color.y, ps.color.z, 0.0f);
             if (push_next) {
                 const uint32_t fl = LIGHTS ? ((ps.is_specular ? PF_SPECULAR : 0u) | (ps.did_direct ? PF_DID_DIRECT : 0u)) : 0u;
@@ -1002,10 +971,41 @@ __global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHA
         uint32_t c0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 128u;
         for (;;) {
             while (count < 32u && c0 < n) {  // warp-uniform: take in the survivors of the warp's next chunk
+                // all of the chunk's loads first (eight per lane in flight), then the decisions
+                uint32_t insts[4], seeds[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     const uint32_t i = c0 + 32u * (uint32_t)j + lane;
-                    const bool live = i < n && wf.hit[i].z != RT_HIT_DONE;
+                    insts[j] = i < n ? wf.hit[i].z : 0xFFFFFFFFu;
+                    seeds[j] = i < n ? __float_as_uint(wf.ray_d[i].w) : 0u;  // the path's seed, as ray-gen left it (PACKED)
+                }
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t i = c0 + 32u * (uint32_t)j + lane;
+                    bool live = false;
+                    if (i < n) {
+                        const uint32_t inst = insts[j];
+                        float4 c4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                        if (inst == 0xFFFFFFFFu) {
+                            const vec3 c = add3(mk3(0.0f, 0.0f, 0.0f), mul3(mk3(1.0f, 1.0f, 1.0f), clearc));
+                            c4 = make_float4(c.x, c.y, c.z, 0.0f);
+                        } else {
+                            live = true;
+                            const uint2 dd = __ldg(reinterpret_cast<const uint2*>(&sc.objects[inst].dead_diffuse));
+                            if (dd.x != 0u) {
+                                uint32_t s = seeds[j];
+                                rnd01(s);
+                                rnd01(s);
+                                const float ry = rnd01(s);
+                                const float lobe = rnd01(s);
+                                if (!(lobe < __uint_as_float(dd.y)) && ry > 0.0f) {
+                                    live = false;
+                                    if (COUNT) c_hits++;
+                                }
+                            }
+                        }
+                        wf.col[i] = c4;
+                    }
                     const uint32_t b = __ballot_sync(0xFFFFFFFFu, live);
                     if (live) ring[(head + count + (uint32_t)__popc(b & lt)) % 160u] = i;
                     count += (uint32_t)__popc(b);
@@ -1346,11 +1346,10 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
     const char* tail_env = getenv("RT_TAIL");  // tests and A/B runs: "0" = never, "1" = whenever the depths allow it
     const bool tail_small = tail_env ? tail_env[0] == '1' : tail_hint <= (uint32_t)dims.num_sms * 1024u;
     const bool tail_ok = RT_TAIL_DEPTH > 0 && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY) && fp.max_depth - RT_TAIL_DEPTH >= 2 && tail_small;
-    // first-hit filter (end of wf_extend_packet_kernel): light-less scenes with qualifying objects, packets on.  RT_FILTER=0 turns
-    // it off (tests, A/B runs); the image does not depend on it.
+    // first-hit filter (the scan of wf_shade_kernel<., true, false, true>): light-less scenes with qualifying objects.  RT_FILTER=0
+    // turns it off (tests, A/B runs); the image does not depend on it.
     const char* filter_env = getenv("RT_FILTER");
-    const bool filter = sc.any_dead_diffuse != 0u && sc.n_lights == 0u && RT_PACK_SEEDS && !RT_FUSED_RAYGEN && !(fp.flags & RT_FLAG_PER_RAY_PRIMARY) &&
-                        !(filter_env && filter_env[0] == '0');
+    const bool filter = sc.any_dead_diffuse != 0u && sc.n_lights == 0u && RT_PACK_SEEDS && !RT_FUSED_RAYGEN && !(filter_env && filter_env[0] == '0');
     for (int depth = 0; depth < fp.max_depth; depth++) {
         if (depth == RT_TAIL_DEPTH && tail_ok) {
             const int g = std::min(dims.num_sms * 8, need);
@@ -1370,7 +1369,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
             // packets first; what they hand back (tiles across an axis plane) goes through the per-ray kernel
             pf.begin(RT_K_EXTEND_PACKET, stream);
             wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, fp, v, w->queue[0].p, fp.width, n_px,
-                                                                                     filter ? 1u : 0u, res.counters);
+                                                                                     res.counters);
             pf.end(stream);
             pf.begin(RT_K_EXTEND, stream);
             if (RT_EXTEND_COOP)
@@ -1497,7 +1496,7 @@ static int corner_hits_t(const SceneView& sc, const FrameParams& fp, FrameResour
     const int need = (int)((n + 127) / 128);
     corner_raygen_kernel<<<std::min<uint32_t>((n + 255) / 256, (uint32_t)dims.num_sms * 16), 256, 0, stream>>>(fp, d_rows, n_rows, v);
     wf_reset_kernel<<<1, 32, 0, stream>>>(v.ctrl, 0u, n);
-    wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, fp, v, w->queue[0].p, fp.width, n, 0u, res.counters);
+    wf_extend_packet_kernel<COUNT><<<std::min(g_pkt, need), 128, 0, stream>>>(sc, fp, v, w->queue[0].p, fp.width, n, res.counters);
     wf_extend_coop_kernel<COUNT><<<std::min(g_coop, need), 128, 0, stream>>>(sc, v, w->queue[0].p, CT_FB, fp.width, n, res.counters);
     FRAME_TRY(cudaGetLastError());
     if (res.launches) *res.launches += 4;

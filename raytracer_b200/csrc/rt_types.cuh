@@ -77,7 +77,7 @@ struct __align__(16) DevObject {  // 128 B
     uint32_t tri_offset;  // first flat triangle id
     uint32_t n_tris;
     uint32_t mesh_index;
-    // First-hit filter of the packet kernel (rt_frame.cu, "dead diffuse lobe"): 1 when a hit on this object that draws the Lambert
+    // First-hit filter of the hit shader's first launch (rt_frame.cu, wf_shade_kernel DENSE, "dead diffuse lobe"): 1 when a hit on this object that draws the Lambert
     // lobe ends its path without a colour term whatever the geometry — metallic == 1 makes the lobe's value exactly zero, and the
     // object's normals and matrix are checked (host side, rt_api.cu) to keep every intermediate finite.  spec_prob is
     // specularProbability (simple.rchit:69-75) of the object's material, computed on the device by the shader's own function.

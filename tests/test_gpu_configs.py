@@ -123,13 +123,13 @@ def test_tail_kernel_in_a_lit_scene_vs_oracle(monkeypatch):
         c.close()
 
 
-# ---- first-hit filter (end of wf_extend_packet_kernel): paths whose end needs no hit shader ------------------------------
+# ---- first-hit filter (the scan of the first wf_shade_kernel launch): paths whose end needs no hit shader ------------------------------
 @pytest.mark.parametrize("size", [(320, 180), (300, 170)], ids=["whole_groups", "ragged_groups"])
 @pytest.mark.parametrize("flt", ["0", None], ids=["filter_off", "filter_on"])
 def test_config3_first_hit_filter_vs_oracle(flt, size, monkeypatch):
     """Light-less scene, all-metal materials (what the reference's loader makes of Sponza): a first hit that draws the Lambert
-    lobe multiplies the throughput by exactly zero, so the packet kernel ends such paths (and misses) itself and hands only the
-    rest to the hit shader.  On and off, at a width that is a whole number of 128-ray groups and at one that is not, the image
+    lobe multiplies the throughput by exactly zero, so the first shade launch ends such paths (and misses) in its scan and runs
+    the hit shader on the rest only.  On and off, at a width that is a whole number of 128-ray groups and at one that is not, the image
     and the ray / hit counters equal the oracle's."""
     W, H = size
     n = 4
