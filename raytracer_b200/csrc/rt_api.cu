@@ -192,8 +192,9 @@ void rt_destroy(rt_ctx* ctx) {
 // (simple.rchit:416-422: albedo * (1 - metallic) * (1 - F) / pi), so the path ends without a colour term — PROVIDED every
 // intermediate of the hit shader is finite: a NaN normal turns `payload.hit` false and the ray-gen shader adds the sky term
 // instead (the object-without-normals rule).  The three checks below guarantee finiteness, conservatively.
-// True when every vertex normal is finite with length in [0.5, 2] and the three normals of every triangle have pairwise dot
-// products >= 0.1: any barycentric mix of them is then finite and at least 0.28 long.
+// True when every vertex normal is finite with length in [0.5, 2] and, for every triangle, each of its three normals has a
+// dot product >= 0.25 with their sum g: any barycentric mix n of them then has g . n >= 0.25, i.e. |n| >= 0.25 / |g| >= 0.04 —
+// finite and safely non-zero (pairwise angles up to ~100 degrees pass, which coarse smooth-shaded meshes need).
 static bool mesh_normals_safe(const HostMesh& m) {
     for (const rt_vertex& v : m.v) {
         double l2 = 0.0;
@@ -204,13 +205,10 @@ static bool mesh_normals_safe(const HostMesh& m) {
         if (!(l2 >= 0.25 && l2 <= 4.0)) return false;
     }
     for (size_t t = 0; t + 2 < m.idx.size(); t += 3) {
-        const float* a = m.v[m.idx[t]].normal;
-        const float* b = m.v[m.idx[t + 1]].normal;
-        const float* c = m.v[m.idx[t + 2]].normal;
-        const double ab = (double)a[0] * b[0] + (double)a[1] * b[1] + (double)a[2] * b[2];
-        const double ac = (double)a[0] * c[0] + (double)a[1] * c[1] + (double)a[2] * c[2];
-        const double bc = (double)b[0] * c[0] + (double)b[1] * c[1] + (double)b[2] * c[2];
-        if (!(ab >= 0.1 && ac >= 0.1 && bc >= 0.1)) return false;
+        const float* n[3] = {m.v[m.idx[t]].normal, m.v[m.idx[t + 1]].normal, m.v[m.idx[t + 2]].normal};
+        const double g[3] = {(double)n[0][0] + n[1][0] + n[2][0], (double)n[0][1] + n[1][1] + n[2][1], (double)n[0][2] + n[1][2] + n[2][2]};
+        for (int i = 0; i < 3; i++)
+            if (!(n[i][0] * g[0] + n[i][1] * g[1] + n[i][2] * g[2] >= 0.25)) return false;
     }
     return true;
 }
