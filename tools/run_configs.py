@@ -169,15 +169,21 @@ def main():
     a = ap.parse_args()
     os.makedirs(a.out, exist_ok=True)
     q = a.quick
-    rows = [
-        run_config("1_cornell_box", "cornell_box", 512, 512, 1, 3, a.out, small=(128, 128)),
-        run_config("1b_cornell_box_d4", "cornell_box", 512, 512, 16, 4, a.out, small=(128, 128)),
-        run_config("2_cornell_pbr", "cornell_pbr", 1024, 1024, 64, 3, a.out, small=(128, 128)),
-        run_config("3_sponza_proxy", "sponza-proxy", 1920, 1080, 32 if q else 256, 8, a.out, small=(160, 90)),
-        run_config("4_conference_restir", "conference", 1920, 1080, 16, 1, a.out, restir=True, small=(96, 54)),
-        run_config("4b_conference_mirror_chairs", "conference_mirror_chairs", 1920, 1080, 64, 3, a.out, small=(160, 90)),
-        run_config("5_multi_dispersion_4k", "multi_dispersion", 3840, 2160, 64 if q else 1024, 3, a.out, small=(160, 90)),
+    specs = [
+        ("1_cornell_box", "cornell_box", 512, 512, 1, 3, dict(small=(128, 128))),
+        ("1b_cornell_box_d4", "cornell_box", 512, 512, 16, 4, dict(small=(128, 128))),
+        ("2_cornell_pbr", "cornell_pbr", 1024, 1024, 64, 3, dict(small=(128, 128))),
+        ("3_sponza_proxy", "sponza-proxy", 1920, 1080, 32 if q else 256, 8, dict(small=(160, 90))),
+        ("4_conference_restir", "conference", 1920, 1080, 16, 1, dict(restir=True, small=(96, 54))),
+        ("4b_conference_mirror_chairs", "conference_mirror_chairs", 1920, 1080, 64, 3, dict(small=(160, 90))),
+        ("5_multi_dispersion_4k", "multi_dispersion", 3840, 2160, 64 if q else 1024, 3, dict(small=(160, 90))),
     ]
+    rows = []
+    for tag, name, W, H, spp, depth, kw in specs:
+        rows.append(run_config(tag, name, W, H, spp, depth, a.out, **kw))
+        print(json.dumps(rows[-1]), flush=True)  # a row is on record as soon as it exists
+        with open(os.path.join(a.out, "configs_partial.json"), "w") as f:
+            json.dump(rows, f, indent=1)
     with open(os.path.join(a.out, "configs.json"), "w") as f:
         json.dump(rows, f, indent=1)
     cols = ["config", "res", "spp", "depth", "triangles", "lights", "mrays_s", "ms_per_frame", "loads_per_ray", "bytes_per_ray", "cpu_full", "speedup", "parity", "ssim"]
