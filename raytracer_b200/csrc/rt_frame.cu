@@ -843,8 +843,11 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 // in pixel order.  History (profiles/r2q_filter.md): a global survivor queue filled at the end of the packet kernel interleaved
 // the tiles of all packets in flight — hit shader 11 % faster for 57 % fewer entries, bounce-1 kernels 32 % slower; marking the
 // hit records there instead cost the packet kernel 8 % (scattered colour writes, a dependent table load per ray).
+#ifndef RT_SHADE_DENSE_MIN_BLOCKS
+#define RT_SHADE_DENSE_MIN_BLOCKS RT_SHADE_MIN_BLOCKS /* 8 / 9 / 10 blocks per SM (64 / 56 / 48 registers): frame 0.4207 / 0.4205 / 0.4207 ms (r2v A/B, twice each) */
+#endif
 template <bool COUNT, bool FIRST, bool LIGHTS, bool DENSE = false>
-__global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
+__global__ void __launch_bounds__(128, LIGHTS ? RT_SHADE_LIT_MIN_BLOCKS : (DENSE ? RT_SHADE_DENSE_MIN_BLOCKS : RT_SHADE_MIN_BLOCKS)) wf_shade_kernel(SceneView sc, FrameParams fp, WfView wf, const uint32_t* q_in,
                                                        uint32_t q_idx, uint32_t* q_out, int depth, DevCounters* counters) {
     constexpr bool PACKED = !LIGHTS && RT_PACK_SEEDS;
     const uint32_t n = wf.ctrl[q_idx];
@@ -1322,6 +1325,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         ds.shw = persistent_grid(wf_shadow_kernel<COUNT>, 128, sms);
         ds.shd = persistent_grid(wf_shade_kernel<COUNT, false, true>, 128, sms);
         ds.shd0 = persistent_grid(wf_shade_kernel<COUNT, false, false>, 128, sms);
+        ds.shd0d = persistent_grid(wf_shade_kernel<COUNT, true, false, true>, 128, sms);
         ds.nee = persistent_grid(wf_nee_kernel<COUNT>, 128, sms);
         ds.ready = true;
     }
@@ -1390,7 +1394,7 @@ static int frame_wavefront_t(const SceneView& sc, const FrameParams& fp, FrameRe
         pf.begin(RT_K_SHADE, stream);
         {
             const bool lit = sc.n_lights != 0u;
-            const int g = std::min(lit ? g_shd : g_shd0, need);
+            const int g = std::min(lit ? g_shd : ((depth == 0 && filter) ? ds.shd0d : g_shd0), need);
             uint32_t* qo = w->queue[q_in ^ 1u].p;
             if (depth == 0 && lit) wf_shade_kernel<COUNT, true, true><<<g, 128, 0, stream>>>(sc, fp, v, qi, q_in, qo, depth, res.counters);
             else if (depth == 0 && filter) wf_shade_kernel<COUNT, true, false, true><<<g, 128, 0, stream>>>(sc, fp, v, qi, q_in, qo, depth, res.counters);

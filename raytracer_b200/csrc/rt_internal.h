@@ -142,7 +142,7 @@ struct KernelProfiler {
 // the first frame a context launches (occupancy query on ITS device), never shared between contexts.
 struct LaunchDims {
     int num_sms = 0;
-    struct Set { bool ready = false; int ext = 0, shw = 0, shd = 0, shd0 = 0, pkt = 0, coop = 0, nee = 0; } set[2];
+    struct Set { bool ready = false; int ext = 0, shw = 0, shd = 0, shd0 = 0, shd0d = 0, pkt = 0, coop = 0, nee = 0; } set[2];
     bool srgb_table_ready = false;  // c_srgb_thresholds uploaded to this context's device
 };
 
