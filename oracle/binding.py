@@ -65,6 +65,8 @@ def lib():
         L.orc_sincos.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
         L.orc_unit_sample_brdf.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_unit_eval_brdf.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_unit_specular_probability.argtypes = [C.c_void_p]
+        L.orc_unit_specular_probability.restype = C.c_float
         L.orc_set_num_threads.argtypes = [C.c_int]
         L.orc_max_threads.restype = C.c_int
         _lib = L

@@ -22,6 +22,7 @@ void raster_gbuffer(const Scene& s, const float* cam, uint32_t W, uint32_t H, fl
 void unit_raster_vertex(const float* model16, const float* pos3, const float* normal3, const float* cam, float out[10]);
 void unit_sample_brdf(const Material& m, V3 wo, float rx, float ry, uint32_t* seed, float out[8]);
 void unit_eval_brdf(const Material& m, V3 wo, V3 wi, float out[4]);
+float unit_specular_probability(const Material& m);
 }  // namespace orc
 
 using namespace orc;
@@ -172,6 +173,7 @@ void orc_sincos(const float* a, uint32_t n, float* s, float* c) {
 void orc_unit_sample_brdf(const void* material44, const float* wo3, float rx, float ry, uint32_t* seed, float* out8) {
     unit_sample_brdf(*(const Material*)material44, v3(wo3[0], wo3[1], wo3[2]), rx, ry, seed, out8);
 }
+float orc_unit_specular_probability(const void* material44) { return unit_specular_probability(*(const Material*)material44); }
 void orc_unit_eval_brdf(const void* material44, const float* wo3, const float* wi3, float* out4) {
     unit_eval_brdf(*(const Material*)material44, v3(wo3[0], wo3[1], wo3[2]), v3(wi3[0], wi3[1], wi3[2]), out4);
 }

@@ -847,6 +847,7 @@ void unit_sample_brdf(const Material& m, V3 wo, float rx, float ry, uint32_t* se
     out[0] = b.direction.x; out[1] = b.direction.y; out[2] = b.direction.z;
     out[3] = b.value.x; out[4] = b.value.y; out[5] = b.value.z; out[6] = b.pdf; out[7] = b.isSpecular ? 1.0f : 0.0f;
 }
+float unit_specular_probability(const Material& m) { return getSpecularProbability(m); }  // simple.rchit:69-75
 void unit_eval_brdf(const Material& m, V3 wo, V3 wi, float out[4]) {
     V3 f = evaluateFullBRDF(wo, wi, m);
     out[0] = f.x; out[1] = f.y; out[2] = f.z;

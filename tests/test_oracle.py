@@ -274,6 +274,52 @@ def test_oracle_reproduces_the_function_vectors_of_rchit_spv(oracle_lib):
         assert np.array_equal(o4[:3].view(np.uint32), z["units/evaluateFullBRDF"][k].view(np.uint32)), k
 
 
+def test_dead_diffuse_rule_of_the_first_hit_filter(oracle_lib):
+    """The rule the CUDA path's first-hit filter rests on (rt_frame.cu, wf_shade_kernel DENSE): on a material with
+    metallic == 1, a lobe draw that picks the Lambert lobe (`rnd >= specularWeight`, simple.rchit:408) with ry > 0 returns a
+    direction above the surface, a value of exactly zero and a finite positive pdf — so the hit shader leaves payload.hit true
+    with throughput 0 and the path ends without a colour term.  Checked (a) on the vectors the SHIPPED rchit.spv computed
+    (tests/golden/spirv_frames.npz) and (b) on 20 000 random inputs through the oracle, with the filter's own predicate (the
+    oracle's specular probability, the LCG draw) deciding which samples the rule is claimed for; incl. grazing and
+    below-horizon view directions, roughness 0 and 1, albedo 0."""
+    import ctypes as C
+
+    z = _spirv_fixture()
+    mats, out = z["units/materials"], z["units/sampleBRDF"]
+    metal = mats[:, 8] == 1.0
+    lambert = metal & (out[:, 7] == 0.0) & (out[:, 2] > 0.0)
+    assert lambert.sum() >= 8  # the fixture holds such draws
+    assert (out[lambert, 3:6] == 0.0).all() and np.isfinite(out[lambert, 6]).all() and (out[lambert, 6] > 0.0).all()
+
+    L = oracle_lib.lib()
+    rng = np.random.default_rng(7)
+    n_claimed = 0
+    for k in range(20000):
+        m = np.zeros(11, np.float32)
+        m[0:3] = rng.choice([0.0, 1.0, rng.random()], 3) if k % 5 == 0 else rng.random(3)
+        m[7] = rng.choice([0.0, 1.0, rng.random()])   # roughness
+        m[8] = 1.0                                       # metallic
+        th = rng.choice([0.0, 1e-7, np.pi / 2 - 1e-6, np.pi / 2, np.pi / 2 + 0.3, rng.random() * np.pi / 2])
+        ph = rng.random() * 2 * np.pi
+        wo = np.array([np.sin(th) * np.cos(ph), np.sin(th) * np.sin(ph), np.cos(th)], np.float32)
+        rx, ry = np.float32(rng.random()), np.float32(rng.choice([0.0, 2.0 ** -24, rng.random()]))
+        seed_in = int(rng.integers(0, 2 ** 32))
+        lobe, _ = oracle_lib.rnd_seq(seed_in, 1)
+        sw = np.float32(L.orc_unit_specular_probability(m.ctypes.data))
+        claimed = (not (lobe[0] < sw)) and ry > 0.0        # the filter's predicate
+        seed = C.c_uint32(seed_in)
+        o8 = np.zeros(8, np.float32)
+        L.orc_unit_sample_brdf(m.ctypes.data, wo.ctypes.data, float(rx), float(ry), C.byref(seed), o8.ctypes.data)
+        if claimed:
+            n_claimed += 1
+            assert o8[7] == 0.0 and o8[2] > 0.0, (k, o8)                      # Lambert lobe, direction above the surface
+            assert (o8[3:6] == 0.0).all(), (k, o8)                             # value exactly zero
+            assert np.isfinite(o8[6]) and o8[6] > 0.0, (k, o8)                # finite positive pdf -> payload.hit stays true
+            thr = np.float32(1.0) * (o8[3:6] * o8[2] / o8[6])                  # simple.rchit:694
+            assert (thr == 0.0).all()
+    assert n_claimed > 3000
+
+
 @pytest.mark.skipif(not os.path.isdir("/root/reference/shaders"), reason="reference mount absent (the fixture itself is committed)")
 def test_the_fixture_is_what_the_binaries_compute(oracle_lib):
     """Re-executes a sample of pixels from /root/reference/shaders/*.spv: the committed frames really come from the binaries."""
