@@ -326,6 +326,13 @@ RT_API int rt_trace_rays_any(rt_ctx* ctx, const float* rays, uint32_t n, const u
 #define RT_STATIC_MAX_RAYS 65536u
 RT_API uint32_t rt_static_max_rays(void);
 RT_API int rt_trace_rays_closest_static(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id);
+/* Diagnostic, host-only (needs no device and no context; NO COUNTERPART IN THE REFERENCE): 1 when an object made of this mesh, this
+ * model matrix (column-major 4x4, as rt_object.model) and this material qualifies for the first-hit filter of the light-less path
+ * tracer — metallic == 1 with finite albedo / roughness; vertex normals finite, 0.5 - 2 long and, per triangle,
+ * within a half space of their sum; mat3(model) finite, of ordinary size and conditioned below 1e4 — and 0 otherwise or for a
+ * malformed mesh.  The image never depends on the answer: the filter only ends paths whose outcome is exactly what the hit shader
+ * computes for them (simple.rchit:403-449 and :690-700, simple.rgen:111-118); objects that do not qualify go through the hit shader. */
+RT_API int rt_filter_qualifies(const rt_mesh* mesh, const float model[16], const rt_material* material);
 /* BVH download for the bit-exact comparison with the deterministic CPU twin.
  * nodes: n_nodes x 128 B, tris: n_triangles x 48 B, morton/sorted ids: n_triangles each; NULL skips. */
 RT_API int rt_get_bvh(rt_ctx* ctx, void* nodes, size_t nodes_bytes, void* tris, size_t tris_bytes, uint64_t* morton,

@@ -195,8 +195,9 @@ void rt_destroy(rt_ctx* ctx) {
 // True when every vertex normal is finite with length in [0.5, 2] and, for every triangle, each of its three normals has a
 // dot product >= 0.25 with their sum g: any barycentric mix n of them then has g . n >= 0.25, i.e. |n| >= 0.25 / |g| >= 0.04 —
 // finite and safely non-zero (pairwise angles up to ~100 degrees pass, which coarse smooth-shaded meshes need).
-static bool mesh_normals_safe(const HostMesh& m) {
-    for (const rt_vertex& v : m.v) {
+static bool mesh_normals_safe(const rt_vertex* vtx, size_t nv, const uint32_t* idx, size_t ni) {
+    for (size_t q = 0; q < nv; q++) {
+        const rt_vertex& v = vtx[q];
         double l2 = 0.0;
         for (int k = 0; k < 3; k++) {
             if (!std::isfinite(v.normal[k])) return false;
@@ -204,8 +205,8 @@ static bool mesh_normals_safe(const HostMesh& m) {
         }
         if (!(l2 >= 0.25 && l2 <= 4.0)) return false;
     }
-    for (size_t t = 0; t + 2 < m.idx.size(); t += 3) {
-        const float* n[3] = {m.v[m.idx[t]].normal, m.v[m.idx[t + 1]].normal, m.v[m.idx[t + 2]].normal};
+    for (size_t t = 0; t + 2 < ni; t += 3) {
+        const float* n[3] = {vtx[idx[t]].normal, vtx[idx[t + 1]].normal, vtx[idx[t + 2]].normal};
         const double g[3] = {(double)n[0][0] + n[1][0] + n[2][0], (double)n[0][1] + n[1][1] + n[2][1], (double)n[0][2] + n[1][2] + n[2][2]};
         for (int i = 0; i < 3; i++)
             if (!(n[i][0] * g[0] + n[i][1] * g[1] + n[i][2] * g[2] >= 0.25)) return false;
@@ -426,7 +427,7 @@ int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const 
         hm[i].idx.assign(m.indices, m.indices + m.n_indices);
         hm[i].vertex_base = (uint32_t)nv;
         hm[i].index_base = (uint32_t)ni;
-        hm[i].normals_safe = mesh_normals_safe(hm[i]);
+        hm[i].normals_safe = mesh_normals_safe(hm[i].v.data(), hm[i].v.size(), hm[i].idx.data(), hm[i].idx.size());
         nv += m.n_vertices;
         ni += m.n_indices;
     }
@@ -459,6 +460,16 @@ int rt_build_scene(rt_ctx* ctx, const rt_mesh* meshes, uint32_t n_meshes, const 
     ctx->tables_dirty = true;
     ctx->geometry_dirty = true;
     return rt_flush_scene(ctx);
+}
+
+// host-only diagnostic: the three checks behind DevObject::dead_diffuse for one (mesh, matrix, material) combination
+int rt_filter_qualifies(const rt_mesh* mesh, const float model[16], const rt_material* material) {
+    if (!mesh || !model || !material) return 0;
+    if ((mesh->n_vertices && !mesh->vertices) || (mesh->n_indices && !mesh->indices) || (mesh->n_indices % 3u) != 0u) return 0;
+    for (uint32_t k = 0; k < mesh->n_indices; k++)
+        if (mesh->indices[k] >= mesh->n_vertices) return 0;
+    return (mesh_normals_safe(mesh->vertices, mesh->n_vertices, mesh->indices, mesh->n_indices) && model_matrix_safe(model) &&
+            material_dead_diffuse(*material)) ? 1 : 0;
 }
 
 int rt_scene_info_get(rt_ctx* ctx, rt_scene_info* out) {

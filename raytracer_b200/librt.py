@@ -35,6 +35,7 @@ EXPORTS = (
     "rt_default_restir_params", "rt_restir_frame", "rt_readback_reservoirs", "rt_get_counters", "rt_reset_counters",
     "rt_last_trace_ms", "rt_event_record", "rt_event_elapsed_ms", "rt_event_elapsed_per_device", "rt_set_profiling", "rt_get_kernel_profile",
     "rt_trace_rays_closest", "rt_trace_rays_any", "rt_get_bvh", "rt_static_max_rays", "rt_trace_rays_closest_static",
+    "rt_filter_qualifies",
 )
 
 
@@ -158,9 +159,24 @@ def load() -> C.CDLL:
     L.rt_static_max_rays.argtypes = []
     L.rt_static_max_rays.restype = u32
     L.rt_trace_rays_closest_static.argtypes = [vp, f32p, u32, vp, vp]
+    L.rt_filter_qualifies.argtypes = [C.POINTER(RtMesh), vp, vp]
+    L.rt_filter_qualifies.restype = C.c_int
     L.rt_get_bvh.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t, vp, vp]
     _lib = L
     return L
+
+
+def filter_qualifies(mesh, model_matrix, material) -> bool:
+    """rt_filter_qualifies (host-only, needs no GPU): would hits on an object made of this Mesh, 4x4 column-major model matrix and
+    Material qualify for the first-hit filter?"""
+    L = load()
+    v = np.ascontiguousarray(mesh.vertices)
+    ix = np.ascontiguousarray(mesh.indices, dtype=np.uint32)
+    m = RtMesh()
+    m.vertices, m.n_vertices, m.indices, m.n_indices = v.ctypes.data, len(v), ix.ctypes.data, len(ix)
+    mm = np.ascontiguousarray(np.asarray(model_matrix, np.float32).reshape(16))
+    rec = np.ascontiguousarray(material.packed().reshape(1))
+    return bool(L.rt_filter_qualifies(C.byref(m), mm.ctypes.data, rec.ctypes.data))
 
 
 def _p(a):

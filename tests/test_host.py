@@ -233,3 +233,36 @@ def test_strip_balancer_keeps_the_partition_and_converges():
         assert o[n_full] == n_full % world
     assert b.best[0] < 1.012 < ratios[0]
     assert [int((b.best_owners() == r).sum()) for r in range(world)] == [int((rr == r).sum()) for r in range(world)]
+
+
+def test_which_objects_the_first_hit_filter_may_end_early():
+    """rt_filter_qualifies (host-only): the filter ends a path at a Lambert-lobe draw only on objects for which
+    every intermediate of the hit shader is provably finite — a NaN normal would turn `payload.hit` false and the pixel would get
+    the sky colour instead of nothing (simple.rchit:690-700, simple.rgen:106-118).  The checks are conservative: what fails them
+    simply goes through the hit shader."""
+    import raytracer_b200 as rb
+    from raytracer_b200 import librt, proxy_scenes
+
+    metal = rb.Material("metal", albedo=(0.9, 0.7, 0.4), roughness=0.6, metallic=1.0)
+    eye = np.eye(4, dtype=np.float32).T.reshape(16)
+    sphere, plane = rb.create_sphere(), rb.create_plane()
+    assert librt.filter_qualifies(sphere, eye, metal) and librt.filter_qualifies(plane, eye, metal)
+    # materials: anything but metallic == 1 keeps a non-zero Lambert lobe; non-finite parameters are left to the shader
+    for kw in (dict(metallic=0.999), dict(metallic=0.0), dict(metallic=1.0, roughness=float("nan")), dict(metallic=1.0, albedo=(0.5, float("inf"), 0.5))):
+        assert not librt.filter_qualifies(sphere, eye, rb.Material("m", **{**dict(albedo=(0.5, 0.5, 0.5), roughness=0.5), **kw}))
+    # meshes: no normals, non-finite normals, normals that can cancel inside a triangle, normals of the wrong length
+    for edit in (lambda n: n.__setitem__(slice(None), 0.0), lambda n: n.__setitem__((3, 1), np.nan), lambda n: n.__setitem__(slice(None, None, 2), -n[::2]),
+                 lambda n: n.__setitem__(slice(None), n * 3.0)):
+        m = rb.create_sphere()
+        edit(m.vertices["normal"])
+        assert not librt.filter_qualifies(m, eye, metal)
+    # matrices: uniform scales of ordinary size pass, a squash by 1e-5, a singular, a huge and a non-finite matrix do not
+    def scaled(sx, sy, sz):
+        return np.diag([sx, sy, sz, 1.0]).astype(np.float32).reshape(16)
+    assert librt.filter_qualifies(sphere, scaled(0.008, 0.008, 0.008), metal) and librt.filter_qualifies(sphere, scaled(50, 20, 80), metal)
+    for mm in (scaled(0.5, 1e-5, 0.5), scaled(1, 0, 1), scaled(1e7, 1e7, 1e7), scaled(np.nan, 1, 1)):
+        assert not librt.filter_qualifies(sphere, mm, metal)
+    # the benchmarked scene: the reference's loader leaves every glTF material metallic, most of the proxy qualifies
+    s = proxy_scenes.sponza_proxy()
+    q = [librt.filter_qualifies(s.meshes[o.mesh_index], o.transform.model_matrix, s.materials[o.material_index]) for o in s.objects]
+    assert 0.75 * len(q) < sum(q) < len(q)
