@@ -170,10 +170,11 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / max(args.steps, 1), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.scene} {W}x{H} depth {args.max_depth} rr 3, {args.spp_per_step} spp per step",
-                       "sample": f"rows {band[0]}..{band[1]} of one frame per step"},
+            # the arm's own `config` (workload string identical to the CUDA arm's); what was sampled is said in cpu_baseline.sample
+            "config": {"workload": f"{args.scene} {W}x{H} depth {args.max_depth} rr 3, {args.spp_per_step} spp per step"},
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port",
-                             "sample": f"{args.steps} steps x {rows} rows x {W} px, frames 1..{args.steps}"},
+                             "sample": f"{args.steps} steps x rows {band[0]}..{band[1]} ({rows} rows) x {W} px of one frame per step, "
+                                       f"frames 1..{args.steps}"},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "reference GLSL/Vulkan path unavailable on this box; CPU port of the same shader math (oracle/)"}
