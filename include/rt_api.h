@@ -328,7 +328,7 @@ RT_API uint32_t rt_static_max_rays(void);
 RT_API int rt_trace_rays_closest_static(rt_ctx* ctx, const float* rays, uint32_t n, float* out_tuv, uint32_t* out_id);
 /* Diagnostic, host-only (needs no device and no context; NO COUNTERPART IN THE REFERENCE): 1 when an object made of this mesh, this
  * model matrix (column-major 4x4, as rt_object.model) and this material qualifies for the first-hit filter of the light-less path
- * tracer — metallic == 1 with finite albedo / roughness; vertex normals finite, 0.5 - 2 long and, per triangle,
+ * tracer — metallic == 1 with albedo and roughness finite and at most 1e6 in magnitude; vertex normals finite, 0.5 - 2 long and, per triangle,
  * within a half space of their sum; mat3(model) finite, of ordinary size and conditioned below 1e4 — and 0 otherwise or for a
  * malformed mesh.  The image never depends on the answer: the filter only ends paths whose outcome is exactly what the hit shader
  * computes for them (simple.rchit:403-449 and :690-700, simple.rgen:111-118); objects that do not qualify go through the hit shader. */

@@ -233,9 +233,13 @@ static bool model_matrix_safe(const float* model16) {
     const double fro = std::sqrt(fro2), inv_fro = std::sqrt(cof2) / std::fabs(det);
     return fro >= 1e-6 && fro <= 1e6 && std::isfinite(inv_fro) && fro * inv_fro <= 1e4;
 }
+// metallic == 1 makes albedo * (1 - metallic) an exact zero; albedo and roughness must be finite AND of ordinary size: a roughness
+// beyond ~1e19 overflows D_GGX's alpha^2 into inf / inf = NaN, the pdf test of simple.rchit:693 then fails and the path gets a
+// sky term instead of ending quietly (glTF keeps both in [0, 1]; the bound is generous).
 static bool material_dead_diffuse(const rt_material& m) {
-    return m.metallic == 1.0f && std::isfinite(m.albedo[0]) && std::isfinite(m.albedo[1]) && std::isfinite(m.albedo[2]) &&
-           std::isfinite(m.roughness);
+    for (int k = 0; k < 3; k++)
+        if (!(std::fabs(m.albedo[k]) <= 1e6f)) return false;  // also rejects NaN
+    return m.metallic == 1.0f && std::fabs(m.roughness) <= 1e6f;
 }
 
 static void make_dev_object(const rt_ctx* ctx, uint32_t i, uint32_t tri_offset, DevObject* o) {

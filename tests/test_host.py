@@ -248,7 +248,8 @@ def test_which_objects_the_first_hit_filter_may_end_early():
     sphere, plane = rb.create_sphere(), rb.create_plane()
     assert librt.filter_qualifies(sphere, eye, metal) and librt.filter_qualifies(plane, eye, metal)
     # materials: anything but metallic == 1 keeps a non-zero Lambert lobe; non-finite parameters are left to the shader
-    for kw in (dict(metallic=0.999), dict(metallic=0.0), dict(metallic=1.0, roughness=float("nan")), dict(metallic=1.0, albedo=(0.5, float("inf"), 0.5))):
+    for kw in (dict(metallic=0.999), dict(metallic=0.0), dict(metallic=1.0, roughness=float("nan")), dict(metallic=1.0, albedo=(0.5, float("inf"), 0.5)),
+               dict(metallic=1.0, roughness=1e20), dict(metallic=1.0, albedo=(0.5, 0.5, -3e7))):  # alpha^2 would overflow D_GGX
         assert not librt.filter_qualifies(sphere, eye, rb.Material("m", **{**dict(albedo=(0.5, 0.5, 0.5), roughness=0.5), **kw}))
     # meshes: no normals, non-finite normals, normals that can cancel inside a triangle, normals of the wrong length
     for edit in (lambda n: n.__setitem__(slice(None), 0.0), lambda n: n.__setitem__((3, 1), np.nan), lambda n: n.__setitem__(slice(None, None, 2), -n[::2]),

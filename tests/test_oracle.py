@@ -296,8 +296,9 @@ def test_dead_diffuse_rule_of_the_first_hit_filter(oracle_lib):
     n_claimed = 0
     for k in range(20000):
         m = np.zeros(11, np.float32)
-        m[0:3] = rng.choice([0.0, 1.0, rng.random()], 3) if k % 5 == 0 else rng.random(3)
-        m[7] = rng.choice([0.0, 1.0, rng.random()])   # roughness
+        # every third sample at the bounds rt_filter_qualifies admits (|albedo|, |roughness| <= 1e6), the rest in glTF's [0, 1]
+        m[0:3] = rng.choice([0.0, 1.0, 1e6, -1e6, rng.random()], 3) if k % 3 == 0 else rng.random(3)
+        m[7] = rng.choice([0.0, 1.0, 1e6, -1e6, rng.random()]) if k % 3 == 0 else rng.choice([0.0, 1.0, rng.random()])   # roughness
         m[8] = 1.0                                       # metallic
         th = rng.choice([0.0, 1e-7, np.pi / 2 - 1e-6, np.pi / 2, np.pi / 2 + 0.3, rng.random() * np.pi / 2])
         ph = rng.random() * 2 * np.pi
@@ -317,7 +318,7 @@ def test_dead_diffuse_rule_of_the_first_hit_filter(oracle_lib):
             assert np.isfinite(o8[6]) and o8[6] > 0.0, (k, o8)                # finite positive pdf -> payload.hit stays true
             thr = np.float32(1.0) * (o8[3:6] * o8[2] / o8[6])                  # simple.rchit:694
             assert (thr == 0.0).all()
-    assert n_claimed > 3000
+    assert n_claimed > 2500
 
 
 @pytest.mark.skipif(not os.path.isdir("/root/reference/shaders"), reason="reference mount absent (the fixture itself is committed)")
